@@ -1,0 +1,160 @@
+/* pokec_b200.h -- C ABI of libpokec_b200.so: the B200 (sm_100a) scoring path behind the reference's
+ * C++ `Recommender` (pymlex/recommendation-system-pokec, include/recommender.h:17-71).
+ *
+ * Everything the reference's Recommender computes on the hot path -- Fill-Aware Similarity (FAS),
+ * per-column idf, candidate scoring with top-k, collaborative friend / club propagation -- is
+ * reached through the entry points below.  Plain pointers and sizes only; all array arguments are
+ * HOST pointers unless the name starts with `d_` (device pointers, used by the multi-GPU plumbing).
+ * The library copies what it keeps.  There is NO CPU fallback: every scoring entry point needs a
+ * CUDA device and fails with PK_ERR_CUDA otherwise.
+ *
+ * Threading: one pk_store may be used from one host thread at a time (the reference's callers are
+ * single-threaded: src/api_cli.cpp:176, python/app.py:56-59).  Nothing is ever written to stdout
+ * (stdout is api_cli's JSON channel, src/api_cli.cpp:172-255); diagnostics go to pk_last_error().
+ *
+ * Reference-side binding: see INTEGRATION.md (replacement translation units for recommender*.cpp
+ * that implement the unchanged include/recommender.h on top of this ABI).
+ */
+#ifndef POKEC_B200_H
+#define POKEC_B200_H
+
+#include <stdint.h>
+#include "pokec_world.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct pk_store pk_store;
+
+enum {
+    PK_OK = 0,
+    PK_ERR_ARG = -1,         /* bad argument (null pointer, negative size, ...) */
+    PK_ERR_CUDA = -2,        /* CUDA runtime failure or no device */
+    PK_ERR_UNSUPPORTED = -3, /* outside the supported envelope (T > 64, token id >= 2^26, k > 256) */
+    PK_ERR_STATE = -4        /* call order (no world loaded, ...) */
+};
+
+/* ---- life cycle ------------------------------------------------------------------------------ */
+
+/* Message of the last failing call on this thread (never NULL). */
+const char* pk_last_error(void);
+
+/* ABI version of this header (PK_ABI_VERSION). */
+#define PK_ABI_VERSION 1
+int pk_abi_version(void);
+
+/* Number of CUDA devices visible (0 when there is none; never fails). */
+int pk_device_count(void);
+
+/* Replaces `Recommender::Recommender(profiles*, adj_list*)` (src/recommender.cpp:9-16): an empty
+ * store bound to CUDA device `device`. */
+int pk_store_create(int device, pk_store** out);
+void pk_store_destroy(pk_store* s);
+
+/* Uploads the flat form of `profiles` + `adj_list` (include/user_profile.h:10-20,
+ * include/recommender.h:46-49) and the normalizers carried by `w` (may be all-absent).  Token ids
+ * must be < 2^26 and n_text_cols <= 64.  Cells need not be sorted (sorted on ingest). */
+int pk_store_load_world(pk_store* s, const pk_world* w);
+
+/* Candidate shard for the full scan: rows [row_begin,row_end) of the loaded world (world order).
+ * Queries may be any loaded user.  Default: all rows.  (north_star: candidates partitioned by
+ * user-id range across the GPUs of one box.) */
+int pk_store_set_shard(pk_store* s, int64_t row_begin, int64_t row_end);
+
+/* Replaces set_field_normalizers + set_column_normalizers (src/recommender.cpp:27-33): `n_fields`
+ * = 7 + T entries, the 7 fixed keys (public, gender, completion, age, region, clubs, friends)
+ * followed by the text columns.  has[i]==0 means "no entry in the map" (z = 6(s-0.5),
+ * src/recommender_similarity.cpp:28-36). */
+int pk_set_normalizers(pk_store* s, const float* mean, const float* sd, const uint8_t* has, int n_fields);
+
+/* Replaces Recommender::compute_idf_from_profiles (src/recommender.cpp:43-66): per column document
+ * frequencies on the device, idf = logf(1 + N/(1+df)) (float, evaluated with the host libm so the
+ * table is bit-identical to the reference's).  double_log != 0 selects TFIDFIndex::build's variant
+ * (src/tfidf_index.cpp:7-30: (float)log(1.0 + N/(1.0+df)) in double). */
+int pk_compute_idf(pk_store* s, int double_log);
+
+/* Replaces Recommender::set_tfidf_index for one column (src/recommender.cpp:35-37): the column's
+ * idf map becomes exactly {token[i] -> idf[i]}.  Tokens absent from the map score with idf 1.0f
+ * (src/recommender.cpp:78).  n < 0 erases the column's entry: that column then uses the raw-count
+ * cosine (src/recommender.cpp:141-163 via src/recommender_similarity.cpp:99-104). */
+int pk_set_idf(pk_store* s, int col, const int32_t* token, const float* idf, int64_t n);
+
+/* Reads back a column's idf map (the public member idf_per_col, include/recommender.h:53), sorted
+ * by token id.  pk_idf_size returns -1 in *n when the column has no entry.  df may be NULL; it is 0
+ * for entries that came from pk_set_idf. */
+int pk_idf_size(pk_store* s, int col, int64_t* n);
+int pk_get_idf(pk_store* s, int col, int32_t* token, float* idf, int32_t* df, int64_t cap);
+
+/* Replaces one row of the caller-owned adjacency after the caller mutated it behind the
+ * Recommender (src/test.cpp:59-73).  n == 0 keeps an empty row; the row is created if missing. */
+int pk_set_adj_row(pk_store* s, int32_t uid, const int32_t* nb, int64_t n);
+
+/* ---- scoring --------------------------------------------------------------------------------- */
+
+/* Replaces Recommender::profile_similarity (src/recommender_similarity.cpp:10-128) for n pairs
+ * (A = a_uid[i], B = b_uid[i]).  out[i] = -1 when either uid has no profile. */
+int pk_pair_similarity(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid, float* out);
+
+/* Per-field float similarities of n pairs: out[i*(3+T) + j], j = 0 region, 1 clubs, 2 friends,
+ * 3+t text column t; -1 = field absent on either side.  (The float rounding points of
+ * src/recommender.cpp:116,127,138.) */
+int pk_pair_fields(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid, float* out);
+
+/* Set-overlap counts of n pairs (which: 0 clubs, 1 friends), the integer numerator of
+ * vec_set_similarity (src/recommender.cpp:119-128); -1 when either uid has no profile. */
+int pk_pair_overlap(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid, int which, int32_t* out);
+
+/* The north-star path: FAS of every query against EVERY candidate profile of the shard, top-k by
+ * the reference comparator (score desc, uid asc; src/recommender_graph.cpp:97-100).
+ * exclude_mode: PK_EXCLUDE_* (pokec_world.h).  out_id/out_score are [nq][k] (unused slots: -1 / 0),
+ * out_cnt[nq] the number of valid entries.  Unknown query uid -> cnt 0. */
+int pk_fullscan_topk(pk_store* s, int nq, const int32_t* q_uid, int k, int exclude_mode,
+                     int32_t* out_id, float* out_score, int32_t* out_cnt);
+
+/* Batched form of the reference's recommend calls (include/recommender.h:24-28):
+ *   PK_MODE_GRAPH  recommend_graph_registration == recommend_by_interest (src/recommender_graph.cpp:33-103,224-227)
+ *   PK_MODE_COLLAB recommend_collaborative (src/recommender_graph.cpp:105-222)
+ *   PK_MODE_CLUBS  recommend_clubs_collab (src/recommender_clubs.cpp:10-73; out_id = club ids, limit ignored)
+ * Same output layout as pk_fullscan_topk. */
+int pk_recommend(pk_store* s, int mode, int nq, const int32_t* q_uid, int k, int limit,
+                 int32_t* out_id, float* out_score, int32_t* out_cnt);
+
+/* Candidate id lists of one user (integer contract): PK_MODE_GRAPH = gather_candidates_local
+ * (src/recommender_graph.cpp:10-31), PK_MODE_COLLAB = the FoF expansion of :114-125.
+ * Returns the list length in *n (may exceed cap; only cap entries are written). */
+int pk_candidates(pk_store* s, int mode, int32_t uid, int limit, int32_t* out, int64_t cap, int64_t* n);
+
+/* ---- multi-GPU plumbing (one process per GPU; the all-gather itself is the caller's NCCL) ----- */
+
+/* Local top-k of the shard as packed sort keys on the DEVICE: d_keys is a device buffer of
+ * nq*k uint64 ((float bits << 33) | (~(uid ^ 0x80000000) << 1) | 1; 0 = empty slot).  Asynchronous
+ * on the store's stream: call pk_sync() before another stream or library reads d_keys. */
+int pk_fullscan_local_keys(pk_store* s, int nq, const int32_t* q_uid, int k, int exclude_mode, uint64_t* d_keys);
+
+/* Merges n_lists key lists ([n_lists][nq][k] on the device, e.g. the all-gathered per-rank lists)
+ * into the final host result. */
+int pk_merge_keys(pk_store* s, const uint64_t* d_keys, int n_lists, int nq, int k,
+                  int32_t* out_id, float* out_score, int32_t* out_cnt);
+
+int pk_sync(pk_store* s);
+/* The CUDA stream (cudaStream_t) every kernel of this store is launched on. */
+void* pk_stream(pk_store* s);
+
+/* ---- introspection (bench / tests) ----------------------------------------------------------- */
+
+enum {
+    PK_STAT_KERNEL_LAUNCHES = 0,   /* kernels launched by this store since creation */
+    PK_STAT_PAIRS_SCORED = 1,      /* (query, candidate) pairs of the last scoring call */
+    PK_STAT_STORE_BYTES = 2,       /* bytes of the packed device record store (whole world) */
+    PK_STAT_SCAN_KERNEL_NS = 3,    /* device time of the scan kernel(s) of the last scoring call (CUDA events) */
+    PK_STAT_SCAN_LAUNCHES = 4,     /* scan kernel launches of the last scoring call */
+    PK_STAT_GROUPS = 5,            /* query groups of the last scoring call */
+    PK_STAT_SHARD_RECORD_BYTES = 6 /* bytes of the packed records inside the candidate shard */
+};
+int64_t pk_stat(pk_store* s, int which);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

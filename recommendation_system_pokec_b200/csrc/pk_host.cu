@@ -1,0 +1,1463 @@
+// pk_host.cu -- host side of libpokec_b200.so: the C ABI of include/pokec_b200.h.
+//
+// Host work is limited to what the reference's Recommender also does outside the per-pair math:
+// uid -> row lookup, walking the caller's adjacency to enumerate candidates in the reference's
+// order (src/recommender_graph.cpp:10-31,114-125), planning query groups, and decoding results.
+// Every similarity, every idf count and every top-k selection runs in the sm_100a kernels of
+// pk_build.cuh / pk_scan.cuh.  There is no CPU scoring path.
+#include "pokec_b200.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <unordered_map>
+#include <unordered_set>
+#include <vector>
+
+#include "pk_layout.h"
+#include "pk_build.cuh"
+#include "pk_scan.cuh"
+#include "pk_clubs.cuh"
+
+using namespace pk;
+
+namespace {
+
+thread_local std::string g_err = "";
+
+int fail(int code, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CK(call)                                                                                       \
+    do {                                                                                               \
+        cudaError_t e_ = (call);                                                                       \
+        if (e_ != cudaSuccess)                                                                         \
+            return fail(PK_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+    } while (0)
+
+#define TRY(call)                 \
+    do {                          \
+        int rc_ = (call);         \
+        if (rc_ != PK_OK) return rc_; \
+    } while (0)
+
+// grow-only device buffer
+template <class T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t n) {
+        if (n <= cap) return PK_OK;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = n + n / 4 + 16;
+        cudaError_t e = cudaMalloc((void**)&p, want * sizeof(T));
+        if (e != cudaSuccess) return fail(PK_ERR_CUDA, "cudaMalloc(%zu bytes): %s", want * sizeof(T), cudaGetErrorString(e));
+        cap = want;
+        return PK_OK;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    ~DevBuf() { release(); }
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+};
+
+int log2_table(uint64_t entries) {   // smallest L >= 1 with 2^L >= 2*entries
+    int L = 1;
+    while ((1ull << L) < 2 * entries) ++L;
+    return L;
+}
+
+// host restatement of the reference's logistic / z (src/recommender_similarity.cpp:18-36); used ONLY to
+// tabulate constants that depend on the normalizers, never on a pair of profiles.
+double h_sigmoid(double x) {
+    if (x >= 0) { double e = std::exp(-x); return 1.0 / (1.0 + e); }
+    double e = std::exp(x);
+    return e / (1.0 + e);
+}
+
+}  // namespace
+
+struct pk_store {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int max_smem = 0;
+
+    // ---- host-side view of the world -------------------------------------------------------
+    int n = 0, T = 0;
+    bool loaded = false;
+    std::vector<int32_t> uid;
+    std::vector<std::pair<int32_t, int32_t>> uid_sorted;   // (uid, row)
+    std::vector<uint32_t> h_ncl, h_nfr, h_ntok;
+    std::vector<int32_t> adj_uid;
+    std::vector<int64_t> adj_ptr;
+    std::vector<int32_t> adj;
+    std::unordered_map<int32_t, int32_t> adj_row;
+    std::unordered_map<int32_t, std::vector<int32_t>> adj_override;
+
+    // ---- device raw world ---------------------------------------------------------------------
+    DevBuf<int32_t> d_uid, d_pub, d_comp, d_gender, d_age, d_region, d_tok_id, d_tok_tf;
+    DevBuf<int64_t> d_clubs_ptr, d_friends_ptr, d_tok_ptr;
+    DevBuf<uint32_t> d_clubs, d_friends;
+    int64_t nnz = 0;
+
+    // ---- idf ------------------------------------------------------------------------------------
+    std::vector<uint8_t> col_state;   // 0 absent, 1 computed from profiles, 2 caller-supplied
+    std::vector<std::vector<int32_t>> custom_tok;
+    std::vector<std::vector<float>> custom_idf;
+    int double_log = 0;
+    bool idf_dirty = true;
+    DevBuf<uint32_t> d_idf_key, d_idf_df;
+    DevBuf<float> d_idf_val;
+    int idf_log_cap = 0;
+    DevBuf<uint8_t> d_col_has;
+
+    // ---- normalizers ----------------------------------------------------------------------------
+    std::vector<float> nmean, nsd;
+    std::vector<uint8_t> nhas;
+    bool norm_dirty = true;
+    int max_comp = 0, max_age = 0;
+    DevBuf<NormTables> d_norm;
+    DevBuf<double> d_tab_comp, d_tab_age;
+
+    // ---- packed store ---------------------------------------------------------------------------
+    bool store_dirty = true;
+    DevBuf<uint4> d_rec;
+    DevBuf<uint64_t> d_rec_off;
+    std::vector<uint64_t> h_rec_off;
+    uint64_t store_u4 = 0;
+    int64_t shard_begin = 0, shard_end = 0;
+
+    // ---- per-call scratch (grow-only) -------------------------------------------------------------
+    DevBuf<GroupDesc> d_groups;
+    DevBuf<WorkItem> d_items;
+    DevBuf<uint8_t> d_arena;
+    DevBuf<int32_t> d_excl, d_cand_rows, d_i32a, d_i32b, d_i32c, d_i32d, d_i32e;
+    DevBuf<int64_t> d_i64a;
+    DevBuf<uint64_t> d_keys_a, d_keys_b, d_keys_c;
+    DevBuf<float> d_f32a, d_fields;
+    DevBuf<double> d_f64a;
+    DevBuf<uint32_t> d_u32a;
+    DevBuf<int> d_flag;
+    DevBuf<ClubEdge> d_edges;
+    int64_t last_idf_n = 0;
+
+    // ---- stats ------------------------------------------------------------------------------------
+    int64_t stat_launches = 0, stat_pairs = 0, stat_scan_ns = 0, stat_scan_launches = 0, stat_groups = 0;
+
+    int row_of(int32_t u) const {
+        auto it = std::lower_bound(uid_sorted.begin(), uid_sorted.end(), std::make_pair(u, INT32_MIN));
+        if (it == uid_sorted.end() || it->first != u) return -1;
+        return it->second;
+    }
+    // the caller's adjacency row (with pk_set_adj_row overrides); returns false when there is no row
+    bool adj_of(int32_t u, const int32_t** b, const int32_t** e) const {
+        if (!adj_override.empty()) {
+            auto io = adj_override.find(u);
+            if (io != adj_override.end()) {
+                *b = io->second.data();
+                *e = io->second.data() + io->second.size();
+                return true;
+            }
+        }
+        auto it = adj_row.find(u);
+        if (it == adj_row.end()) return false;
+        *b = adj.data() + adj_ptr[it->second];
+        *e = adj.data() + adj_ptr[it->second + 1];
+        return true;
+    }
+};
+
+namespace {
+
+template <class T>
+int upload(pk_store* s, DevBuf<T>& buf, const T* src, size_t n) {
+    TRY(buf.reserve(std::max<size_t>(n, 1)));
+    if (n) CK(cudaMemcpyAsync(buf.p, src, n * sizeof(T), cudaMemcpyHostToDevice, s->stream));
+    return PK_OK;
+}
+template <class T>
+int upload(pk_store* s, DevBuf<T>& buf, const std::vector<T>& v) {
+    return upload(s, buf, v.data(), v.size());
+}
+
+RawWorld raw_world(pk_store* s) {
+    RawWorld W;
+    W.n = s->n; W.T = s->T;
+    W.uid = s->d_uid.p; W.pub = s->d_pub.p; W.comp = s->d_comp.p; W.gender = s->d_gender.p; W.age = s->d_age.p;
+    W.region = s->d_region.p;
+    W.clubs_ptr = s->d_clubs_ptr.p; W.clubs = s->d_clubs.p;
+    W.friends_ptr = s->d_friends_ptr.p; W.friends = s->d_friends.p;
+    W.tok_ptr = s->d_tok_ptr.p; W.tok_id = s->d_tok_id.p; W.tok_tf = s->d_tok_tf.p;
+    return W;
+}
+
+IdfTable idf_table(pk_store* s) {
+    IdfTable I;
+    I.key = s->d_idf_key.p; I.df = s->d_idf_df.p; I.idf = s->d_idf_val.p; I.log_cap = s->idf_log_cap;
+    return I;
+}
+
+// ---- idf table ------------------------------------------------------------------------------------
+int rebuild_idf(pk_store* s) {
+    if (!s->idf_dirty) return PK_OK;
+    const int T = s->T;
+    bool any_computed = false;
+    uint64_t custom_entries = 0;
+    std::vector<uint8_t> computed(std::max(T, 1), 0), has(std::max(T, 1), 0);
+    for (int t = 0; t < T; ++t) {
+        computed[t] = s->col_state[t] == 1;
+        has[t] = s->col_state[t] != 0;
+        any_computed |= computed[t] != 0;
+        if (s->col_state[t] == 2) custom_entries += s->custom_tok[t].size();
+    }
+    TRY(upload(s, s->d_col_has, has));
+    uint64_t want = custom_entries + 1024;
+    if (any_computed) want += (uint64_t)s->nnz / 2;
+    int log_cap = std::max(10, log2_table(want) - 1);
+    DevBuf<uint8_t> d_computed;
+    TRY(upload(s, d_computed, computed));
+    TRY(s->d_flag.reserve(4));
+    for (;; ++log_cap) {
+        if (log_cap > 31) return fail(PK_ERR_UNSUPPORTED, "idf table would exceed 2^31 slots");
+        const size_t cap = (size_t)1 << log_cap;
+        TRY(s->d_idf_key.reserve(cap));
+        TRY(s->d_idf_df.reserve(cap));
+        TRY(s->d_idf_val.reserve(cap));
+        s->idf_log_cap = log_cap;
+        CK(cudaMemsetAsync(s->d_idf_key.p, 0xFF, cap * 4, s->stream));
+        CK(cudaMemsetAsync(s->d_idf_df.p, 0, cap * 4, s->stream));
+        CK(cudaMemsetAsync(s->d_idf_val.p, 0, cap * 4, s->stream));
+        CK(cudaMemsetAsync(s->d_flag.p, 0, sizeof(int), s->stream));
+        IdfTable I = idf_table(s);
+        if (any_computed && s->n > 0) {
+            const int64_t cells = (int64_t)s->n * T;
+            df_count_kernel<<<(unsigned)((cells + 255) / 256), 256, 0, s->stream>>>(raw_world(s), I, d_computed.p, s->d_flag.p);
+            ++s->stat_launches;
+            // idf(df) evaluated with the host libm: bit-identical to src/recommender.cpp:61 (logf, float)
+            // or src/tfidf_index.cpp:25 (double log, rounded to float)
+            std::vector<float> idf_of_df((size_t)s->n + 1);
+            const size_t total_users = (size_t)s->n;
+            for (size_t d = 0; d <= total_users; ++d) {
+                if (s->double_log) idf_of_df[d] = (float)std::log(1.0 + (double)(int)total_users / (1.0 + (double)(int)d));
+                else idf_of_df[d] = logf(1.0f + (float)total_users / (1.0f + (float)(int)d));
+            }
+            TRY(upload(s, s->d_f32a, idf_of_df));
+            CK(cudaStreamSynchronize(s->stream));   // idf_of_df is a local
+            idf_fill_kernel<<<(unsigned)((cap + 255) / 256), 256, 0, s->stream>>>(I, s->d_f32a.p, (int64_t)s->n);
+            ++s->stat_launches;
+        }
+        for (int t = 0; t < T; ++t) {
+            if (s->col_state[t] != 2 || s->custom_tok[t].empty()) continue;
+            const int64_t m = (int64_t)s->custom_tok[t].size();
+            TRY(upload(s, s->d_i32a, s->custom_tok[t]));
+            TRY(upload(s, s->d_f32a, s->custom_idf[t]));
+            idf_custom_kernel<<<(unsigned)((m + 255) / 256), 256, 0, s->stream>>>(I, t, s->d_i32a.p, s->d_f32a.p, m, s->d_flag.p);
+            ++s->stat_launches;
+            CK(cudaStreamSynchronize(s->stream));
+        }
+        int overflow = 0;
+        CK(cudaMemcpyAsync(&overflow, s->d_flag.p, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+        if (!overflow) break;
+    }
+    s->idf_dirty = false;
+    s->store_dirty = true;
+    return PK_OK;
+}
+
+// ---- normalizer constants ------------------------------------------------------------------------
+int rebuild_norm(pk_store* s) {
+    if (!s->norm_dirty) return PK_OK;
+    const int T = s->T, nf = kNumFixed + T;
+    NormTables N;
+    memset(&N, 0, sizeof(N));
+    auto z = [&](int f, double sv) -> double {
+        if (N.use_norm[f]) return (sv - N.mean[f]) / N.sd[f];
+        return 6.0 * (sv - 0.5);
+    };
+    for (int f = 0; f < nf; ++f) {
+        N.mean[f] = (double)s->nmean[f];
+        N.sd[f] = (double)s->nsd[f];
+        N.use_norm[f] = (s->nhas[f] && (double)s->nsd[f] > 0.0) ? 1 : 0;
+        N.sig0[f] = h_sigmoid(z(f, 0.0));
+        N.sig1[f] = h_sigmoid(z(f, 1.0));
+    }
+    N.total_possible = nf;
+    for (int u = 0; u <= nf; ++u) N.ftab[u] = (double)u / (double)nf;
+    for (int a = 0; a < 4; ++a)
+        for (int b = 0; b < 4; ++b)
+            for (int m = 0; m < 4; ++m) {
+                double v = 0.0;
+                if (a > 0 && b > 0) {
+                    float sv = (float)((double)m / (std::sqrt((double)a) * std::sqrt((double)b)));
+                    v = h_sigmoid(z(4, (double)sv));
+                }
+                N.region[(a * 4 + b) * 4 + m] = v;
+            }
+    N.dim_comp = std::min(std::max(s->max_comp, 0), 255) + 1;
+    N.dim_age = std::min(std::max(s->max_age, 0), 255) + 1;
+    for (int which = 0; which < 2; ++which) {
+        const int dim = which ? N.dim_age : N.dim_comp;
+        const int f = which ? 3 : 2;
+        std::vector<double> tab((size_t)dim * dim, 0.0);
+        for (int c = 1; c < dim; ++c)
+            for (int q = 1; q < dim; ++q) {
+                const int amin = std::min(c, q), amax = std::max(c, q);
+                tab[(size_t)c * dim + q] = h_sigmoid(z(f, (double)amin / (double)amax));
+            }
+        TRY(upload(s, which ? s->d_tab_age : s->d_tab_comp, tab));
+        CK(cudaStreamSynchronize(s->stream));
+    }
+    TRY(s->d_norm.reserve(1));
+    CK(cudaMemcpyAsync(s->d_norm.p, &N, sizeof(N), cudaMemcpyHostToDevice, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    s->norm_dirty = false;
+    return PK_OK;
+}
+
+// ---- packed record store ---------------------------------------------------------------------------
+int rebuild_store(pk_store* s) {
+    TRY(rebuild_idf(s));
+    if (!s->store_dirty) return PK_OK;
+    const int n = s->n;
+    s->h_rec_off.assign((size_t)n + 1, 0);
+    if (n > 0) {
+        TRY(s->d_u32a.reserve((size_t)2 * n));
+        const unsigned blocks = (unsigned)(((int64_t)n * 32 + 255) / 256);
+        record_size_kernel<<<blocks, 256, 0, s->stream>>>(raw_world(s), s->d_u32a.p, s->d_u32a.p + n);
+        ++s->stat_launches;
+        std::vector<uint32_t> sz((size_t)2 * n);
+        CK(cudaMemcpyAsync(sz.data(), s->d_u32a.p, sz.size() * 4, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+        s->h_ntok.assign(sz.begin() + n, sz.end());
+        for (int r = 0; r < n; ++r) s->h_rec_off[r + 1] = s->h_rec_off[r] + sz[r];
+    }
+    s->store_u4 = s->h_rec_off[n];
+    TRY(s->d_rec.reserve(std::max<uint64_t>(s->store_u4, 1)));
+    TRY(upload(s, s->d_rec_off, s->h_rec_off));
+    if (n > 0) {
+        const unsigned blocks = (unsigned)(((int64_t)n * 32 + 255) / 256);
+        pack_kernel<<<blocks, 256, 0, s->stream>>>(raw_world(s), idf_table(s), s->d_col_has.p, s->d_rec_off.p, s->d_rec.p);
+        ++s->stat_launches;
+    }
+    CK(cudaStreamSynchronize(s->stream));
+    CK(cudaGetLastError());
+    s->store_dirty = false;
+    return PK_OK;
+}
+
+int ensure_ready(pk_store* s) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
+    CK(cudaSetDevice(s->device));
+    TRY(rebuild_store(s));
+    TRY(rebuild_norm(s));
+    return PK_OK;
+}
+
+// ---- group planning --------------------------------------------------------------------------------
+
+struct Plan {
+    std::vector<GroupDesc> groups;
+    std::vector<int32_t> excl;    // concatenated exclusion ids
+    uint64_t arena_bytes = 0;
+    uint32_t max_smem_arena = 0;  // over groups that fit shared memory
+};
+
+uint32_t align16(uint32_t x) { return (x + 15u) & ~15u; }
+
+// lays out the tables of a group whose members are rows[0..n_lanes); excl_n = exclusion ids per lane
+void layout_group(pk_store* s, GroupDesc& g, const uint32_t* excl_n) {
+    uint64_t ncl = 0, nfr = 0, ntok = 0, nex = 0;
+    for (int l = 0; l < g.n_lanes; ++l) {
+        const int r = g.row[l];
+        if (r < 0) continue;
+        ncl += s->h_ncl[r]; nfr += s->h_nfr[r]; ntok += s->h_ntok[r];
+        if (excl_n) nex += excl_n[l];
+    }
+    g.log_sc = log2_table(ncl); g.log_sf = log2_table(nfr); g.log_sa = log2_table(nex); g.log_st = log2_table(ntok);
+    uint32_t off = 0;
+    g.off_nq = off; off += align16((uint32_t)s->T * 32u * 8u);
+    g.off_clubs = off; off += (8u << g.log_sc);
+    g.off_friends = off; off += (8u << g.log_sf);
+    g.off_adj = off; off += (8u << g.log_sa);
+    g.off_text = align16(off); off = g.off_text + (16u << g.log_st);
+    g.off_vals = off; off += align16((uint32_t)ntok * 8u);
+    g.n_vals = (uint32_t)ntok;
+    g.arena_bytes = align16(off);
+}
+
+uint32_t scan_fixed_smem(int Kp) {
+    const uint32_t norm = (uint32_t)((sizeof(NormTables) + 15) & ~15u);
+    return norm + 32u * Kp * 8u + 32u * 8u + 32u * 4u + 16u;
+}
+
+struct Launcher {
+    pk_store* s;
+    Plan* plan;
+    std::vector<WorkItem> items_sm, items_gl;
+};
+
+int upload_plan(pk_store* s, Plan& plan, bool with_excl) {
+    uint64_t off = 0;
+    for (auto& g : plan.groups) {
+        g.arena_off = (uint32_t)off;
+        off += g.arena_bytes;
+        if (off > 0xF0000000ull) return fail(PK_ERR_UNSUPPORTED, "query batch too large for one arena (split the batch)");
+    }
+    plan.arena_bytes = off;
+    TRY(s->d_arena.reserve(std::max<uint64_t>(off, 16)));
+    CK(cudaMemsetAsync(s->d_arena.p, 0, std::max<uint64_t>(off, 16), s->stream));
+    TRY(upload(s, s->d_groups, plan.groups));
+    if (with_excl) TRY(upload(s, s->d_excl, plan.excl));
+    if (!plan.groups.empty()) {
+        PrepParams P;
+        P.rec = s->d_rec.p; P.rec_off = s->d_rec_off.p; P.groups = s->d_groups.p; P.arena = s->d_arena.p;
+        P.excl_ids = with_excl ? s->d_excl.p : nullptr;
+        group_prep_kernel<<<(unsigned)plan.groups.size(), kPrepThreads, 0, s->stream>>>(P);
+        ++s->stat_launches;
+        CK(cudaGetLastError());
+    }
+    return PK_OK;
+}
+
+template <int EPI, bool FIELDS>
+int launch_scan_t(pk_store* s, ScanParams P, const std::vector<WorkItem>& items, bool sm, uint32_t smem_bytes) {
+    if (items.empty()) return PK_OK;
+    TRY(upload(s, s->d_items, items));
+    P.items = s->d_items.p;
+    CK(cudaEventRecord(s->ev0, s->stream));
+    if (sm) {
+        auto kern = fas_scan_kernel<true, EPI, FIELDS>;
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+        kern<<<(unsigned)items.size(), kScanThreads, smem_bytes, s->stream>>>(P);
+    } else {
+        auto kern = fas_scan_kernel<false, EPI, FIELDS>;
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+        kern<<<(unsigned)items.size(), kScanThreads, smem_bytes, s->stream>>>(P);
+    }
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(s->ev1, s->stream));
+    CK(cudaStreamSynchronize(s->stream));   // d_items is reused by the next launch
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+    s->stat_scan_ns += (int64_t)(ms * 1e6);
+    ++s->stat_scan_launches;
+    ++s->stat_launches;
+    return PK_OK;
+}
+
+// runs the scan for items whose group fits shared memory, then for the others
+template <int EPI, bool FIELDS>
+int run_scan(pk_store* s, const Plan& plan, ScanParams P, const std::vector<WorkItem>& items) {
+    std::vector<WorkItem> a, b;
+    for (const auto& it : items) (plan.groups[it.group].in_smem ? a : b).push_back(it);
+    const uint32_t fixed = scan_fixed_smem(EPI == EPI_TOPK ? P.Kp : 0);
+    P.smem_arena_bytes = plan.max_smem_arena;
+    TRY((launch_scan_t<EPI, FIELDS>(s, P, a, true, plan.max_smem_arena + fixed)));
+    P.smem_arena_bytes = 0;
+    TRY((launch_scan_t<EPI, FIELDS>(s, P, b, false, fixed)));
+    return PK_OK;
+}
+
+ScanParams base_scan_params(pk_store* s, int K) {
+    ScanParams P;
+    memset(&P, 0, sizeof(P));
+    P.rec = s->d_rec.p; P.rec_off = s->d_rec_off.p; P.groups = s->d_groups.p; P.arena = s->d_arena.p;
+    P.norm = s->d_norm.p; P.tab_comp = s->d_tab_comp.p; P.tab_age = s->d_tab_age.p;
+    P.T = s->T; P.K = K; P.Kp = (K + 31) / 32 * 32; P.exclude_mode = PK_EXCLUDE_NONE;
+    P.nf = 3 + s->T + 2;
+    return P;
+}
+
+void finish_group(pk_store* s, Plan& plan, GroupDesc& g, const uint32_t* excl_n, int Kp) {
+    layout_group(s, g, excl_n);
+    const uint32_t budget = (uint32_t)s->max_smem - scan_fixed_smem(Kp) - 256u;
+    g.in_smem = g.arena_bytes <= budget;
+    if (g.in_smem) plan.max_smem_arena = std::max(plan.max_smem_arena, g.arena_bytes);
+    plan.groups.push_back(g);
+}
+
+void decode_keys(const uint64_t* keys, int nq, int k, int32_t* out_id, float* out_score, int32_t* out_cnt) {
+    for (int q = 0; q < nq; ++q) {
+        int c = 0;
+        for (int i = 0; i < k; ++i) {
+            const uint64_t key = keys[(size_t)q * k + i];
+            if (key == 0ull) { out_id[(size_t)q * k + i] = -1; out_score[(size_t)q * k + i] = 0.0f; continue; }
+            out_id[(size_t)q * k + i] = key_id(key);
+            uint32_t b = key_score_bits(key);
+            float f;
+            memcpy(&f, &b, 4);
+            out_score[(size_t)q * k + i] = f;
+            ++c;
+        }
+        out_cnt[q] = c;
+    }
+}
+
+int check_topk_args(pk_store* s, int nq, const int32_t* q_uid, int k) {
+    if (nq < 0 || k < 0 || (nq > 0 && !q_uid)) return fail(PK_ERR_ARG, "bad nq/k/q_uid");
+    if (k > kMaxK) return fail(PK_ERR_UNSUPPORTED, "k = %d exceeds the supported maximum %d", k, kMaxK);
+    (void)s;
+    return PK_OK;
+}
+
+// ---- full scan ---------------------------------------------------------------------------------------
+// leaves the merged keys [nq][k] in s->d_keys_b
+int fullscan_device(pk_store* s, int nq, const int32_t* q_uid, int k, int exclude_mode) {
+    s->stat_scan_ns = 0; s->stat_scan_launches = 0; s->stat_pairs = 0; s->stat_groups = 0;
+    const int K = std::max(k, 1), Kp = (K + 31) / 32 * 32;
+    TRY(s->d_keys_b.reserve((size_t)std::max(nq, 1) * K));
+    CK(cudaMemsetAsync(s->d_keys_b.p, 0, (size_t)std::max(nq, 1) * K * 8, s->stream));
+    const int64_t n_cand = s->shard_end - s->shard_begin;
+    if (nq == 0 || k == 0 || n_cand <= 0) { CK(cudaStreamSynchronize(s->stream)); return PK_OK; }
+
+    // group the queries that have a profile, in caller order
+    Plan plan;
+    std::vector<int32_t> q_slot0(nq, 0), q_nl(nq, 0), q_lane(nq, 0);
+    GroupDesc g;
+    std::vector<uint32_t> excl_n(32, 0);
+    auto reset = [&]() {
+        memset(&g, 0, sizeof(g));
+        for (int l = 0; l < 32; ++l) { g.row[l] = -1; g.qidx[l] = -1; }
+        std::fill(excl_n.begin(), excl_n.end(), 0u);
+        g.adj_begin[0] = (int32_t)plan.excl.size();
+    };
+    reset();
+    const uint32_t budget = (uint32_t)s->max_smem - scan_fixed_smem(Kp) - 256u;
+    auto close_group = [&]() {
+        if (g.n_lanes == 0) return;
+        for (int l = g.n_lanes; l < 32; ++l) g.adj_begin[l + 1] = g.adj_begin[g.n_lanes];
+        finish_group(s, plan, g, excl_n.data(), Kp);
+        reset();
+    };
+    for (int q = 0; q < nq; ++q) {
+        const int r = s->row_of(q_uid[q]);
+        if (r < 0) continue;
+        const int32_t *ab = nullptr, *ae = nullptr;
+        uint32_t nex = 0;
+        if (exclude_mode >= PK_EXCLUDE_SELF_AND_ADJ && s->adj_of(q_uid[q], &ab, &ae)) nex = (uint32_t)(ae - ab);
+        if (g.n_lanes > 0) {   // would adding this query overflow the shared-memory budget?
+            GroupDesc t = g;
+            t.row[t.n_lanes] = r;
+            std::vector<uint32_t> en = excl_n;
+            en[t.n_lanes] = nex;
+            ++t.n_lanes;
+            layout_group(s, t, en.data());
+            if (t.arena_bytes > budget) close_group();
+        }
+        const int l = g.n_lanes;
+        g.row[l] = r; g.qidx[l] = q; excl_n[l] = nex;
+        if (nex) plan.excl.insert(plan.excl.end(), ab, ae);
+        g.adj_begin[l + 1] = (int32_t)plan.excl.size();
+        q_lane[q] = l;
+        q_slot0[q] = (int32_t)plan.groups.size();   // group index for now
+        q_nl[q] = 1;
+        ++g.n_lanes;
+        if (g.n_lanes == 32) close_group();
+    }
+    close_group();
+    const int ng = (int)plan.groups.size();
+    s->stat_groups = ng;
+    if (ng == 0) { CK(cudaStreamSynchronize(s->stream)); return PK_OK; }
+    TRY(upload_plan(s, plan, exclude_mode >= PK_EXCLUDE_SELF_AND_ADJ));
+
+    // work items: every group scans the whole shard, split into slices so that the grid fills the GPU
+    int sm_count = 148;
+    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, s->device);
+    int64_t splits = (int64_t)(sm_count * 6 + ng - 1) / ng;
+    splits = std::max<int64_t>(1, std::min<int64_t>(splits, (n_cand + 1023) / 1024));
+    std::vector<WorkItem> items;
+    std::vector<int32_t> g_slot0(ng);
+    for (int gi = 0; gi < ng; ++gi) {
+        g_slot0[gi] = (int32_t)items.size();
+        for (int64_t sp = 0; sp < splits; ++sp) {
+            WorkItem it;
+            it.group = gi;
+            it.cand_begin = (int32_t)(s->shard_begin + n_cand * sp / splits);
+            it.cand_end = (int32_t)(s->shard_begin + n_cand * (sp + 1) / splits);
+            it.out_slot = (int32_t)items.size();
+            items.push_back(it);
+        }
+        s->stat_pairs += (int64_t)plan.groups[gi].n_lanes * n_cand;
+    }
+    for (int q = 0; q < nq; ++q) {
+        if (q_nl[q] == 0) continue;
+        q_slot0[q] = g_slot0[q_slot0[q]];
+        q_nl[q] = (int32_t)splits;
+    }
+    TRY(s->d_keys_a.reserve(items.size() * 32 * (size_t)Kp));
+    ScanParams P = base_scan_params(s, K);
+    P.exclude_mode = exclude_mode;
+    P.out_keys = s->d_keys_a.p;
+    // out_slot must index d_keys_a for both launches: keep the original slots
+    TRY((run_scan<EPI_TOPK, false>(s, plan, P, items)));
+
+    TRY(upload(s, s->d_i32a, q_slot0));
+    TRY(upload(s, s->d_i32b, q_nl));
+    TRY(upload(s, s->d_i32c, q_lane));
+    MergeParams M;
+    memset(&M, 0, sizeof(M));
+    M.keys = s->d_keys_a.p; M.slot0 = s->d_i32a.p; M.n_lists_q = s->d_i32b.p; M.lane = s->d_i32c.p;
+    M.nq = nq; M.K = K; M.stride_k = Kp; M.out_keys = s->d_keys_b.p;
+    if (splits > 128 * 8) return fail(PK_ERR_UNSUPPORTED, "too many splits");
+    merge_topk_kernel<<<nq, 128, 0, s->stream>>>(M);
+    ++s->stat_launches;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(s->stream));
+    return PK_OK;
+}
+
+// ---- candidate enumeration on the host (integer, order-sensitive; mirrors the reference) -----------
+
+// src/recommender_graph.cpp:10-31
+void gather_candidates(const pk_store* s, int32_t user, int limit, std::vector<int32_t>& out) {
+    out.clear();
+    const int32_t *b, *e;
+    if (!s->adj_of(user, &b, &e)) return;
+    std::unordered_set<int32_t> seen;
+    for (const int32_t* pf = b; pf != e; ++pf) {
+        const int32_t f = *pf;
+        if (f == user) continue;
+        if (seen.insert(f).second) out.push_back(f);
+        if ((int)out.size() >= limit) return;
+        const int32_t *b2, *e2;
+        if (!s->adj_of(f, &b2, &e2)) continue;
+        for (const int32_t* pff = b2; pff != e2; ++pff) {
+            const int32_t ff = *pff;
+            if (ff == user) continue;
+            if (seen.insert(ff).second) {
+                out.push_back(ff);
+                if ((int)out.size() >= limit) return;
+            }
+        }
+    }
+}
+
+// src/recommender_graph.cpp:114-125 (limit < 0 = unlimited, used by the clubs path)
+void collab_candidates(const pk_store* s, int32_t user, const int32_t* fb, const int32_t* fe, int limit, bool limited,
+                       std::vector<int32_t>& out) {
+    out.clear();
+    std::unordered_set<int32_t> seen;
+    for (const int32_t* pf = fb; pf != fe; ++pf) {
+        const int32_t *b2, *e2;
+        if (!s->adj_of(*pf, &b2, &e2)) continue;
+        for (const int32_t* p = b2; p != e2; ++p) {
+            const int32_t fof = *p;
+            if (fof == user) continue;
+            if (seen.insert(fof).second) out.push_back(fof);
+            if (limited && (int)out.size() >= limit) break;
+        }
+        if (limited && (int)out.size() >= limit) break;
+    }
+}
+
+GroupDesc empty_group() {
+    GroupDesc g;
+    memset(&g, 0, sizeof(g));
+    for (int l = 0; l < 32; ++l) { g.row[l] = -1; g.qidx[l] = -1; }
+    return g;
+}
+
+// ---- recommend: graph / interest ---------------------------------------------------------------------
+int recommend_graph(pk_store* s, int nq, const int32_t* q_uid, int k, int limit, uint64_t* h_keys) {
+    const int K = std::max(k, 1), Kp = (K + 31) / 32 * 32;
+    Plan plan;
+    std::vector<int32_t> cand_rows;
+    std::vector<WorkItem> items;
+    std::vector<int32_t> q_slot0(nq, 0), q_nl(nq, 0), q_lane(nq, 0);
+    std::vector<int32_t> cands;
+    for (int q = 0; q < nq; ++q) {
+        const int32_t user = q_uid[q];
+        const int r = s->row_of(user);
+        if (r < 0) continue;                                    // src/recommender_graph.cpp:40
+        gather_candidates(s, user, limit, cands);
+        std::unordered_set<int32_t> existing;                   // :46-49
+        const int32_t *b, *e;
+        if (s->adj_of(user, &b, &e)) existing.insert(b, e);
+        existing.insert(user);
+        const int32_t c0 = (int32_t)cand_rows.size();
+        for (int32_t c : cands) {
+            if (existing.count(c)) continue;
+            const int rc = s->row_of(c);
+            if (rc < 0) continue;                               // :54
+            cand_rows.push_back(rc);
+        }
+        const int32_t c1 = (int32_t)cand_rows.size();
+        if (c1 == c0) continue;
+        GroupDesc g = empty_group();
+        g.n_lanes = 1; g.row[0] = r; g.qidx[0] = q;
+        WorkItem it;
+        it.group = (int32_t)plan.groups.size();
+        it.cand_begin = c0; it.cand_end = c1; it.out_slot = (int32_t)items.size();
+        finish_group(s, plan, g, nullptr, Kp);
+        q_slot0[q] = it.out_slot; q_nl[q] = 1; q_lane[q] = 0;
+        items.push_back(it);
+        s->stat_pairs += c1 - c0;
+    }
+    s->stat_groups = (int64_t)plan.groups.size();
+    std::vector<uint64_t> keys((size_t)std::max(nq, 1) * K, 0ull);
+    if (!items.empty()) {
+        TRY(upload_plan(s, plan, false));
+        TRY(upload(s, s->d_cand_rows, cand_rows));
+        TRY(s->d_keys_a.reserve(items.size() * 32 * (size_t)Kp));
+        TRY(s->d_keys_b.reserve((size_t)nq * K));
+        ScanParams P = base_scan_params(s, K);
+        P.cand_rows = s->d_cand_rows.p;
+        P.out_keys = s->d_keys_a.p;
+        TRY((run_scan<EPI_TOPK, false>(s, plan, P, items)));
+        TRY(upload(s, s->d_i32a, q_slot0));
+        TRY(upload(s, s->d_i32b, q_nl));
+        TRY(upload(s, s->d_i32c, q_lane));
+        MergeParams M;
+        memset(&M, 0, sizeof(M));
+        M.keys = s->d_keys_a.p; M.slot0 = s->d_i32a.p; M.n_lists_q = s->d_i32b.p; M.lane = s->d_i32c.p;
+        M.nq = nq; M.K = K; M.stride_k = Kp; M.out_keys = s->d_keys_b.p;
+        merge_topk_kernel<<<nq, 128, 0, s->stream>>>(M);
+        ++s->stat_launches;
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(keys.data(), s->d_keys_b.p, (size_t)nq * K * 8, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+    }
+    memcpy(h_keys, keys.data(), (size_t)nq * K * 8);
+    return PK_OK;
+}
+
+// ---- recommend: collaborative friends / clubs --------------------------------------------------------
+//
+// Both need w_f = FAS(user, f) for the user's friends and the matrix FAS(f, c) of friends x
+// friend-of-friend candidates (src/recommender_graph.cpp:127-136,167-180; src/recommender_clubs.cpp:23-64).
+// One store-mode scan computes both: per user one 1-lane group {user} x friends, and per 32 distinct
+// friends one group x candidates.
+struct CollabUser {
+    int q = -1;                       // caller-side query index
+    int32_t uid = 0;
+    int row = -1;
+    std::vector<int32_t> friends;     // adjacency row, in order (duplicates kept)
+    std::vector<int32_t> fr_slot;     // per friend entry: index among the distinct friends with a profile, -1 = none
+    std::vector<int32_t> slot_row;    // row of each distinct friend
+    std::vector<int32_t> slot_uid;
+    std::vector<int32_t> cands;       // candidate uids with a profile, in reference order
+    std::vector<int32_t> cand_row;
+    int32_t w_out0 = 0;               // first output row of the {user} x distinct-friends scan
+    int32_t mat_out0 = 0;             // first output row of the friends x cands scan ([group][cand])
+};
+
+int collab_prepare(pk_store* s, int nq, const int32_t* q_uid, int limit, bool limited, std::vector<CollabUser>& users,
+                   Plan& plan, std::vector<WorkItem>& items, std::vector<int32_t>& cand_rows, int64_t* out_rows) {
+    int64_t rows = 0;
+    std::vector<int32_t> tmp;
+    for (int q = 0; q < nq; ++q) {
+        CollabUser u;
+        u.q = q; u.uid = q_uid[q]; u.row = s->row_of(u.uid);
+        if (u.row < 0) continue;                                         // src/recommender_graph.cpp:130
+        const int32_t *b, *e;
+        if (s->adj_of(u.uid, &b, &e)) u.friends.assign(b, e);
+        std::unordered_map<int32_t, int32_t> slot_of;
+        for (int32_t f : u.friends) {
+            const int rf = s->row_of(f);
+            if (rf < 0) { u.fr_slot.push_back(-1); continue; }           // :134
+            auto ins = slot_of.emplace(f, (int32_t)u.slot_row.size());
+            if (ins.second) { u.slot_row.push_back(rf); u.slot_uid.push_back(f); }
+            u.fr_slot.push_back(ins.first->second);
+        }
+        collab_candidates(s, u.uid, u.friends.data(), u.friends.data() + u.friends.size(), limit, limited, tmp);
+        for (int32_t c : tmp) {
+            const int rc = s->row_of(c);
+            if (rc < 0) continue;                                        // :172
+            u.cands.push_back(c);
+            u.cand_row.push_back(rc);
+        }
+        const int nslots = (int)u.slot_row.size();
+        if (nslots > 0) {
+            // {user} x friends
+            GroupDesc g = empty_group();
+            g.n_lanes = 1; g.row[0] = u.row; g.qidx[0] = q;
+            WorkItem it;
+            it.group = (int32_t)plan.groups.size();
+            it.cand_begin = (int32_t)cand_rows.size();
+            cand_rows.insert(cand_rows.end(), u.slot_row.begin(), u.slot_row.end());
+            it.cand_end = (int32_t)cand_rows.size();
+            it.out_slot = (int32_t)rows;
+            u.w_out0 = (int32_t)rows;
+            rows += nslots;
+            finish_group(s, plan, g, nullptr, 0);
+            items.push_back(it);
+            s->stat_pairs += nslots;
+            // friends x candidates
+            if (!u.cands.empty()) {
+                const int32_t cb = (int32_t)cand_rows.size();
+                cand_rows.insert(cand_rows.end(), u.cand_row.begin(), u.cand_row.end());
+                const int32_t ce = (int32_t)cand_rows.size();
+                u.mat_out0 = (int32_t)rows;
+                for (int g0 = 0; g0 < nslots; g0 += 32) {
+                    GroupDesc gg = empty_group();
+                    gg.n_lanes = std::min(32, nslots - g0);
+                    for (int l = 0; l < gg.n_lanes; ++l) { gg.row[l] = u.slot_row[g0 + l]; gg.qidx[l] = q; }
+                    WorkItem it2;
+                    it2.group = (int32_t)plan.groups.size();
+                    it2.cand_begin = cb; it2.cand_end = ce; it2.out_slot = (int32_t)rows;
+                    rows += ce - cb;
+                    finish_group(s, plan, gg, nullptr, 0);
+                    items.push_back(it2);
+                    s->stat_pairs += (int64_t)gg.n_lanes * (ce - cb);
+                }
+            }
+        }
+        if (rows > 0x7fffff00ll / 32) return fail(PK_ERR_UNSUPPORTED, "collaborative batch too large (split the batch)");
+        users.push_back(std::move(u));
+    }
+    *out_rows = rows;
+    return PK_OK;
+}
+
+int recommend_collab(pk_store* s, int nq, const int32_t* q_uid, int k, int limit, uint64_t* h_keys) {
+    const int K = std::max(k, 1);
+    std::vector<CollabUser> users;
+    Plan plan;
+    std::vector<WorkItem> items;
+    std::vector<int32_t> cand_rows;
+    int64_t rows = 0;
+    TRY(collab_prepare(s, nq, q_uid, limit, true, users, plan, items, cand_rows, &rows));
+    s->stat_groups = (int64_t)plan.groups.size();
+    std::vector<uint64_t> keys((size_t)std::max(nq, 1) * K, 0ull);
+    const int nu = (int)users.size();
+    if (nu > 0 && rows > 0) {
+        TRY(upload_plan(s, plan, false));
+        TRY(upload(s, s->d_cand_rows, cand_rows));
+        TRY(s->d_f32a.reserve((size_t)rows * 32));
+        ScanParams P = base_scan_params(s, K);
+        P.cand_rows = s->d_cand_rows.p;
+        P.out_f = s->d_f32a.p;
+        TRY((run_scan<EPI_STORE, false>(s, plan, P, items)));
+
+        // reduce in friend order, then top-k per user
+        std::vector<int32_t> ucb(nu + 1, 0), ufb(nu + 1, 0), fr_slot, cand_uid, u_ncand(nu);
+        std::vector<int64_t> u_w0(nu), u_mat0(nu);
+        for (int i = 0; i < nu; ++i) {
+            const CollabUser& u = users[i];
+            ucb[i + 1] = ucb[i] + (int32_t)u.cands.size();
+            ufb[i + 1] = ufb[i] + (int32_t)u.friends.size();
+            fr_slot.insert(fr_slot.end(), u.fr_slot.begin(), u.fr_slot.end());
+            cand_uid.insert(cand_uid.end(), u.cands.begin(), u.cands.end());
+            u_w0[i] = (int64_t)u.w_out0 * 32;
+            u_mat0[i] = (int64_t)u.mat_out0 * 32;
+            u_ncand[i] = (int32_t)u.cands.size();
+        }
+        const int total_c = ucb[nu];
+        if (total_c > 0) {
+            TRY(upload(s, s->d_i32a, ucb));
+            TRY(upload(s, s->d_i32b, ufb));
+            TRY(upload(s, s->d_i32c, fr_slot));
+            TRY(upload(s, s->d_i32d, cand_uid));
+            std::vector<int64_t> offs(u_w0);
+            offs.insert(offs.end(), u_mat0.begin(), u_mat0.end());
+            TRY(upload(s, s->d_i64a, offs));
+            TRY(s->d_keys_a.reserve(total_c));
+            TRY(s->d_keys_b.reserve((size_t)nu * K));
+            CollabReduceParams R;
+            R.fas = s->d_f32a.p; R.user_cand_begin = s->d_i32a.p; R.user_fr_begin = s->d_i32b.p; R.fr_slot = s->d_i32c.p;
+            R.user_w_off = s->d_i64a.p; R.user_mat_off = s->d_i64a.p + nu; R.cand_uid = s->d_i32d.p;
+            R.out_keys = s->d_keys_a.p; R.nu = nu;
+            collab_reduce_kernel<<<dim3(8, nu), 128, 0, s->stream>>>(R);
+            ++s->stat_launches;
+            slice_topk_kernel<<<nu, 256, 0, s->stream>>>(s->d_keys_a.p, s->d_i32a.p, K, s->d_keys_b.p);
+            ++s->stat_launches;
+            CK(cudaGetLastError());
+            std::vector<uint64_t> uk((size_t)nu * K);
+            CK(cudaMemcpyAsync(uk.data(), s->d_keys_b.p, uk.size() * 8, cudaMemcpyDeviceToHost, s->stream));
+            CK(cudaStreamSynchronize(s->stream));
+            for (int i = 0; i < nu; ++i) memcpy(&keys[(size_t)users[i].q * K], &uk[(size_t)i * K], (size_t)K * 8);
+        }
+    }
+    memcpy(h_keys, keys.data(), (size_t)nq * K * 8);
+    return PK_OK;
+}
+
+int recommend_clubs(pk_store* s, int nq, const int32_t* q_uid, int k, uint64_t* h_keys) {
+    const int K = std::max(k, 1);
+    std::vector<CollabUser> users;
+    Plan plan;
+    std::vector<WorkItem> items;
+    std::vector<int32_t> cand_rows;
+    int64_t rows = 0;
+    TRY(collab_prepare(s, nq, q_uid, 0, false, users, plan, items, cand_rows, &rows));
+    s->stat_groups = (int64_t)plan.groups.size();
+    std::vector<uint64_t> keys((size_t)std::max(nq, 1) * K, 0ull);
+    const int nu = (int)users.size();
+    if (nu > 0 && rows > 0) {
+        TRY(upload_plan(s, plan, false));
+        TRY(upload(s, s->d_cand_rows, cand_rows));
+        TRY(s->d_f32a.reserve((size_t)rows * 32));
+        ScanParams P = base_scan_params(s, K);
+        P.cand_rows = s->d_cand_rows.p;
+        P.out_f = s->d_f32a.p;
+        TRY((run_scan<EPI_STORE, false>(s, plan, P, items)));
+
+        // edge stream per user, in the reference's visiting order: 1-hop entries (target = friend), then
+        // 2-hop entries (target = fof); each entry carries the indices of the FAS values it needs.
+        std::vector<ClubEdge> edges;
+        std::vector<int32_t> ueb(nu + 1, 0), ucon(nu + 1, 0), urow(nu);
+        std::vector<uint32_t> con_off;   // per edge: first contribution index (relative to the user)
+        for (int i = 0; i < nu; ++i) {
+            const CollabUser& u = users[i];
+            urow[i] = u.row;
+            std::unordered_map<int32_t, int32_t> cand_idx;
+            cand_idx.reserve(u.cands.size() * 2);
+            for (size_t c = 0; c < u.cands.size(); ++c) cand_idx.emplace(u.cands[c], (int32_t)c);
+            const int64_t ncand = (int64_t)u.cands.size();
+            uint64_t con = 0;
+            auto w_index = [&](int slot) { return ((int64_t)u.w_out0 + slot) * 32; };
+            for (size_t fi = 0; fi < u.friends.size(); ++fi) {          // src/recommender_clubs.cpp:34-43
+                const int sl = u.fr_slot[fi];
+                if (sl < 0) continue;
+                ClubEdge e;
+                e.w_idx = w_index(sl); e.s_idx = -1; e.target_row = u.slot_row[sl];
+                con_off.push_back((uint32_t)con);
+                con += s->h_ncl[e.target_row];
+                edges.push_back(e);
+            }
+            for (size_t fi = 0; fi < u.friends.size(); ++fi) {          // :45-64
+                const int sl = u.fr_slot[fi];
+                const int32_t *b2, *e2;
+                if (!s->adj_of(u.friends[fi], &b2, &e2)) continue;
+                if (sl < 0) continue;
+                for (const int32_t* p = b2; p != e2; ++p) {
+                    if (*p == u.uid) continue;
+                    auto ic = cand_idx.find(*p);
+                    if (ic == cand_idx.end()) continue;                 // no profile
+                    ClubEdge e;
+                    e.w_idx = w_index(sl);
+                    e.s_idx = ((int64_t)u.mat_out0 + (int64_t)(sl >> 5) * ncand + ic->second) * 32 + (sl & 31);
+                    e.target_row = u.cand_row[ic->second];
+                    con_off.push_back((uint32_t)con);
+                    con += s->h_ncl[e.target_row];
+                    edges.push_back(e);
+                }
+            }
+            if (con > 0x7fffffffull) return fail(PK_ERR_UNSUPPORTED, "club contribution stream too large");
+            ueb[i + 1] = (int32_t)edges.size();
+            // table capacity for the user's distinct clubs (power of two >= 2 * contributions)
+            const int64_t capu = (int64_t)1 << log2_table(std::max<uint64_t>(con, 1));
+            if ((int64_t)ucon[i] + capu > 0x7fffffffll) return fail(PK_ERR_UNSUPPORTED, "club batch too large (split the batch)");
+            ucon[i + 1] = ucon[i] + (int32_t)capu;
+        }
+        const int64_t total_slots = ucon[nu];
+        if (!edges.empty()) {
+            TRY(s->d_edges.reserve(edges.size()));
+            CK(cudaMemcpyAsync(s->d_edges.p, edges.data(), edges.size() * sizeof(ClubEdge), cudaMemcpyHostToDevice, s->stream));
+            TRY(upload(s, s->d_u32a, con_off));
+            TRY(upload(s, s->d_i32a, ueb));
+            TRY(upload(s, s->d_i32b, ucon));
+            TRY(upload(s, s->d_i32c, urow));
+            // per contribution slot index: sized by the largest per-user contribution count is not known
+            // per user on the device, so it shares the table-slot budget (contributions <= capacity / 2)
+            TRY(s->d_i32d.reserve((size_t)total_slots));
+            TRY(s->d_keys_a.reserve((size_t)total_slots));          // club id + 1 per slot (as uint64: low 32 bits), then keys
+            TRY(s->d_f64a.reserve((size_t)total_slots));
+            TRY(s->d_keys_b.reserve((size_t)nu * K));
+            CK(cudaMemsetAsync(s->d_keys_a.p, 0, (size_t)total_slots * 8, s->stream));
+            CK(cudaMemsetAsync(s->d_f64a.p, 0, (size_t)total_slots * 8, s->stream));
+            ClubParams C;
+            C.rec = s->d_rec.p; C.rec_off = s->d_rec_off.p; C.fas = s->d_f32a.p; C.edges = s->d_edges.p;
+            C.con_off = s->d_u32a.p; C.user_edge_begin = s->d_i32a.p; C.user_slot_begin = s->d_i32b.p;
+            C.user_row = s->d_i32c.p; C.con_slot = s->d_i32d.p; C.slot_key = s->d_keys_a.p; C.slot_acc = s->d_f64a.p;
+            clubs_scatter_kernel<<<nu, kClubThreads, 0, s->stream>>>(C);
+            ++s->stat_launches;
+            slice_topk_kernel<<<nu, 256, 0, s->stream>>>(s->d_keys_a.p, s->d_i32b.p, K, s->d_keys_b.p);
+            ++s->stat_launches;
+            CK(cudaGetLastError());
+            std::vector<uint64_t> uk((size_t)nu * K);
+            CK(cudaMemcpyAsync(uk.data(), s->d_keys_b.p, uk.size() * 8, cudaMemcpyDeviceToHost, s->stream));
+            CK(cudaStreamSynchronize(s->stream));
+            for (int i = 0; i < nu; ++i) memcpy(&keys[(size_t)users[i].q * K], &uk[(size_t)i * K], (size_t)K * 8);
+        }
+    }
+    memcpy(h_keys, keys.data(), (size_t)nq * K * 8);
+    return PK_OK;
+}
+
+// ---- pairs --------------------------------------------------------------------------------------------
+// groups of 32 distinct `a` rows x the union of their `b` rows; the wanted (a, b) entries are picked
+// from the [cand][32] block on the host.
+template <bool FIELDS>
+int pairs_run(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid, std::vector<float>& out_f,
+              std::vector<float>& out_fields, std::vector<int64_t>& where) {
+    s->stat_scan_ns = 0; s->stat_scan_launches = 0; s->stat_pairs = 0;
+    where.assign((size_t)n, -1);
+    const int nf = 3 + s->T + 2;
+    // process in batches of pairs so that the outputs stay bounded
+    const int64_t kBatch = FIELDS ? 32768 : 1 << 20;
+    out_f.clear();
+    out_fields.clear();
+    std::vector<float> hf;
+    for (int64_t p0 = 0; p0 < n; p0 += kBatch) {
+        const int64_t p1 = std::min(n, p0 + kBatch);
+        Plan plan;
+        std::vector<WorkItem> items;
+        std::vector<int32_t> cand_rows;
+        int64_t rows = 0;
+        // pairs with both profiles, ordered by a
+        std::vector<std::pair<int32_t, int64_t>> order;   // (row a, pair index)
+        for (int64_t i = p0; i < p1; ++i) {
+            const int ra = s->row_of(a_uid[i]);
+            if (ra < 0 || s->row_of(b_uid[i]) < 0) continue;
+            order.emplace_back(ra, i);
+        }
+        std::sort(order.begin(), order.end());
+        size_t i = 0;
+        const int64_t base_out = FIELDS ? (int64_t)out_fields.size() / nf : (int64_t)out_f.size();
+        while (i < order.size()) {
+            GroupDesc g = empty_group();
+            WorkItem it;
+            it.group = (int32_t)plan.groups.size();
+            it.cand_begin = (int32_t)cand_rows.size();
+            it.out_slot = (int32_t)rows;
+            int prev = -1;
+            while (i < order.size()) {
+                if (order[i].first != prev) {
+                    if (g.n_lanes == 32) break;
+                    g.row[g.n_lanes++] = order[i].first;
+                    prev = order[i].first;
+                }
+                const int rb = s->row_of(b_uid[order[i].second]);
+                where[order[i].second] = base_out + ((int64_t)rows + (int64_t)(cand_rows.size() - it.cand_begin)) * 32 + (g.n_lanes - 1);
+                cand_rows.push_back(rb);
+                ++i;
+            }
+            it.cand_end = (int32_t)cand_rows.size();
+            rows += it.cand_end - it.cand_begin;
+            s->stat_pairs += (int64_t)g.n_lanes * (it.cand_end - it.cand_begin);
+            finish_group(s, plan, g, nullptr, 0);
+            items.push_back(it);
+        }
+        if (items.empty()) continue;
+        TRY(upload_plan(s, plan, false));
+        TRY(upload(s, s->d_cand_rows, cand_rows));
+        TRY(s->d_f32a.reserve((size_t)rows * 32));
+        ScanParams P = base_scan_params(s, 1);
+        P.cand_rows = s->d_cand_rows.p;
+        P.out_f = s->d_f32a.p;
+        if (FIELDS) {
+            TRY(s->d_fields.reserve((size_t)rows * 32 * nf));
+            P.out_fields = s->d_fields.p;
+        }
+        TRY((run_scan<EPI_STORE, FIELDS>(s, plan, P, items)));
+        if (FIELDS) {
+            const size_t o = out_fields.size();
+            out_fields.resize(o + (size_t)rows * 32 * nf);
+            CK(cudaMemcpyAsync(out_fields.data() + o, s->d_fields.p, (size_t)rows * 32 * nf * 4, cudaMemcpyDeviceToHost, s->stream));
+        } else {
+            const size_t o = out_f.size();
+            out_f.resize(o + (size_t)rows * 32);
+            CK(cudaMemcpyAsync(out_f.data() + o, s->d_f32a.p, (size_t)rows * 32 * 4, cudaMemcpyDeviceToHost, s->stream));
+        }
+        CK(cudaStreamSynchronize(s->stream));
+    }
+    return PK_OK;
+}
+
+}  // namespace
+
+// =======================================================================================================
+// C ABI
+// =======================================================================================================
+extern "C" {
+
+const char* pk_last_error(void) { return g_err.c_str(); }
+int pk_abi_version(void) { return PK_ABI_VERSION; }
+
+int pk_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int pk_store_create(int device, pk_store** out) {
+    if (!out) return fail(PK_ERR_ARG, "null out pointer");
+    *out = nullptr;
+    int ndev = pk_device_count();
+    if (ndev <= 0) return fail(PK_ERR_CUDA, "no CUDA device: libpokec_b200 has no CPU path");
+    if (device < 0 || device >= ndev) return fail(PK_ERR_ARG, "device %d out of range (%d visible)", device, ndev);
+    CK(cudaSetDevice(device));
+    pk_store* s = new pk_store();
+    s->device = device;
+    cudaError_t e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreate(&s->ev0);
+    if (e == cudaSuccess) e = cudaEventCreate(&s->ev1);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&s->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+    if (e != cudaSuccess) { delete s; return fail(PK_ERR_CUDA, "store init: %s", cudaGetErrorString(e)); }
+    *out = s;
+    return PK_OK;
+}
+
+void pk_store_destroy(pk_store* s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
+    cudaStream_t st = s->stream;
+    delete s;
+    if (st) cudaStreamDestroy(st);
+}
+
+int pk_store_load_world(pk_store* s, const pk_world* w) {
+    if (!s || !w) return fail(PK_ERR_ARG, "null argument");
+    const int n = w->n_users, T = w->n_text_cols, m = w->n_adj_rows;
+    if (n < 0 || T < 0 || m < 0) return fail(PK_ERR_ARG, "negative size");
+    if (T > kMaxT) return fail(PK_ERR_UNSUPPORTED, "%d text columns; at most %d are supported", T, kMaxT);
+    if (n > 0 && (!w->uid || !w->pub || !w->comp || !w->gender || !w->age || !w->region || !w->clubs_ptr || !w->friends_ptr ||
+                  !w->tok_ptr))
+        return fail(PK_ERR_ARG, "null profile array");
+    if (m > 0 && (!w->adj_uid || !w->adj_ptr)) return fail(PK_ERR_ARG, "null adjacency array");
+    CK(cudaSetDevice(s->device));
+    const int64_t ncl = n ? w->clubs_ptr[n] : 0, nfr = n ? w->friends_ptr[n] : 0, nnz = n ? w->tok_ptr[(int64_t)n * T] : 0;
+    // cells sorted by token id (the reference's cells are hash maps: order-free); ids must fit 26 bits
+    std::vector<int32_t> tid, ttf;
+    const int32_t *tok_id = w->tok_id, *tok_tf = w->tok_tf;
+    bool sorted = true;
+    for (int64_t c = 0; c < (int64_t)n * T; ++c) {
+        const int64_t b = w->tok_ptr[c], e = w->tok_ptr[c + 1];
+        if (e < b) return fail(PK_ERR_ARG, "tok_ptr not monotone");
+        for (int64_t j = b; j < e; ++j) {
+            if ((uint32_t)tok_id[j] >= (1u << kTokBits)) return fail(PK_ERR_UNSUPPORTED, "token id %d outside [0, 2^26)", tok_id[j]);
+            if (j > b && tok_id[j] <= tok_id[j - 1]) sorted = false;
+        }
+    }
+    if (!sorted) {
+        tid.assign(tok_id, tok_id + nnz);
+        ttf.assign(tok_tf, tok_tf + nnz);
+        std::vector<std::pair<int32_t, int32_t>> tmp;
+        for (int64_t c = 0; c < (int64_t)n * T; ++c) {
+            const int64_t b = w->tok_ptr[c], e = w->tok_ptr[c + 1];
+            if (e - b < 2 || std::is_sorted(tid.begin() + b, tid.begin() + e)) continue;
+            tmp.clear();
+            for (int64_t j = b; j < e; ++j) tmp.emplace_back(tid[j], ttf[j]);
+            std::sort(tmp.begin(), tmp.end());
+            for (int64_t j = b; j < e; ++j) { tid[j] = tmp[j - b].first; ttf[j] = tmp[j - b].second; }
+        }
+        tok_id = tid.data(); tok_tf = ttf.data();
+    }
+    s->n = n; s->T = T; s->nnz = nnz;
+    s->uid.assign(w->uid, w->uid + n);
+    s->uid_sorted.resize(n);
+    for (int i = 0; i < n; ++i) s->uid_sorted[i] = {w->uid[i], i};
+    std::sort(s->uid_sorted.begin(), s->uid_sorted.end());
+    for (int i = 1; i < n; ++i)
+        if (s->uid_sorted[i].first == s->uid_sorted[i - 1].first) return fail(PK_ERR_ARG, "duplicate profile uid %d", s->uid_sorted[i].first);
+    s->h_ncl.resize(n); s->h_nfr.resize(n); s->h_ntok.assign(n, 0);
+    s->max_comp = 0; s->max_age = 0;
+    for (int i = 0; i < n; ++i) {
+        s->h_ncl[i] = (uint32_t)(w->clubs_ptr[i + 1] - w->clubs_ptr[i]);
+        s->h_nfr[i] = (uint32_t)(w->friends_ptr[i + 1] - w->friends_ptr[i]);
+        s->max_comp = std::max(s->max_comp, w->comp[i]);
+        s->max_age = std::max(s->max_age, w->age[i]);
+    }
+    s->adj_uid.assign(w->adj_uid, w->adj_uid + m);
+    s->adj_ptr.assign(w->adj_ptr, w->adj_ptr + (m ? m + 1 : 0));
+    if (m == 0) s->adj_ptr.assign(1, 0);
+    s->adj.assign(w->adj, w->adj + (m ? w->adj_ptr[m] : 0));
+    s->adj_row.clear();
+    s->adj_row.reserve((size_t)m * 2);
+    for (int r = 0; r < m; ++r) s->adj_row[w->adj_uid[r]] = r;
+    s->adj_override.clear();
+
+    TRY(upload(s, s->d_uid, w->uid, n)); TRY(upload(s, s->d_pub, w->pub, n)); TRY(upload(s, s->d_comp, w->comp, n));
+    TRY(upload(s, s->d_gender, w->gender, n)); TRY(upload(s, s->d_age, w->age, n)); TRY(upload(s, s->d_region, w->region, (size_t)3 * n));
+    std::vector<int64_t> one(1, 0);
+    TRY(upload(s, s->d_clubs_ptr, n ? w->clubs_ptr : one.data(), (size_t)n + 1));
+    TRY(upload(s, s->d_friends_ptr, n ? w->friends_ptr : one.data(), (size_t)n + 1));
+    TRY(upload(s, s->d_tok_ptr, n ? w->tok_ptr : one.data(), (size_t)n * T + 1));
+    TRY(upload(s, s->d_clubs, w->clubs, (size_t)ncl)); TRY(upload(s, s->d_friends, w->friends, (size_t)nfr));
+    TRY(upload(s, s->d_tok_id, tok_id, (size_t)nnz)); TRY(upload(s, s->d_tok_tf, tok_tf, (size_t)nnz));
+    CK(cudaStreamSynchronize(s->stream));
+
+    s->col_state.assign(T, 0);
+    s->custom_tok.assign(T, {});
+    s->custom_idf.assign(T, {});
+    s->idf_dirty = true; s->store_dirty = true;
+    const int nf = kNumFixed + T;
+    s->nmean.assign(nf, 0.f); s->nsd.assign(nf, 0.f); s->nhas.assign(nf, 0);
+    if (w->norm_mean && w->norm_sd && w->norm_has)
+        for (int f = 0; f < nf; ++f) { s->nmean[f] = w->norm_mean[f]; s->nsd[f] = w->norm_sd[f]; s->nhas[f] = w->norm_has[f]; }
+    s->norm_dirty = true;
+    s->shard_begin = 0; s->shard_end = n;
+    s->loaded = true;
+    return PK_OK;
+}
+
+int pk_store_set_shard(pk_store* s, int64_t row_begin, int64_t row_end) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
+    if (row_begin < 0 || row_end < row_begin || row_end > s->n) return fail(PK_ERR_ARG, "bad shard [%lld,%lld)", (long long)row_begin, (long long)row_end);
+    s->shard_begin = row_begin; s->shard_end = row_end;
+    return PK_OK;
+}
+
+int pk_set_normalizers(pk_store* s, const float* mean, const float* sd, const uint8_t* has, int n_fields) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
+    if (n_fields != kNumFixed + s->T) return fail(PK_ERR_ARG, "n_fields = %d, expected %d", n_fields, kNumFixed + s->T);
+    if (!mean || !sd) return fail(PK_ERR_ARG, "null normalizer array");
+    for (int f = 0; f < n_fields; ++f) { s->nmean[f] = mean[f]; s->nsd[f] = sd[f]; s->nhas[f] = has ? has[f] : 1; }
+    s->norm_dirty = true;
+    return PK_OK;
+}
+
+int pk_compute_idf(pk_store* s, int double_log) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
+    for (int t = 0; t < s->T; ++t) { s->col_state[t] = 1; s->custom_tok[t].clear(); s->custom_idf[t].clear(); }
+    s->double_log = double_log ? 1 : 0;
+    s->idf_dirty = true;
+    CK(cudaSetDevice(s->device));
+    return rebuild_idf(s);
+}
+
+int pk_set_idf(pk_store* s, int col, const int32_t* token, const float* idf, int64_t n) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
+    if (col < 0 || col >= s->T) return fail(PK_ERR_ARG, "column %d out of range", col);
+    if (n > 0 && (!token || !idf)) return fail(PK_ERR_ARG, "null idf arrays");
+    if (n < 0) {
+        s->col_state[col] = 0; s->custom_tok[col].clear(); s->custom_idf[col].clear();
+    } else {
+        for (int64_t i = 0; i < n; ++i)
+            if ((uint32_t)token[i] >= (1u << kTokBits)) return fail(PK_ERR_UNSUPPORTED, "token id %d outside [0, 2^26)", token[i]);
+        s->col_state[col] = 2;
+        s->custom_tok[col].assign(token, token + n);
+        s->custom_idf[col].assign(idf, idf + n);
+    }
+    s->idf_dirty = true;
+    return PK_OK;
+}
+
+int pk_idf_size(pk_store* s, int col, int64_t* n) {
+    if (!s || !n) return fail(PK_ERR_ARG, "null argument");
+    if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
+    if (col < 0 || col >= s->T) return fail(PK_ERR_ARG, "column %d out of range", col);
+    if (s->col_state[col] == 0) { *n = -1; return PK_OK; }
+    TRY(pk_get_idf(s, col, nullptr, nullptr, nullptr, 0));
+    *n = s->last_idf_n;
+    return PK_OK;
+}
+
+int pk_get_idf(pk_store* s, int col, int32_t* token, float* idf, int32_t* df, int64_t cap) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
+    if (col < 0 || col >= s->T) return fail(PK_ERR_ARG, "column %d out of range", col);
+    CK(cudaSetDevice(s->device));
+    TRY(rebuild_idf(s));
+    s->last_idf_n = 0;
+    if (s->col_state[col] == 0) return PK_OK;
+    // count, then export
+    DevBuf<unsigned long long> d_cnt;
+    TRY(d_cnt.reserve(1));
+    const size_t tcap = (size_t)1 << s->idf_log_cap;
+    for (int pass = 0; pass < 2; ++pass) {
+        const int64_t want = pass == 0 ? 0 : s->last_idf_n;
+        TRY(s->d_i32a.reserve(std::max<int64_t>(want, 1)));
+        TRY(s->d_i32b.reserve(std::max<int64_t>(want, 1)));
+        TRY(s->d_f32a.reserve(std::max<int64_t>(want, 1)));
+        CK(cudaMemsetAsync(d_cnt.p, 0, 8, s->stream));
+        idf_export_kernel<<<(unsigned)((tcap + 255) / 256), 256, 0, s->stream>>>(idf_table(s), col, s->d_i32a.p, s->d_f32a.p, s->d_i32b.p,
+                                                                               d_cnt.p, want);
+        ++s->stat_launches;
+        unsigned long long cnt = 0;
+        CK(cudaMemcpyAsync(&cnt, d_cnt.p, 8, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+        s->last_idf_n = (int64_t)cnt;
+        if (pass == 0 && (cnt == 0 || !token)) return PK_OK;
+    }
+    const int64_t m = s->last_idf_n;
+    std::vector<int32_t> ht(m), hd(m);
+    std::vector<float> hv(m);
+    CK(cudaMemcpyAsync(ht.data(), s->d_i32a.p, m * 4, cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaMemcpyAsync(hd.data(), s->d_i32b.p, m * 4, cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaMemcpyAsync(hv.data(), s->d_f32a.p, m * 4, cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    std::vector<int64_t> ord(m);
+    for (int64_t i = 0; i < m; ++i) ord[i] = i;
+    std::sort(ord.begin(), ord.end(), [&](int64_t a, int64_t b) { return ht[a] < ht[b]; });
+    for (int64_t i = 0; i < m && i < cap; ++i) {
+        token[i] = ht[ord[i]];
+        if (idf) idf[i] = hv[ord[i]];
+        if (df) df[i] = hd[ord[i]];
+    }
+    return PK_OK;
+}
+
+int pk_set_adj_row(pk_store* s, int32_t uid, const int32_t* nb, int64_t n) {
+    if (!s || n < 0 || (n > 0 && !nb)) return fail(PK_ERR_ARG, "bad argument");
+    if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
+    s->adj_override[uid].assign(nb, nb + n);
+    return PK_OK;
+}
+
+int pk_pair_similarity(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid, float* out) {
+    TRY(ensure_ready(s));
+    if (n < 0 || (n > 0 && (!a_uid || !b_uid || !out))) return fail(PK_ERR_ARG, "bad argument");
+    std::vector<float> f, fields;
+    std::vector<int64_t> where;
+    TRY(pairs_run<false>(s, n, a_uid, b_uid, f, fields, where));
+    for (int64_t i = 0; i < n; ++i) out[i] = where[i] < 0 ? -1.0f : f[where[i]];
+    return PK_OK;
+}
+
+int pk_pair_fields(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid, float* out) {
+    TRY(ensure_ready(s));
+    if (n < 0 || (n > 0 && (!a_uid || !b_uid || !out))) return fail(PK_ERR_ARG, "bad argument");
+    std::vector<float> f, fields;
+    std::vector<int64_t> where;
+    TRY(pairs_run<true>(s, n, a_uid, b_uid, f, fields, where));
+    const int nfo = 3 + s->T, nf = nfo + 2;
+    for (int64_t i = 0; i < n; ++i)
+        for (int j = 0; j < nfo; ++j) out[i * nfo + j] = where[i] < 0 ? -1.0f : fields[(size_t)where[i] * nf + j];
+    return PK_OK;
+}
+
+int pk_pair_overlap(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid, int which, int32_t* out) {
+    TRY(ensure_ready(s));
+    if (n < 0 || which < 0 || which > 1 || (n > 0 && (!a_uid || !b_uid || !out))) return fail(PK_ERR_ARG, "bad argument");
+    std::vector<float> f, fields;
+    std::vector<int64_t> where;
+    TRY(pairs_run<true>(s, n, a_uid, b_uid, f, fields, where));
+    const int nf = 3 + s->T + 2;
+    for (int64_t i = 0; i < n; ++i) {
+        if (where[i] < 0) { out[i] = -1; continue; }
+        float v = fields[(size_t)where[i] * nf + 3 + s->T + which];
+        int32_t iv;
+        memcpy(&iv, &v, 4);
+        // the slot keeps its -1.0f initialiser when the field is absent on either side: overlap 0
+        out[i] = (v == -1.0f) ? 0 : iv;
+    }
+    return PK_OK;
+}
+
+int pk_fullscan_topk(pk_store* s, int nq, const int32_t* q_uid, int k, int exclude_mode, int32_t* out_id, float* out_score,
+                     int32_t* out_cnt) {
+    TRY(ensure_ready(s));
+    TRY(check_topk_args(s, nq, q_uid, k));
+    if (nq > 0 && (!out_cnt || (k > 0 && (!out_id || !out_score)))) return fail(PK_ERR_ARG, "null output");
+    if (exclude_mode < PK_EXCLUDE_NONE || exclude_mode > PK_EXCLUDE_SELF_AND_ADJ) return fail(PK_ERR_ARG, "bad exclude_mode");
+    if (nq == 0) return PK_OK;
+    if (k == 0) { for (int q = 0; q < nq; ++q) out_cnt[q] = 0; return PK_OK; }
+    TRY(fullscan_device(s, nq, q_uid, k, exclude_mode));
+    std::vector<uint64_t> keys((size_t)nq * k);
+    CK(cudaMemcpyAsync(keys.data(), s->d_keys_b.p, keys.size() * 8, cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    decode_keys(keys.data(), nq, k, out_id, out_score, out_cnt);
+    return PK_OK;
+}
+
+int pk_fullscan_local_keys(pk_store* s, int nq, const int32_t* q_uid, int k, int exclude_mode, uint64_t* d_keys) {
+    TRY(ensure_ready(s));
+    TRY(check_topk_args(s, nq, q_uid, k));
+    if (nq > 0 && k > 0 && !d_keys) return fail(PK_ERR_ARG, "null d_keys");
+    if (nq == 0 || k == 0) return PK_OK;
+    TRY(fullscan_device(s, nq, q_uid, k, exclude_mode));
+    CK(cudaMemcpyAsync(d_keys, s->d_keys_b.p, (size_t)nq * k * 8, cudaMemcpyDeviceToDevice, s->stream));
+    return PK_OK;
+}
+
+int pk_merge_keys(pk_store* s, const uint64_t* d_keys, int n_lists, int nq, int k, int32_t* out_id, float* out_score,
+                  int32_t* out_cnt) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    if (n_lists < 1 || nq < 0 || k < 0 || k > kMaxK) return fail(PK_ERR_ARG, "bad n_lists/nq/k");
+    if (nq == 0) return PK_OK;
+    if (k == 0) { for (int q = 0; q < nq; ++q) out_cnt[q] = 0; return PK_OK; }
+    if (!d_keys || !out_id || !out_score || !out_cnt) return fail(PK_ERR_ARG, "null argument");
+    if (n_lists > 128 * 8) return fail(PK_ERR_UNSUPPORTED, "at most 1024 lists");
+    CK(cudaSetDevice(s->device));
+    TRY(s->d_keys_c.reserve((size_t)nq * k));
+    MergeParams M;
+    memset(&M, 0, sizeof(M));
+    M.keys = d_keys; M.n_lists = n_lists; M.nq = nq; M.K = k; M.stride_k = k; M.out_keys = s->d_keys_c.p;
+    merge_topk_kernel<<<nq, 128, 0, s->stream>>>(M);
+    ++s->stat_launches;
+    CK(cudaGetLastError());
+    std::vector<uint64_t> keys((size_t)nq * k);
+    CK(cudaMemcpyAsync(keys.data(), s->d_keys_c.p, keys.size() * 8, cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    decode_keys(keys.data(), nq, k, out_id, out_score, out_cnt);
+    return PK_OK;
+}
+
+int pk_recommend(pk_store* s, int mode, int nq, const int32_t* q_uid, int k, int limit, int32_t* out_id, float* out_score,
+                 int32_t* out_cnt) {
+    TRY(ensure_ready(s));
+    TRY(check_topk_args(s, nq, q_uid, k));
+    if (nq > 0 && (!out_cnt || (k > 0 && (!out_id || !out_score)))) return fail(PK_ERR_ARG, "null output");
+    if (mode != PK_MODE_GRAPH && mode != PK_MODE_COLLAB && mode != PK_MODE_CLUBS) return fail(PK_ERR_ARG, "bad mode %d", mode);
+    if (nq == 0) return PK_OK;
+    if (k == 0) { for (int q = 0; q < nq; ++q) out_cnt[q] = 0; return PK_OK; }
+    s->stat_scan_ns = 0; s->stat_scan_launches = 0; s->stat_pairs = 0; s->stat_groups = 0;
+    std::vector<uint64_t> keys((size_t)nq * k, 0ull);
+    if (mode == PK_MODE_GRAPH) TRY(recommend_graph(s, nq, q_uid, k, limit, keys.data()));
+    else if (mode == PK_MODE_COLLAB) TRY(recommend_collab(s, nq, q_uid, k, limit, keys.data()));
+    else TRY(recommend_clubs(s, nq, q_uid, k, keys.data()));
+    decode_keys(keys.data(), nq, k, out_id, out_score, out_cnt);
+    return PK_OK;
+}
+
+int pk_candidates(pk_store* s, int mode, int32_t uid, int limit, int32_t* out, int64_t cap, int64_t* n) {
+    if (!s || !n || (cap > 0 && !out)) return fail(PK_ERR_ARG, "null argument");
+    if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
+    std::vector<int32_t> c;
+    if (mode == PK_MODE_GRAPH) gather_candidates(s, uid, limit, c);
+    else if (mode == PK_MODE_COLLAB) {
+        const int32_t *b = nullptr, *e = nullptr;
+        if (s->adj_of(uid, &b, &e)) collab_candidates(s, uid, b, e, limit, true, c);
+    } else return fail(PK_ERR_ARG, "bad mode %d", mode);
+    *n = (int64_t)c.size();
+    for (int64_t i = 0; i < (int64_t)c.size() && i < cap; ++i) out[i] = c[i];
+    return PK_OK;
+}
+
+int pk_sync(pk_store* s) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    CK(cudaSetDevice(s->device));
+    CK(cudaStreamSynchronize(s->stream));
+    return PK_OK;
+}
+
+void* pk_stream(pk_store* s) { return s ? (void*)s->stream : nullptr; }
+
+int64_t pk_stat(pk_store* s, int which) {
+    if (!s) return -1;
+    switch (which) {
+        case PK_STAT_KERNEL_LAUNCHES: return s->stat_launches;
+        case PK_STAT_PAIRS_SCORED: return s->stat_pairs;
+        case PK_STAT_STORE_BYTES: return (int64_t)s->store_u4 * 16;
+        case PK_STAT_SCAN_KERNEL_NS: return s->stat_scan_ns;
+        case PK_STAT_SCAN_LAUNCHES: return s->stat_scan_launches;
+        case PK_STAT_GROUPS: return s->stat_groups;
+        case PK_STAT_SHARD_RECORD_BYTES:
+            if (s->h_rec_off.size() < (size_t)s->n + 1) return 0;
+            return (int64_t)(s->h_rec_off[s->shard_end] - s->h_rec_off[s->shard_begin]) * 16;
+        default: return -1;
+    }
+}
+
+}  // extern "C"

@@ -1,0 +1,633 @@
+// pk_scan.cuh -- the scoring kernels.
+//
+// fas_scan_kernel is the device form of Recommender::profile_similarity
+// (reference src/recommender_similarity.cpp:10-124) applied to (query group x candidate) tiles,
+// with the top-k of src/recommender_graph.cpp:97-101 fused in.
+//
+// Mapping.  A group is <= 32 query users; lane l of every warp of the CTA owns query l.  A warp
+// takes one candidate record at a time: the record's clubs / friends / tokens are read with
+// coalesced loads (lane i owns element i) and every element is looked up ONCE in the group's
+// inverted hash tables (element -> 32-bit mask of the queries that contain it), which live in
+// shared memory.  Hits are redistributed with warp shuffles so that lane l accumulates the overlap
+// count / tf-idf dot product of ITS query, then each lane finishes its own FAS in fp64 exactly as
+// the reference does (float rounding of every per-field similarity, z-score, logistic, mean,
+// fill factor, harmonic mean, final float).  Control flow is warp-uniform except for predication.
+#pragma once
+#include "pk_build.cuh"
+#include "pk_layout.h"
+
+namespace pk {
+
+constexpr int kScanThreads = 512;
+constexpr int kScanWarps = kScanThreads / 32;
+constexpr int kPrepThreads = 256;
+constexpr unsigned kFull = 0xffffffffu;
+
+enum { EPI_TOPK = 0, EPI_STORE = 1 };
+
+// ------------------------------------------------------------------------------------------------
+// group tables: built in the global arena by group_prep_kernel
+// ------------------------------------------------------------------------------------------------
+
+// set table slot: {key, mask}; text table slot: {key, mask, base, 0}.  A slot is empty iff mask == 0.
+__device__ __forceinline__ void table_insert(unsigned long long* slot0, uint32_t stride_u64, int log_size, uint32_t key,
+                                             uint32_t bit) {
+    const uint32_t msk = (1u << log_size) - 1u;
+    uint32_t slot = hash_u32(key, log_size);
+    const unsigned long long nw = (unsigned long long)key | ((unsigned long long)bit << 32);
+    for (;;) {
+        unsigned long long* p = slot0 + (size_t)slot * stride_u64;
+        unsigned long long cur = *reinterpret_cast<volatile unsigned long long*>(p);
+        if (cur == 0ull) {
+            unsigned long long old = atomicCAS(p, 0ull, nw);
+            if (old == 0ull) return;
+            cur = old;
+        }
+        if ((uint32_t)cur == key) {
+            atomicOr(reinterpret_cast<unsigned int*>(p) + 1, bit);
+            return;
+        }
+        slot = (slot + 1) & msk;
+    }
+}
+
+struct PrepParams {
+    const uint4* rec;
+    const uint64_t* rec_off;
+    const GroupDesc* groups;
+    uint8_t* arena;               // zero-filled by the host before the launch
+    const int32_t* excl_ids;      // per-batch exclusion ids (adjacency rows of the queries), may be null
+};
+
+// one CTA per group
+__global__ void __launch_bounds__(kPrepThreads) group_prep_kernel(const PrepParams P) {
+    const GroupDesc& gd = P.groups[blockIdx.x];
+    uint8_t* base = P.arena + gd.arena_off;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = kPrepThreads / 32;
+    double* nq = reinterpret_cast<double*>(base + gd.off_nq);
+    unsigned long long* t_clubs = reinterpret_cast<unsigned long long*>(base + gd.off_clubs);
+    unsigned long long* t_friends = reinterpret_cast<unsigned long long*>(base + gd.off_friends);
+    unsigned long long* t_adj = reinterpret_cast<unsigned long long*>(base + gd.off_adj);
+    unsigned long long* t_text = reinterpret_cast<unsigned long long*>(base + gd.off_text);
+    double* vals = reinterpret_cast<double*>(base + gd.off_vals);
+
+    // phase 1: insert every element of every query of the group
+    for (int L = warp; L < gd.n_lanes; L += nwarps) {
+        const int row = gd.row[L];
+        if (row < 0) continue;
+        const uint32_t* r = reinterpret_cast<const uint32_t*>(P.rec + P.rec_off[row]);
+        const uint32_t ncl = r[8], nfr = r[9], ncells = r[10], ntok = r[11];
+        const uint32_t o_clubs = kHdrWords, o_friends = o_clubs + pad4(ncl), o_cells = o_friends + pad4(nfr),
+                       o_keys = o_cells + 4 * ncells;
+        const uint32_t bit = 1u << L;
+        for (uint32_t i = lane; i < ncl; i += 32) table_insert(t_clubs, 1, gd.log_sc, r[o_clubs + i], bit);
+        for (uint32_t i = lane; i < nfr; i += 32) table_insert(t_friends, 1, gd.log_sf, r[o_friends + i], bit);
+        if (P.excl_ids)
+            for (int i = gd.adj_begin[L] + lane; i < gd.adj_begin[L + 1]; i += 32)
+                table_insert(t_adj, 1, gd.log_sa, (uint32_t)P.excl_ids[i], bit);
+        for (uint32_t i = lane; i < ntok; i += 32) table_insert(t_text, 2, gd.log_st, r[o_keys + i], bit);
+        for (uint32_t k = lane; k < ncells; k += 32) {
+            const uint32_t t = r[o_cells + 4 * k];
+            nq[t * 32 + L] = *reinterpret_cast<const double*>(r + o_cells + 4 * k + 2);
+        }
+    }
+    __syncthreads();
+
+    // phase 2: base[slot] = exclusive prefix sum of popc(mask) over the text table
+    __shared__ uint32_t warp_sums[kPrepThreads / 32];
+    __shared__ uint32_t running;
+    if (tid == 0) running = 0;
+    __syncthreads();
+    const uint32_t st = 1u << gd.log_st;
+    uint32_t* t_text32 = reinterpret_cast<uint32_t*>(t_text);
+    for (uint32_t c0 = 0; c0 < st; c0 += kPrepThreads) {
+        const uint32_t s = c0 + tid;
+        const uint32_t cnt = (s < st) ? __popc(t_text32[4 * s + 1]) : 0u;
+        uint32_t inc = cnt;
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t v = __shfl_up_sync(kFull, inc, o);
+            if (lane >= o) inc += v;
+        }
+        if (lane == 31) warp_sums[warp] = inc;
+        __syncthreads();
+        uint32_t woff = 0;
+        for (int w2 = 0; w2 < warp; ++w2) woff += warp_sums[w2];
+        const uint32_t run = running;
+        if (s < st) t_text32[4 * s + 2] = run + woff + inc - cnt;
+        __syncthreads();
+        if (tid == kPrepThreads - 1) running = run + woff + inc;
+        __syncthreads();
+    }
+
+    // phase 3: per-(token, query) weights, compacted by the rank of the query inside the mask
+    const uint32_t msk = st - 1u;
+    for (int L = warp; L < gd.n_lanes; L += nwarps) {
+        const int row = gd.row[L];
+        if (row < 0) continue;
+        const uint32_t* r = reinterpret_cast<const uint32_t*>(P.rec + P.rec_off[row]);
+        const uint32_t ncl = r[8], nfr = r[9], ncells = r[10], ntok = r[11];
+        const uint32_t o_keys = kHdrWords + pad4(ncl) + pad4(nfr) + 4 * ncells, o_w = o_keys + pad4(ntok);
+        const double* w = reinterpret_cast<const double*>(r + o_w);
+        for (uint32_t i = lane; i < ntok; i += 32) {
+            const uint32_t key = r[o_keys + i];
+            uint32_t slot = hash_u32(key, gd.log_st);
+            for (;;) {
+                const uint32_t k2 = t_text32[4 * slot], m2 = t_text32[4 * slot + 1];
+                if (m2 != 0 && k2 == key) {
+                    vals[t_text32[4 * slot + 2] + __popc(m2 & ((1u << L) - 1u))] = w[i];
+                    break;
+                }
+                if (m2 == 0) break;   // cannot happen: the key was inserted in phase 1
+                slot = (slot + 1) & msk;
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// scoring
+// ------------------------------------------------------------------------------------------------
+
+struct ScanParams {
+    const uint4* rec;
+    const uint64_t* rec_off;
+    const GroupDesc* groups;
+    const WorkItem* items;
+    const uint8_t* arena;
+    const NormTables* norm;
+    const double* tab_comp;      // [dim_comp][dim_comp] sigmoid(z(min/max)), index [cand][query]
+    const double* tab_age;
+    const int32_t* cand_rows;    // explicit candidate rows, or null = the row index itself
+    int T;
+    int K, Kp;                   // top-k and its padding to a multiple of 32
+    int exclude_mode;
+    uint32_t smem_arena_bytes;   // shared-memory bytes reserved for the group tables
+    uint64_t* out_keys;          // EPI_TOPK: [item.out_slot][32][Kp]
+    float* out_f;                // EPI_STORE: [(item.out_slot + i)][32]
+    float* out_fields;           // FIELDS: [(item.out_slot + i)][32][nf]
+    int nf;                      // 3 + T + 2
+};
+
+// src/recommender_similarity.cpp:18-26
+__device__ __forceinline__ double pk_sigmoid(double x) {
+    const double e = exp(-fabs(x));
+    const double num = (x >= 0.0) ? 1.0 : e;
+    return num / (1.0 + e);
+}
+
+// src/recommender_similarity.cpp:28-36 / :105-111
+__device__ __forceinline__ double pk_z(const NormTables* N, int field, double s) {
+    if (N->use_norm[field]) return (s - N->mean[field]) / N->sd[field];
+    return 6.0 * (s - 0.5);
+}
+
+__device__ __forceinline__ uint32_t probe_set(const uint2* tab, int log_size, uint32_t key) {
+    const uint32_t msk = (1u << log_size) - 1u;
+    uint32_t slot = hash_u32(key, log_size);
+    for (;;) {
+        const uint2 e = tab[slot];
+        if (e.y == 0u) return 0u;
+        if (e.x == key) return e.y;
+        slot = (slot + 1) & msk;
+    }
+}
+
+__device__ __forceinline__ uint32_t probe_text(const uint4* tab, int log_size, uint32_t key, uint32_t* base) {
+    const uint32_t msk = (1u << log_size) - 1u;
+    uint32_t slot = hash_u32(key, log_size);
+    for (;;) {
+        const uint4 e = tab[slot];
+        if (e.y == 0u) return 0u;
+        if (e.x == key) { *base = e.z; return e.y; }
+        slot = (slot + 1) & msk;
+    }
+}
+
+// Warp-cooperative insertion of `key` into query `ql`'s descending top-k list (all lanes call it
+// with the same arguments).  Rare after the first few hundred candidates, hence the simple lock.
+__device__ __forceinline__ void topk_insert(uint64_t* list, int K, int Kp, uint64_t key, int* lock,
+                                            volatile uint64_t* tau, int lane) {
+    if (lane == 0) {
+        while (atomicCAS(lock, 0, 1) != 0) __nanosleep(64);
+    }
+    __syncwarp();
+    __threadfence_block();
+    volatile uint64_t* vl = list;
+    if (key > vl[K - 1]) {
+        int pos = 0;
+        for (int s0 = 0; s0 < Kp; s0 += 32) {
+            const int i = s0 + lane;
+            const bool gt = (i < K) && (vl[i] > key);
+            pos += __popc(__ballot_sync(kFull, gt));
+        }
+        for (int s0 = Kp - 32; s0 >= 0 && s0 + 32 > pos; s0 -= 32) {
+            const int i = s0 + lane;
+            const bool mv = (i > pos) && (i < K);
+            uint64_t v = 0;
+            if (mv) v = vl[i - 1];
+            __syncwarp();
+            if (mv) vl[i] = v;
+            __syncwarp();
+        }
+        if (lane == 0) vl[pos] = key;
+        __syncwarp();
+        if (lane == 0) *tau = vl[K - 1];
+    }
+    __threadfence_block();
+    __syncwarp();
+    if (lane == 0) atomicExch(lock, 0);
+}
+
+template <bool SM, int EPI, bool FIELDS>
+__global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanParams P) {
+    extern __shared__ uint4 smem_u4[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(smem_u4);
+    const int tid = threadIdx.x, lane = tid & 31;
+    const WorkItem it = P.items[blockIdx.x];
+    const GroupDesc* gd = P.groups + it.group;
+
+    // ---- shared memory carve-up ------------------------------------------------------------
+    const uint32_t arena_sm = SM ? P.smem_arena_bytes : 0u;
+    NormTables* N = reinterpret_cast<NormTables*>(smem + arena_sm);
+    constexpr uint32_t kNormBytes = (sizeof(NormTables) + 15u) & ~15u;
+    uint64_t* lists = reinterpret_cast<uint64_t*>(smem + arena_sm + kNormBytes);       // [32][Kp]
+    const int Kp = (EPI == EPI_TOPK) ? P.Kp : 0;
+    uint64_t* tau = lists + 32 * Kp;                                                    // [32]
+    int* locks = reinterpret_cast<int*>(tau + 32);                                      // [32]
+    int* next = locks + 32;
+
+    {   // stage the group's tables and the normalizer constants
+        if (SM) {
+            const uint4* src = reinterpret_cast<const uint4*>(P.arena + gd->arena_off);
+            const uint32_t n16 = gd->arena_bytes >> 4;
+            for (uint32_t i = tid; i < n16; i += kScanThreads) smem_u4[i] = __ldg(src + i);
+        }
+        const uint4* nsrc = reinterpret_cast<const uint4*>(P.norm);
+        uint4* ndst = reinterpret_cast<uint4*>(N);
+        for (uint32_t i = tid; i < kNormBytes / 16; i += kScanThreads) ndst[i] = __ldg(nsrc + i);
+        for (int i = tid; i < 32 * Kp; i += kScanThreads) lists[i] = 0ull;
+        if (tid < 32) { tau[tid] = 0ull; locks[tid] = 0; }
+        if (tid == 0) *next = it.cand_begin;
+    }
+    __syncthreads();
+
+    const uint8_t* tb = SM ? smem : (P.arena + gd->arena_off);
+    const double* nq = reinterpret_cast<const double*>(tb + gd->off_nq);
+    const uint2* t_clubs = reinterpret_cast<const uint2*>(tb + gd->off_clubs);
+    const uint2* t_friends = reinterpret_cast<const uint2*>(tb + gd->off_friends);
+    const uint2* t_adj = reinterpret_cast<const uint2*>(tb + gd->off_adj);
+    const uint4* t_text = reinterpret_cast<const uint4*>(tb + gd->off_text);
+    const double* vals = reinterpret_cast<const double*>(tb + gd->off_vals);
+    const int log_sc = gd->log_sc, log_sf = gd->log_sf, log_sa = gd->log_sa, log_st = gd->log_st;
+    const int n_lanes = gd->n_lanes;
+    const int T = P.T;
+
+    // ---- this lane's query --------------------------------------------------------------------
+    const int qrow = (lane < n_lanes) ? gd->row[lane] : -1;
+    const bool q_active = qrow >= 0;
+    int q_uid = 0, q_pub = -1, q_gender = -1, q_comp = 0, q_age = 0, q_r0 = -1, q_r1 = -1, q_r2 = -1, q_acnt = 0;
+    uint32_t q_ncl = 0, q_nfr = 0;
+    uint64_t q_mask = 0;
+    double q_sqc = 0.0, q_sqf = 0.0;
+    if (q_active) {
+        const uint4* qr = P.rec + P.rec_off[qrow];
+        const uint4 a = __ldg(qr), b = __ldg(qr + 1), c = __ldg(qr + 2), d = __ldg(qr + 3), e = __ldg(qr + 4);
+        q_uid = (int)a.x; q_pub = (int)a.y; q_gender = (int)a.z; q_comp = (int)a.w;
+        q_age = (int)b.x; q_r0 = (int)b.y; q_r1 = (int)b.z; q_r2 = (int)b.w;
+        q_ncl = c.x; q_nfr = c.y;
+        q_mask = (uint64_t)d.x | ((uint64_t)d.y << 32);
+        q_acnt = (int)d.z;
+        q_sqc = __hiloint2double((int)e.y, (int)e.x);
+        q_sqf = __hiloint2double((int)e.w, (int)e.z);
+    }
+    const uint32_t lane_lt = (1u << lane) - 1u;
+    const int dim_comp = N->dim_comp, dim_age = N->dim_age;
+    const int total_possible = N->total_possible;
+    (void)total_possible;
+
+    // ---- candidate loop: warps grab small chunks of the item's candidate slice -----------------
+    constexpr int kChunk = 4;
+    for (;;) {
+        int c0 = 0;
+        if (lane == 0) c0 = atomicAdd(next, kChunk);
+        c0 = __shfl_sync(kFull, c0, 0);
+        if (c0 >= it.cand_end) break;
+        const int c1 = min(c0 + kChunk, it.cand_end);
+        for (int ci = c0; ci < c1; ++ci) {
+            const int64_t crow = P.cand_rows ? (int64_t)P.cand_rows[ci] : (int64_t)ci;
+            const uint4* cr = P.rec + P.rec_off[crow];
+            const uint32_t* cw = reinterpret_cast<const uint32_t*>(cr);
+            const uint4 h0 = __ldg(cr), h1 = __ldg(cr + 1), h2 = __ldg(cr + 2), h3 = __ldg(cr + 3), h4 = __ldg(cr + 4);
+            const int c_uid = (int)h0.x, c_pub = (int)h0.y, c_gender = (int)h0.z, c_comp = (int)h0.w;
+            const int c_age = (int)h1.x, c_r0 = (int)h1.y, c_r1 = (int)h1.z, c_r2 = (int)h1.w;
+            const uint32_t c_ncl = h2.x, c_nfr = h2.y, c_ncells = h2.z, c_ntok = h2.w;
+            const uint64_t c_mask = (uint64_t)h3.x | ((uint64_t)h3.y << 32);
+            const int c_bcnt = (int)h3.z;
+            const uint32_t o_clubs = kHdrWords, o_friends = o_clubs + pad4(c_ncl), o_cells = o_friends + pad4(c_nfr),
+                           o_keys = o_cells + 4 * c_ncells, o_w = o_keys + pad4(c_ntok);
+
+            float* fo = nullptr;
+            if (FIELDS) {
+                fo = P.out_fields + ((size_t)(it.out_slot + (ci - it.cand_begin)) * 32 + lane) * P.nf;
+                for (int j = 0; j < P.nf; ++j) fo[j] = -1.0f;
+            }
+
+            double sum = 0.0;
+            int used = 0;
+
+            // public / gender: equality (src/recommender_similarity.cpp:38-50)
+            if (q_pub >= 0 && c_pub >= 0) { sum += (q_pub == c_pub) ? N->sig1[0] : N->sig0[0]; ++used; }
+            if (q_gender >= 0 && c_gender >= 0) { sum += (q_gender == c_gender) ? N->sig1[1] : N->sig0[1]; ++used; }
+            // completion / age: min/max ratio (:52-68), tabulated for small values
+            if (q_comp > 0 && c_comp > 0) {
+                double sg;
+                if (q_comp < dim_comp && c_comp < dim_comp) sg = __ldg(P.tab_comp + (size_t)c_comp * dim_comp + q_comp);
+                else {
+                    const int amin = min(q_comp, c_comp), amax = max(q_comp, c_comp);
+                    sg = pk_sigmoid(pk_z(N, 2, (double)amin / (double)amax));
+                }
+                sum += sg; ++used;
+            }
+            if (q_age > 0 && c_age > 0) {
+                double sg;
+                if (q_age < dim_age && c_age < dim_age) sg = __ldg(P.tab_age + (size_t)c_age * dim_age + q_age);
+                else {
+                    const int amin = min(q_age, c_age), amax = max(q_age, c_age);
+                    sg = pk_sigmoid(pk_z(N, 3, (double)amin / (double)amax));
+                }
+                sum += sg; ++used;
+            }
+            // region (:70-77, src/recommender.cpp:130-139)
+            if (q_acnt > 0 && c_bcnt > 0) {
+                const int matches = (int)(q_r0 >= 0 && c_r0 >= 0 && q_r0 == c_r0) + (int)(q_r1 >= 0 && c_r1 >= 0 && q_r1 == c_r1) +
+                                    (int)(q_r2 >= 0 && c_r2 >= 0 && q_r2 == c_r2);
+                sum += N->region[(q_acnt * 4 + c_bcnt) * 4 + matches];
+                ++used;
+                if (FIELDS) fo[0] = (float)((double)matches / (sqrt((double)q_acnt) * sqrt((double)c_bcnt)));
+            }
+            // clubs / friends: |{b in B : b in A}| / (sqrt|A| sqrt|B|) (:79-91, src/recommender.cpp:119-128)
+            #pragma unroll
+            for (int which = 0; which < 2; ++which) {
+                const uint32_t c_n = which ? c_nfr : c_ncl;
+                if (c_n == 0) continue;                               // warp-uniform
+                const uint32_t off = which ? o_friends : o_clubs;
+                const uint2* tab = which ? t_friends : t_clubs;
+                const int lg = which ? log_sf : log_sc;
+                int inter = 0;
+                for (uint32_t e0 = 0; e0 < c_n; e0 += 32) {
+                    const uint32_t i = e0 + lane;
+                    uint32_t m = 0;
+                    if (i < c_n) m = probe_set(tab, lg, __ldg(cw + off + i));
+                    uint32_t hits = __ballot_sync(kFull, m != 0u);
+                    while (hits) {
+                        const int j = __ffs(hits) - 1;
+                        hits &= hits - 1;
+                        const uint32_t mj = __shfl_sync(kFull, m, j);
+                        inter += (mj >> lane) & 1u;
+                    }
+                }
+                const uint32_t q_n = which ? q_nfr : q_ncl;
+                if (q_n > 0) {
+                    const int f = 5 + which;
+                    double sg = N->sig0[f];
+                    if (inter > 0) {
+                        const double denom = (which ? q_sqf : q_sqc) * __hiloint2double(which ? (int)h4.w : (int)h4.y,
+                                                                                        which ? (int)h4.z : (int)h4.x);
+                        const float s = (denom > 0.0) ? (float)((double)inter / denom) : 0.0f;
+                        sg = pk_sigmoid(pk_z(N, f, (double)s));
+                        if (FIELDS) fo[1 + which] = s;
+                    } else if (FIELDS) fo[1 + which] = 0.0f;
+                    if (FIELDS) fo[3 + T + which] = __int_as_float(inter);
+                    sum += sg; ++used;
+                }
+            }
+            // text columns (:93-114): tf-idf cosine per jointly non-empty column
+            if (c_ncells > 0) {
+                const uint4* cells = cr + (o_cells >> 2);
+                const uint32_t* keys = cw + o_keys;
+                const double* tokw = reinterpret_cast<const double*>(cw + o_w);
+                uint32_t cell = 0;
+                uint4 ch = __ldg(cells);
+                double dot = 0.0;
+                for (uint32_t cb = 0; cb < c_ntok; cb += 32) {
+                    const uint32_t i = cb + lane;
+                    uint32_t m = 0, base = 0;
+                    if (i < c_ntok) m = probe_text(t_text, log_st, __ldg(keys + i), &base);
+                    const uint32_t hitb = __ballot_sync(kFull, m != 0u);
+                    double wc = 0.0;
+                    if (m) wc = __ldg(tokw + i);
+                    const uint32_t chunk_end = min(cb + 32u, c_ntok);
+                    uint32_t pos = cb;
+                    while (pos < chunk_end) {
+                        const uint32_t cend = ch.y;
+                        const uint32_t e = min(cend, chunk_end);
+                        const uint32_t hi = e - cb, lo = pos - cb;
+                        uint32_t bits = hitb & ((hi >= 32u) ? kFull : ((1u << hi) - 1u)) & ~((1u << lo) - 1u);
+                        while (bits) {
+                            const int j = __ffs(bits) - 1;
+                            bits &= bits - 1;
+                            const uint32_t mj = __shfl_sync(kFull, m, j);
+                            const uint32_t bj = __shfl_sync(kFull, base, j);
+                            const double wj = __shfl_sync(kFull, wc, j);
+                            if ((mj >> lane) & 1u) dot = __dadd_rn(dot, __dmul_rn(vals[bj + __popc(mj & lane_lt)], wj));
+                        }
+                        pos = e;
+                        if (pos == cend) {   // cell complete: this lane's sigma for column ct
+                            const int ct = (int)(ch.x & 0xffu);
+                            if ((q_mask >> ct) & 1ull) {
+                                const int f = kNumFixed + ct;
+                                double sg = N->sig0[f];
+                                float s = 0.0f;
+                                if (dot != 0.0) {
+                                    const double denom = nq[ct * 32 + lane] * __hiloint2double((int)ch.w, (int)ch.z);
+                                    s = (denom > 0.0) ? (float)(dot / denom) : 0.0f;
+                                    sg = (s == 1.0f) ? N->sig1[f] : pk_sigmoid(pk_z(N, f, (double)s));
+                                }
+                                if (FIELDS) fo[3 + ct] = s;
+                                sum += sg;
+                            }
+                            dot = 0.0;
+                            ++cell;
+                            if (cell < c_ncells) ch = __ldg(cells + cell);
+                        }
+                    }
+                }
+                used += __popcll(q_mask & c_mask);
+            }
+
+            // S, F, harmonic mean (:116-123)
+            float fas = 0.0f;
+            if (used > 0) {
+                const double S = sum / (double)used;
+                const double F = N->ftab[used];
+                fas = (float)((2.0 * S * F) / (S + F));
+            }
+
+            if (EPI == EPI_STORE) {
+                P.out_f[(size_t)(it.out_slot + (ci - it.cand_begin)) * 32 + lane] = q_active ? fas : -1.0f;
+            } else {
+                bool ok = q_active;
+                if (P.exclude_mode >= PK_EXCLUDE_SELF && c_uid == q_uid) ok = false;
+                if (P.exclude_mode >= PK_EXCLUDE_SELF_AND_ADJ) {
+                    const uint32_t mx = probe_set(t_adj, log_sa, (uint32_t)c_uid);   // warp-uniform probe
+                    if ((mx >> lane) & 1u) ok = false;
+                }
+                const uint64_t key = make_key(__float_as_uint(fas), c_uid);
+                const uint64_t tl = reinterpret_cast<volatile uint64_t*>(tau)[lane];
+                uint32_t pass = __ballot_sync(kFull, ok && key > tl);
+                while (pass) {
+                    const int j = __ffs(pass) - 1;
+                    pass &= pass - 1;
+                    const uint64_t kj = __shfl_sync(kFull, key, j);
+                    topk_insert(lists + j * Kp, P.K, Kp, kj, locks + j, reinterpret_cast<volatile uint64_t*>(tau) + j, lane);
+                }
+            }
+        }
+    }
+
+    if (EPI == EPI_TOPK) {
+        __syncthreads();
+        uint64_t* dst = P.out_keys + (size_t)it.out_slot * 32 * Kp;
+        for (int i = tid; i < 32 * Kp; i += kScanThreads) dst[i] = lists[i];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// merge: per query, the K best keys of n_lists sorted lists
+// ------------------------------------------------------------------------------------------------
+
+struct MergeParams {
+    const uint64_t* keys;       // list l of query q: keys + list_off[...] see below
+    // addressing mode A (scan output): list j of query q = keys + ((slot0[q] + j) * 32 + lane[q]) * stride_k
+    // addressing mode B (gathered):    list j of query q = keys + ((size_t)j * nq + q) * stride_k
+    const int32_t* slot0;       // mode A: first out_slot of the query's group (null = mode B)
+    const int32_t* n_lists_q;   // mode A: number of lists of each query
+    const int32_t* lane;        // mode A
+    int n_lists;                // mode B
+    int nq, K, stride_k;
+    uint64_t* out_keys;         // [nq][K], 0-padded
+};
+
+__global__ void __launch_bounds__(128) merge_topk_kernel(const MergeParams P) {
+    const int q = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool modeA = P.slot0 != nullptr;
+    const int nl = modeA ? P.n_lists_q[q] : P.n_lists;
+    __shared__ uint64_t wbest[4];
+    __shared__ int wown[4];
+    // thread t owns lists t, t+128, ...; head[] positions are kept in registers for up to 8 lists per thread
+    constexpr int kOwn = 8;
+    int head[kOwn];
+    #pragma unroll
+    for (int i = 0; i < kOwn; ++i) head[i] = 0;
+    auto list_ptr = [&](int j) -> const uint64_t* {
+        if (modeA) return P.keys + ((size_t)(P.slot0[q] + j) * 32 + P.lane[q]) * P.stride_k;
+        return P.keys + ((size_t)j * P.nq + q) * P.stride_k;
+    };
+    for (int r = 0; r < P.K; ++r) {
+        uint64_t best = 0ull;
+        int own = -1;
+        #pragma unroll
+        for (int i = 0; i < kOwn; ++i) {
+            const int j = tid + i * 128;
+            if (j < nl && head[i] < P.K) {
+                const uint64_t v = list_ptr(j)[head[i]];
+                if (v > best) { best = v; own = i; }
+            }
+        }
+        // block arg-max
+        uint64_t b = best;
+        int src = tid;
+        for (int o = 16; o; o >>= 1) {
+            const uint64_t ob = __shfl_xor_sync(kFull, b, o);
+            const int os = __shfl_xor_sync(kFull, src, o);
+            if (ob > b || (ob == b && os < src)) { b = ob; src = os; }
+        }
+        if (lane == 0) { wbest[warp] = b; wown[warp] = src; }
+        __syncthreads();
+        uint64_t gb = wbest[0];
+        int gs = wown[0];
+        for (int w2 = 1; w2 < 4; ++w2)
+            if (wbest[w2] > gb) { gb = wbest[w2]; gs = wown[w2]; }
+        if (tid == gs && gb != 0ull && own >= 0) {
+            #pragma unroll
+            for (int i = 0; i < kOwn; ++i)
+                if (i == own) ++head[i];
+        }
+        if (tid == 0) P.out_keys[(size_t)q * P.K + r] = gb;
+        __syncthreads();
+    }
+}
+
+// collaborative reduce (reference src/recommender_graph.cpp:167-180,213): for every candidate of a
+// user, score = sum over the user's friends IN ADJACENCY ORDER of (double)w_f * (double)FAS(f, cand),
+// rounded to float once; emitted as sort keys.  `fas` is the output of the store-mode scan: w_f of
+// distinct friend `sl` sits at user_w_off + sl*32 (1-lane group {user} x friends), FAS(f, cand) at
+// user_mat_off + ((sl/32)*n_cand + cand)*32 + sl%32 (one [cand][32] block per 32 distinct friends).
+struct CollabReduceParams {
+    const float* fas;
+    const int32_t* user_cand_begin;   // [nu+1] candidate slice of each user (global candidate index)
+    const int32_t* user_fr_begin;     // [nu+1] slice of fr_slot
+    const int32_t* fr_slot;           // per (user, friend in adjacency order): distinct-friend slot, -1 = no profile
+    const int64_t* user_w_off;        // [nu]
+    const int64_t* user_mat_off;      // [nu]
+    const int32_t* cand_uid;          // per global candidate index
+    uint64_t* out_keys;               // per global candidate index
+    int nu;
+};
+
+__global__ void collab_reduce_kernel(const CollabReduceParams P) {
+    const int u = blockIdx.y;
+    const int cb = P.user_cand_begin[u], ce = P.user_cand_begin[u + 1];
+    const int fb = P.user_fr_begin[u], fe = P.user_fr_begin[u + 1];
+    const int64_t ncand = ce - cb;
+    const float* wv = P.fas + P.user_w_off[u];
+    const float* mat = P.fas + P.user_mat_off[u];
+    for (int c = cb + blockIdx.x * blockDim.x + threadIdx.x; c < ce; c += gridDim.x * blockDim.x) {
+        double score = 0.0;
+        for (int f = fb; f < fe; ++f) {
+            const int sl = P.fr_slot[f];
+            if (sl < 0) continue;
+            const float w = wv[(int64_t)sl * 32];
+            const float sfc = mat[((int64_t)(sl >> 5) * ncand + (c - cb)) * 32 + (sl & 31)];
+            score = __dadd_rn(score, __dmul_rn((double)w, (double)sfc));
+        }
+        P.out_keys[c] = make_key(__float_as_uint((float)score), P.cand_uid[c]);
+    }
+}
+
+// top-k of a flat key slice per user (collaborative / clubs epilogue): one CTA per user, repeated
+// block-wide max extraction.  Slices are short (<= candidate_limit).
+__global__ void __launch_bounds__(256) slice_topk_kernel(uint64_t* keys, const int32_t* begin, int K, uint64_t* out_keys) {
+    const int u = blockIdx.x;
+    const int b = begin[u], e = begin[u + 1];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __shared__ uint64_t wb[8];
+    __shared__ int wi[8];
+    for (int r = 0; r < K; ++r) {
+        uint64_t best = 0ull;
+        int bi = -1;
+        for (int i = b + tid; i < e; i += 256) {
+            const uint64_t v = keys[i];
+            if (v > best) { best = v; bi = i; }
+        }
+        for (int o = 16; o; o >>= 1) {
+            const uint64_t ob = __shfl_xor_sync(kFull, best, o);
+            const int oi = __shfl_xor_sync(kFull, bi, o);
+            if (ob > best) { best = ob; bi = oi; }
+        }
+        if (lane == 0) { wb[warp] = best; wi[warp] = bi; }
+        __syncthreads();
+        if (tid == 0) {
+            uint64_t gb = 0ull;
+            int gi = -1;
+            for (int w2 = 0; w2 < 8; ++w2)
+                if (wb[w2] > gb) { gb = wb[w2]; gi = wi[w2]; }
+            out_keys[(size_t)u * K + r] = gb;
+            if (gi >= 0) keys[gi] = 0ull;
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace pk

@@ -1,0 +1,225 @@
+"""ctypes binding of libpokec_b200.so (include/pokec_b200.h) -- the Python-side handle of the device store.
+
+`DeviceRecommender` mirrors the reference's C++ `Recommender` (include/recommender.h:17-71) method by
+method, batched: recommend_graph_registration / recommend_by_interest / recommend_collaborative /
+recommend_clubs_collab, set_*_normalizers, compute_idf_from_profiles, set_tfidf_index,
+profile_similarity -- plus the north-star full scan.  It fails loudly when the CUDA library or a
+device is missing; there is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import numpy as np
+
+from .cabi import (PkWorld, make_pk_world, ptr, i32p, f32p, u8p, MODE_GRAPH, MODE_COLLAB, MODE_CLUBS,
+                   EXCLUDE_NONE, EXCLUDE_SELF, EXCLUDE_SELF_AND_ADJ)
+from .world import World
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libpokec_b200.so")
+
+# every symbol include/pokec_b200.h declares
+ABI_SYMBOLS = (
+    "pk_last_error", "pk_abi_version", "pk_device_count", "pk_store_create", "pk_store_destroy",
+    "pk_store_load_world", "pk_store_set_shard", "pk_set_normalizers", "pk_compute_idf", "pk_set_idf",
+    "pk_idf_size", "pk_get_idf", "pk_set_adj_row", "pk_pair_similarity", "pk_pair_fields", "pk_pair_overlap",
+    "pk_fullscan_topk", "pk_recommend", "pk_candidates", "pk_fullscan_local_keys", "pk_merge_keys", "pk_sync",
+    "pk_stream", "pk_stat",
+)
+STAT_KERNEL_LAUNCHES, STAT_PAIRS_SCORED, STAT_STORE_BYTES, STAT_SCAN_KERNEL_NS, STAT_SCAN_LAUNCHES, STAT_GROUPS, \
+    STAT_SHARD_RECORD_BYTES = range(7)
+
+_lib = None
+
+
+class PokecError(RuntimeError):
+    pass
+
+
+def load_library():
+    """dlopen the in-tree CUDA library.  No fallback: a missing build is an error."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise PokecError(f"{LIB_PATH} is missing: run `python -m recommendation_system_pokec_b200.build` "
+                             "(there is no CPU implementation of the scoring path)")
+        lib = C.CDLL(LIB_PATH)
+        lib.pk_last_error.restype = C.c_char_p
+        lib.pk_stat.restype = C.c_int64
+        lib.pk_stat.argtypes = [C.c_void_p, C.c_int]
+        lib.pk_stream.restype = C.c_void_p
+        lib.pk_stream.argtypes = [C.c_void_p]
+        lib.pk_store_destroy.argtypes = [C.c_void_p]
+        lib.pk_store_destroy.restype = None
+        _lib = lib
+    return _lib
+
+
+def _check(lib, rc):
+    if rc != 0:
+        raise PokecError(f"libpokec_b200 error {rc}: {lib.pk_last_error().decode()}")
+
+
+class DeviceRecommender:
+    def __init__(self, world: World, device: int = 0, compute_idf: bool = True):
+        self.lib = load_library()
+        self.world = world
+        self.h = C.c_void_p()
+        _check(self.lib, self.lib.pk_store_create(int(device), C.byref(self.h)))
+        self._pw = make_pk_world(world)
+        _check(self.lib, self.lib.pk_store_load_world(self.h, C.byref(self._pw)))
+        if compute_idf:
+            self.compute_idf()
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.pk_store_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- setters (reference src/recommender.cpp:27-66) ---------------------------------------
+    def set_normalizers(self, mean, sd, has=None):
+        mean = np.ascontiguousarray(mean, np.float32)
+        sd = np.ascontiguousarray(sd, np.float32)
+        has_p = None if has is None else ptr(np.ascontiguousarray(has, np.uint8), u8p)
+        _check(self.lib, self.lib.pk_set_normalizers(self.h, ptr(mean, f32p), ptr(sd, f32p), has_p, len(mean)))
+
+    def compute_idf(self, double_log=False):
+        _check(self.lib, self.lib.pk_compute_idf(self.h, int(double_log)))
+
+    def set_idf(self, col, tokens, idf):
+        t = np.ascontiguousarray(tokens, np.int32)
+        v = np.ascontiguousarray(idf, np.float32)
+        assert t.shape == v.shape
+        _check(self.lib, self.lib.pk_set_idf(self.h, int(col), ptr(t, i32p), ptr(v, f32p), C.c_int64(len(t))))
+
+    def erase_idf_column(self, col):
+        _check(self.lib, self.lib.pk_set_idf(self.h, int(col), None, None, C.c_int64(-1)))
+
+    def idf_size(self, col):
+        n = C.c_int64()
+        _check(self.lib, self.lib.pk_idf_size(self.h, int(col), C.byref(n)))
+        return int(n.value)
+
+    def get_idf(self, col):
+        n = self.idf_size(col)
+        if n < 0:
+            return None
+        tok = np.zeros(max(n, 1), np.int32)
+        idf = np.zeros(max(n, 1), np.float32)
+        df = np.zeros(max(n, 1), np.int32)
+        _check(self.lib, self.lib.pk_get_idf(self.h, int(col), ptr(tok, i32p), ptr(idf, f32p), ptr(df, i32p), C.c_int64(n)))
+        return tok[:n], idf[:n], df[:n]
+
+    def erase_idf_tokens(self, col, tokens):
+        tok, idf, _ = self.get_idf(col)
+        keep = ~np.isin(tok, np.asarray(tokens, np.int32))
+        self.set_idf(col, tok[keep], idf[keep])
+
+    def idf_lookup(self, col, tokens):
+        got = self.get_idf(col)
+        t = np.asarray(tokens, np.int32)
+        if got is None:
+            return np.zeros(len(t), np.float32), np.zeros(len(t), bool)
+        tok, idf, _ = got
+        pos = np.searchsorted(tok, t)
+        pos_c = np.minimum(pos, max(len(tok) - 1, 0))
+        has = (pos < len(tok)) & (tok[pos_c] == t) if len(tok) else np.zeros(len(t), bool)
+        return np.where(has, idf[pos_c] if len(tok) else 0, 0).astype(np.float32), has
+
+    def set_adj_row(self, uid, nb):
+        nb = np.ascontiguousarray(nb, np.int32)
+        _check(self.lib, self.lib.pk_set_adj_row(self.h, int(uid), ptr(nb, i32p), C.c_int64(len(nb))))
+
+    def set_shard(self, row_begin, row_end):
+        _check(self.lib, self.lib.pk_store_set_shard(self.h, C.c_int64(row_begin), C.c_int64(row_end)))
+
+    # ---- pairs -----------------------------------------------------------------------------------
+    def pair_similarity(self, a, b):
+        a = np.ascontiguousarray(a, np.int32)
+        b = np.ascontiguousarray(b, np.int32)
+        out = np.zeros(len(a), np.float32)
+        _check(self.lib, self.lib.pk_pair_similarity(self.h, C.c_int64(len(a)), ptr(a, i32p), ptr(b, i32p), ptr(out, f32p)))
+        return out
+
+    def pair_fields(self, a, b):
+        a = np.ascontiguousarray(a, np.int32)
+        b = np.ascontiguousarray(b, np.int32)
+        out = np.zeros((len(a), 3 + self.world.T), np.float32)
+        _check(self.lib, self.lib.pk_pair_fields(self.h, C.c_int64(len(a)), ptr(a, i32p), ptr(b, i32p), ptr(out, f32p)))
+        return out
+
+    def pair_overlap(self, a, b, which):
+        a = np.ascontiguousarray(a, np.int32)
+        b = np.ascontiguousarray(b, np.int32)
+        out = np.zeros(len(a), np.int32)
+        _check(self.lib, self.lib.pk_pair_overlap(self.h, C.c_int64(len(a)), ptr(a, i32p), ptr(b, i32p), int(which), ptr(out, i32p)))
+        return out
+
+    # ---- recommendations ---------------------------------------------------------------------------
+    @staticmethod
+    def _alloc(nq, k):
+        return (np.full((nq, max(k, 0)), -1, np.int32), np.zeros((nq, max(k, 0)), np.float32), np.zeros(nq, np.int32))
+
+    def fullscan(self, q, k, exclude_mode=EXCLUDE_SELF_AND_ADJ):
+        q = np.ascontiguousarray(q, np.int32)
+        ids, sc, cnt = self._alloc(len(q), k)
+        _check(self.lib, self.lib.pk_fullscan_topk(self.h, len(q), ptr(q, i32p), int(k), int(exclude_mode),
+                                                   ptr(ids, i32p), ptr(sc, f32p), ptr(cnt, i32p)))
+        return ids, sc, cnt
+
+    def recommend(self, mode, q, k, limit=10000):
+        q = np.ascontiguousarray(q, np.int32)
+        ids, sc, cnt = self._alloc(len(q), k)
+        _check(self.lib, self.lib.pk_recommend(self.h, int(mode), len(q), ptr(q, i32p), int(k), int(limit),
+                                               ptr(ids, i32p), ptr(sc, f32p), ptr(cnt, i32p)))
+        return ids, sc, cnt
+
+    # reference method names (include/recommender.h:24-35), batched over users
+    def recommend_graph_registration(self, users, topk, candidate_limit=10000):
+        return self.recommend(MODE_GRAPH, users, topk, candidate_limit)
+
+    recommend_by_interest = recommend_graph_registration
+    recommend_friends_graph = recommend_graph_registration
+    recommend_friends_by_interest = recommend_graph_registration
+
+    def recommend_collaborative(self, users, topk, candidate_limit=10000):
+        return self.recommend(MODE_COLLAB, users, topk, candidate_limit)
+
+    recommend_friends_collab = recommend_collaborative
+
+    def recommend_clubs_collab(self, users, topk, candidate_limit=10000):
+        return self.recommend(MODE_CLUBS, users, topk, candidate_limit)
+
+    def candidates(self, mode, user, limit, cap=1 << 20):
+        out = np.zeros(cap, np.int32)
+        n = C.c_int64()
+        _check(self.lib, self.lib.pk_candidates(self.h, int(mode), int(user), int(limit), ptr(out, i32p), C.c_int64(cap), C.byref(n)))
+        return out[:min(int(n.value), cap)].copy()
+
+    # ---- multi-GPU plumbing --------------------------------------------------------------------------
+    def fullscan_local_keys(self, q, k, exclude_mode, d_keys_ptr: int):
+        q = np.ascontiguousarray(q, np.int32)
+        _check(self.lib, self.lib.pk_fullscan_local_keys(self.h, len(q), ptr(q, i32p), int(k), int(exclude_mode),
+                                                         C.c_void_p(d_keys_ptr)))
+
+    def merge_keys(self, d_keys_ptr: int, n_lists, nq, k):
+        ids, sc, cnt = self._alloc(nq, k)
+        _check(self.lib, self.lib.pk_merge_keys(self.h, C.c_void_p(d_keys_ptr), int(n_lists), int(nq), int(k),
+                                                ptr(ids, i32p), ptr(sc, f32p), ptr(cnt, i32p)))
+        return ids, sc, cnt
+
+    def sync(self):
+        _check(self.lib, self.lib.pk_sync(self.h))
+
+    def stream(self) -> int:
+        return int(self.lib.pk_stream(self.h) or 0)
+
+    def stat(self, which) -> int:
+        return int(self.lib.pk_stat(self.h, int(which)))

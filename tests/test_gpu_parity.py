@@ -1,0 +1,276 @@
+"""Parity of the CUDA path (through the C ABI) with the CPU oracle on the same seeded inputs.
+
+Contract:
+  bit-exact   df counts, idf table, set-overlap counts, per-field float similarities, candidate id lists,
+              top-k id sequences including the uid tie-break
+  tolerance   final FAS / collaborative / club scores: <= 1e-5 relative (north_star); in practice they are
+              bit-identical except where the device exp() and the host exp() round differently, which moves
+              a double by 1 ulp and flips the final float with probability ~1e-8 per value.  Such flips are
+              counted and bounded here, never hidden.
+"""
+import numpy as np
+import pytest
+
+from recommendation_system_pokec_b200.cabi import (MODE_GRAPH, MODE_COLLAB, MODE_CLUBS, EXCLUDE_NONE, EXCLUDE_SELF,
+                                                   EXCLUDE_SELF_AND_ADJ)
+from recommendation_system_pokec_b200.synth import sample_queries
+from tests.conftest import make_test_world
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-5          # north_star tolerance for floating-point scores
+MAX_ULP_FLIP_FRAC = 1e-5  # fraction of scores allowed to differ by one float ulp
+
+
+def bits(x):
+    return np.ascontiguousarray(x, np.float32).view(np.int32)
+
+
+def assert_scores_close(got, want, what):
+    got = np.asarray(got, np.float32)
+    want = np.asarray(want, np.float32)
+    assert got.shape == want.shape
+    denom = np.maximum(np.abs(want), 1e-30)
+    rel = np.abs(got.astype(np.float64) - want) / denom
+    assert float(rel.max(initial=0.0)) <= REL_TOL, f"{what}: max rel err {rel.max()}"
+    ulp = np.abs(bits(got).astype(np.int64) - bits(want).astype(np.int64))
+    assert int(ulp.max(initial=0)) <= 1, f"{what}: a score differs by {ulp.max()} ulps"
+    nflip = int((ulp != 0).sum())
+    assert nflip <= max(1, int(MAX_ULP_FLIP_FRAC * got.size)), f"{what}: {nflip} of {got.size} scores differ by 1 ulp"
+    return nflip
+
+
+def assert_topk_equal(got, want, what):
+    gi, gs, gc = got
+    wi, ws, wc = want
+    assert np.array_equal(gc, wc), f"{what}: result counts differ"
+    if not np.array_equal(gi, wi):
+        # an id swap is only acceptable between neighbours whose reference scores are within one ulp
+        bad = np.argwhere(gi != wi)
+        for q, j in bad:
+            near = np.abs(bits(ws[q]).astype(np.int64) - int(bits(ws[q, j:j + 1])[0])) <= 1
+            assert gi[q, j] in wi[q][near], f"{what}: query {q} rank {j}: id {gi[q, j]} vs {wi[q, j]} not explained by a 1-ulp tie"
+        assert len(bad) <= 4, f"{what}: {len(bad)} id mismatches"
+    assert_scores_close(gs, ws, what)
+
+
+@pytest.fixture(scope="module")
+def env(small_world, oracle_libs):
+    from oracle.oracle import CpuOracle
+    from recommendation_system_pokec_b200.engine import DeviceRecommender
+    dev = DeviceRecommender(small_world)
+    orc = CpuOracle(small_world, "port")
+    yield small_world, dev, orc
+    dev.close()
+    orc.close()
+
+
+def random_pairs(w, n, seed):
+    rng = np.random.default_rng(seed)
+    a = w.uid[rng.integers(0, w.n, n)]
+    b = w.uid[rng.integers(0, w.n, n)]
+    # half of the pairs are (user, one of the user's friends): non-trivial overlaps
+    rows = rng.integers(0, w.n, n // 2)
+    deg = np.diff(w.friends_ptr)[rows]
+    ok = deg > 0
+    pick = w.friends_ptr[rows[ok]] + (rng.random(int(ok.sum())) * deg[ok]).astype(np.int64)
+    a[:int(ok.sum())] = w.uid[rows[ok]]
+    b[:int(ok.sum())] = w.friends[pick].astype(np.int32)
+    return a.astype(np.int32), b.astype(np.int32)
+
+
+def test_idf_table_bit_exact(env):
+    w, dev, orc = env
+    for col in (0, 2, 7, 22, 48):
+        tok, idf, df = dev.get_idf(col)
+        assert len(tok) == orc.idf_size(col)
+        want, has = orc.idf_lookup(col, tok)
+        assert has.all()
+        assert np.array_equal(bits(idf), bits(want)), f"idf of column {col}"
+        cell = np.arange(w.n) * w.T + col
+        cnt = np.zeros(int(tok.max()) + 1 if len(tok) else 1, np.int64)
+        for c in cell:
+            ids = w.tok_id[w.tok_ptr[c]:w.tok_ptr[c + 1]]
+            cnt[ids] += 1
+        assert np.array_equal(df, cnt[tok]), f"df of column {col}"
+
+
+def test_pair_fields_and_overlaps_bit_exact(env):
+    w, dev, orc = env
+    a, b = random_pairs(w, 6000, 1)
+    got = dev.pair_fields(a, b)
+    want = orc.pair_fields(a, b, nthreads=8)
+    assert np.array_equal(bits(got), bits(want))
+    for which in (0, 1):
+        assert np.array_equal(dev.pair_overlap(a, b, which), orc.pair_overlap(a, b, which))
+    assert (orc.pair_overlap(a, b, 1) > 0).sum() > 100   # the sample exercises real overlaps
+
+
+def test_pair_similarity(env):
+    w, dev, orc = env
+    a, b = random_pairs(w, 40000, 2)
+    a[:5] = [-5, 0, 2_000_000_000, a[5], a[6]]          # unknown uids -> -1
+    got = dev.pair_similarity(a, b)
+    want = orc.pair_similarity(a, b, nthreads=8)
+    assert (got[:3] == -1).all() and (want[:3] == -1).all()
+    assert_scores_close(got, want, "pair FAS")
+
+
+@pytest.mark.parametrize("exclude", [EXCLUDE_NONE, EXCLUDE_SELF, EXCLUDE_SELF_AND_ADJ])
+def test_fullscan_topk(env, exclude):
+    w, dev, orc = env
+    q = sample_queries(w, 70, seed=3)
+    got = dev.fullscan(q, 50, exclude)
+    want = orc.fullscan(q, 50, exclude, nthreads=8)
+    assert_topk_equal(got, want, f"fullscan exclude={exclude}")
+    assert dev.stat(1) == len(q) * w.n
+
+
+def test_fullscan_edge_cases(env):
+    w, dev, orc = env
+    q = np.array([w.uid[0], -3, w.uid[5], 999_999_999, w.uid[0]], np.int32)   # unknown + repeated users
+    got = dev.fullscan(q, 7, EXCLUDE_SELF)
+    want = orc.fullscan(q, 7, EXCLUDE_SELF, nthreads=2)
+    assert_topk_equal(got, want, "fullscan with unknown users")
+    assert got[2][1] == 0 and got[2][3] == 0
+    # k larger than the candidate set, k = 1, empty batch, k = 0
+    w2 = make_test_world(n=40, seed=3, pairs=200)
+    from oracle.oracle import CpuOracle
+    from recommendation_system_pokec_b200.engine import DeviceRecommender
+    d2, o2 = DeviceRecommender(w2), CpuOracle(w2, "port")
+    for k in (1, 64, 256):
+        assert_topk_equal(d2.fullscan(w2.uid[:9], k, EXCLUDE_SELF_AND_ADJ), o2.fullscan(w2.uid[:9], k, EXCLUDE_SELF_AND_ADJ), f"tiny world k={k}")
+    ids, sc, cnt = d2.fullscan(np.zeros(0, np.int32), 5)
+    assert ids.shape == (0, 5)
+    ids, sc, cnt = d2.fullscan(w2.uid[:3], 0)
+    assert (cnt == 0).all()
+    from recommendation_system_pokec_b200.engine import PokecError
+    with pytest.raises(PokecError):
+        d2.fullscan(w2.uid[:3], 257)
+    d2.close()
+
+
+@pytest.mark.parametrize("mode,limit", [(MODE_GRAPH, 5000), (MODE_GRAPH, 40), (MODE_COLLAB, 5000), (MODE_COLLAB, 25),
+                                        (MODE_CLUBS, 5000)])
+def test_recommend_modes(env, mode, limit):
+    w, dev, orc = env
+    q = sample_queries(w, 48, seed=4 + mode)
+    q = np.concatenate([q, np.array([-1, 123456789], np.int32)])
+    got = dev.recommend(mode, q, 50, limit)
+    want = orc.recommend(mode, q, 50, limit, nthreads=8)
+    assert_topk_equal(got, want, f"recommend mode={mode} limit={limit}")
+    assert want[2].max() > 0
+
+
+def test_candidate_lists_bit_exact(env):
+    w, dev, orc = env
+    for u in sample_queries(w, 25, seed=9):
+        for mode in (MODE_GRAPH, MODE_COLLAB):
+            for limit in (5000, 17, 1):
+                assert np.array_equal(dev.candidates(mode, u, limit), orc.candidates(mode, int(u), limit))
+
+
+def test_gap_world_all_modes(gap_world, oracle_libs):
+    """non-dense uids, neighbours / adjacency rows without profiles, missing normalizer entries, sd == 0"""
+    from oracle.oracle import CpuOracle
+    from recommendation_system_pokec_b200.engine import DeviceRecommender
+    w = gap_world
+    dev, orc = DeviceRecommender(w), CpuOracle(w, "port")
+    q = sample_queries(w, 40, seed=1)
+    assert_topk_equal(dev.fullscan(q, 20, EXCLUDE_SELF_AND_ADJ), orc.fullscan(q, 20, EXCLUDE_SELF_AND_ADJ, nthreads=8), "gap fullscan")
+    for mode in (MODE_GRAPH, MODE_COLLAB, MODE_CLUBS):
+        assert_topk_equal(dev.recommend(mode, q, 20, 300), orc.recommend(mode, q, 20, 300, nthreads=8), f"gap mode {mode}")
+    a, b = random_pairs(w, 3000, 5)
+    assert np.array_equal(bits(dev.pair_fields(a, b)), bits(orc.pair_fields(a, b, nthreads=8)))
+    dev.close()
+
+
+def test_idf_variants(oracle_libs):
+    """set_tfidf_index semantics: a column without an idf entry uses the raw-count cosine
+    (src/recommender_similarity.cpp:99-104); a token missing from a column's table scores with idf 1.0f
+    (src/recommender.cpp:78); TFIDFIndex::build's double-log idf (src/tfidf_index.cpp:25)."""
+    from oracle.oracle import CpuOracle
+    from recommendation_system_pokec_b200.engine import DeviceRecommender
+    w = make_test_world(n=1200, seed=21, pairs=600)
+    dev, orc = DeviceRecommender(w), CpuOracle(w, "port")
+    a, b = random_pairs(w, 4000, 3)
+    for col in (0, 2, 24):
+        dev.erase_idf_column(col)
+        orc.erase_idf_column(col)
+    tok, _, _ = dev.get_idf(4)
+    drop = tok[::3]
+    dev.erase_idf_tokens(4, drop)
+    orc.erase_idf_tokens(4, drop)
+    assert dev.idf_size(0) == -1 and dev.idf_size(4) == orc.idf_size(4)
+    assert np.array_equal(bits(dev.pair_fields(a, b)), bits(orc.pair_fields(a, b, nthreads=8)))
+    assert_scores_close(dev.pair_similarity(a, b), orc.pair_similarity(a, b, nthreads=8), "FAS with partial idf")
+    dev.compute_idf(double_log=True)
+    orc.compute_idf(double_log=True)
+    t2, i2, _ = dev.get_idf(2)
+    want, has = orc.idf_lookup(2, t2)
+    assert has.all() and np.array_equal(bits(i2), bits(want))
+    assert np.array_equal(bits(dev.pair_fields(a, b)), bits(orc.pair_fields(a, b, nthreads=8)))
+    dev.close()
+
+
+def test_normalizer_update(env):
+    w, dev, orc = env
+    from oracle.oracle import CpuOracle
+    w2 = make_test_world(n=3000, seed=7)
+    rng = np.random.default_rng(0)
+    mean = rng.random(w2.n_fields).astype(np.float32) * 0.4
+    sd = (rng.random(w2.n_fields).astype(np.float32) * 0.3 + 0.05)
+    has = (rng.random(w2.n_fields) < 0.8).astype(np.uint8)
+    w2.set_normalizers(mean, sd, has)
+    o2 = CpuOracle(w2, "port")
+    dev.set_normalizers(mean, sd, has)
+    try:
+        a, b = random_pairs(w2, 5000, 8)
+        assert_scores_close(dev.pair_similarity(a, b), o2.pair_similarity(a, b, nthreads=8), "FAS after set_normalizers")
+    finally:
+        dev.set_normalizers(w.norm_mean, w.norm_sd, w.norm_has)
+
+
+def test_sharded_scan_and_key_merge(env):
+    """two candidate shards scanned separately, their key lists merged (the multi-GPU data path on one GPU)"""
+    import torch
+    w, dev, orc = env
+    q = sample_queries(w, 33, seed=12)
+    k = 50
+    full = dev.fullscan(q, k, EXCLUDE_SELF_AND_ADJ)
+    keys = torch.zeros((2, len(q), k), dtype=torch.int64, device="cuda")
+    cut = w.n // 2 + 17
+    for r, (b, e) in enumerate(((0, cut), (cut, w.n))):
+        dev.set_shard(b, e)
+        dev.fullscan_local_keys(q, k, EXCLUDE_SELF_AND_ADJ, keys[r].data_ptr())
+        dev.sync()
+    dev.set_shard(0, w.n)
+    merged = dev.merge_keys(keys.data_ptr(), 2, len(q), k)
+    for x, y in zip(merged, full):
+        assert np.array_equal(x, y)
+
+
+def test_vs_compiled_reference(small_world, oracle_libs):
+    """the same comparison against the UNMODIFIED reference built from /root/reference (when the prebuilt
+    library travelled with the snapshot)"""
+    from oracle.oracle import CpuOracle, reference_available
+    from recommendation_system_pokec_b200.engine import DeviceRecommender
+    if not reference_available():
+        pytest.skip("oracle/_ref/libpokec_ref.so not present")
+    w = small_world
+    dev, ref = DeviceRecommender(w), CpuOracle(w, "reference")
+    a, b = random_pairs(w, 20000, 13)
+    assert_scores_close(dev.pair_similarity(a, b), ref.pair_similarity(a, b, nthreads=8), "pair FAS vs reference")
+    q = sample_queries(w, 32, seed=14)
+    assert_topk_equal(dev.fullscan(q, 50, EXCLUDE_SELF_AND_ADJ), ref.fullscan(q, 50, EXCLUDE_SELF_AND_ADJ, nthreads=8), "fullscan vs reference")
+    for mode in (MODE_GRAPH, MODE_COLLAB, MODE_CLUBS):
+        assert_topk_equal(dev.recommend(mode, q, 20, 5000), ref.recommend(mode, q, 20, 5000, nthreads=8), f"mode {mode} vs reference")
+    # adjacency mutated behind the recommender (src/test.cpp:59-73)
+    u = int(q[0])
+    ai = int(np.searchsorted(w.adj_uid, u))
+    row = w.adj[w.adj_ptr[ai]:w.adj_ptr[ai + 1]] if ai < w.n_adj_rows and w.adj_uid[ai] == u else np.zeros(0, np.int32)
+    if len(row) > 2:
+        dev.set_adj_row(u, row[: len(row) // 2])
+        ref.set_adj_row(u, row[: len(row) // 2])
+        assert_topk_equal(dev.recommend(MODE_COLLAB, q[:4], 20, 1000), ref.recommend(MODE_COLLAB, q[:4], 20, 1000), "collab after set_adj_row")
+    dev.close()
