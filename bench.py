@@ -1,0 +1,307 @@
+#!/usr/bin/env python
+"""bench.py -- query-users/sec of the FAS top-50 full scan (BASELINE.json configs[1]).
+
+One "step" = one pass of the hot path over one batch: Q = 4096 query users, each scored with
+Fill-Aware Similarity against EVERY one of the 1 632 803 synthetic Pokec-shaped profiles, top-50 per
+query by the reference comparator.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # our CUDA path
+    python bench.py --impl reference [...]                         # the reference's CPU code, host cores
+
+N > 1 is launched by the driver with torch.distributed.run: one process per GPU, candidates partitioned by
+row range (user-id range), per-rank top-k keys all-gathered over NCCL and merged (north_star).
+
+Prints ONE JSON line on rank 0 (see README / DESIGN.md for the keys).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from recommendation_system_pokec_b200.synth import make_world, sample_normalizers, sample_queries, POKEC_N  # noqa: E402
+from recommendation_system_pokec_b200.cabi import EXCLUDE_SELF_AND_ADJ  # noqa: E402
+
+METRIC = "query-users/sec, FAS top-50 full scan vs 1.63M users"
+UNIT = "query-users/s"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def measured_peak_hbm():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """samples nvidia-smi clocks / throttle reasons while the timed region runs"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+                for nme, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nme)
+            except Exception:
+                pass
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def build_world(n_users):
+    t = time.time()
+    w = make_world(n=n_users)
+    mean, sd = sample_normalizers(w, pairs=4000)
+    w.set_normalizers(mean, sd)
+    log(f"[bench] world: {w.meta} ({time.time() - t:.1f}s)")
+    return w
+
+
+def cpu_reference_run(world, n_full, sample_users, q_per_thread, steps, warmup, threads):
+    """Times the reference's own CPU implementation (oracle/_ref, the unmodified reference compiled from
+    /root/reference) -- or the CPU restatement when that library did not travel -- on a bounded sample of the
+    workload: `threads * q_per_thread` query users x the first `sample_users` candidates per step."""
+    from oracle.oracle import CpuOracle, reference_available
+    kind = "reference" if reference_available() else "port"
+    sub = world.head(sample_users)
+    t = time.time()
+    orc = CpuOracle(sub, kind)
+    log(f"[bench] cpu baseline ({kind}) store over {sub.n} users built in {time.time() - t:.1f}s")
+    nq = threads * q_per_thread
+    q = sample_queries(sub, nq, seed=2)
+    times = []
+    for i in range(warmup + steps):
+        t = time.perf_counter()
+        orc.fullscan(q, 50, EXCLUDE_SELF_AND_ADJ, nthreads=threads)
+        dt = time.perf_counter() - t
+        if i >= warmup:
+            times.append(dt)
+    orc.close()
+    total = sum(times)
+    pairs_per_s = len(q) * sub.n * len(times) / total
+    value = pairs_per_s / n_full            # query-users/s against the full candidate set
+    sample = (f"{len(q)} query users x first {sub.n} of {n_full} candidates per step, {len(times)} timed step(s), "
+              f"scaled by candidates ({pairs_per_s / 1e6:.2f} M pairs/s)")
+    return dict(value=value, unit=UNIT, cores=threads, kind=kind, sample=sample), total / len(times)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--users", type=int, default=POKEC_N)
+    ap.add_argument("--queries", type=int, default=4096)
+    ap.add_argument("--topk", type=int, default=50)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample-users", type=int, default=200_000)
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    threads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    config = {"workload": f"FAS interest top-{args.topk} full scan, {args.queries} query users x {args.users} candidates "
+                          f"(BASELINE configs[1])",
+              "users": args.users, "queries_per_step": args.queries, "topk": args.topk,
+              "exclude": "self + existing friends (recommender_graph.cpp:46-52)",
+              "l2": "inputs larger than L2 (packed store >> 126 MB)",
+              "parallelism": f"candidate rows sharded over {world_size} GPU(s), NCCL all-gather + merge" if world_size > 1
+              else "1 GPU"}
+
+    # ------------------------------------------------------------------ reference arm (CPU)
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        w = build_world(args.users)      # the same world as our arm; the sample is its first rows
+        base, step_s = cpu_reference_run(w, args.users, min(args.cpu_sample_users, w.n), 2, max(args.steps, 1), args.warmup, threads)
+        out = {"impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus,
+               "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True,
+               "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+               "cpu_baseline": base,
+               "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+               "gpu_launches": 0}
+        print(json.dumps(out), flush=True)
+        return 0
+
+    # ------------------------------------------------------------------ our arm (CUDA)
+    import torch
+    import torch.distributed as dist
+    from recommendation_system_pokec_b200 import engine
+    from recommendation_system_pokec_b200.engine import DeviceRecommender
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the scoring path has no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local_rank)
+    if world_size > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    world = build_world(args.users)
+    n = world.n
+    t0 = time.time()
+    dev = DeviceRecommender(world, device=local_rank)
+    lo, hi = n * rank // world_size, n * (rank + 1) // world_size
+    dev.set_shard(lo, hi)
+    q = sample_queries(world, args.queries, seed=2)
+    nq, k = len(q), args.topk
+    dev.fullscan_prepare(q, k, EXCLUDE_SELF_AND_ADJ)       # builds idf, packed store, plan
+    dev.sync()
+    log(f"[bench] rank {rank}: store {dev.stat(engine.STAT_STORE_BYTES) / 1e9:.2f} GB packed, shard rows [{lo},{hi}) "
+        f"ready in {time.time() - t0:.1f}s")
+
+    stream = torch.cuda.ExternalStream(dev.stream(), device=local_rank)
+    gathered = torch.zeros((world_size, nq, k), dtype=torch.int64, device=f"cuda:{local_rank}")
+    local = torch.zeros((nq, k), dtype=torch.int64, device=f"cuda:{local_rank}")
+
+    def device_step():
+        dev.fullscan_execute()
+        if world_size > 1:
+            dev.fullscan_keys(local.data_ptr())
+            with torch.cuda.stream(stream):
+                dist.all_gather_into_tensor(gathered.view(-1), local.view(-1))
+            return dev.merge_keys(gathered.data_ptr(), world_size, nq, k)
+        return None
+
+    def e2e_step():
+        if world_size == 1:
+            return dev.fullscan(q, k, EXCLUDE_SELF_AND_ADJ)
+        dev.fullscan_local_keys(q, k, EXCLUDE_SELF_AND_ADJ, local.data_ptr())
+        with torch.cuda.stream(stream):
+            dist.all_gather_into_tensor(gathered.view(-1), local.view(-1))
+        return dev.merge_keys(gathered.data_ptr(), world_size, nq, k)
+
+    def barrier():
+        dev.sync()
+        torch.cuda.synchronize()
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world_size == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident measurement: prepared plan, kernels only --------------------------------
+    for _ in range(args.warmup):
+        device_step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = dev.stat(engine.STAT_KERNEL_LAUNCHES)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for _ in range(args.steps):
+        device_step()
+    ev1.record(stream)
+    barrier()
+    dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    launches = dev.stat(engine.STAT_KERNEL_LAUNCHES) - launches0
+    # scan-kernel time of the LAST timed step (CUDA events on the launching stream, inside the timed region)
+    scan_ns = dev.stat(engine.STAT_SCAN_KERNEL_NS)
+    scan_launches = dev.stat(engine.STAT_SCAN_LAUNCHES)
+    clocks = sampler.stop() if rank == 0 else None
+    value = nq * args.steps / (dev_ms / 1e3)
+
+    # ---- end to end: host uids in, host top-k out, every step -------------------------------------
+    for _ in range(1):
+        e2e_step()
+    barrier()
+    h2d0, d2h0 = dev.stat(engine.STAT_H2D_BYTES), dev.stat(engine.STAT_D2H_BYTES)
+    t = time.perf_counter()
+    for _ in range(args.steps):
+        res = e2e_step()
+    barrier()
+    e2e_s = max_over_ranks(time.perf_counter() - t)
+    h2d = (dev.stat(engine.STAT_H2D_BYTES) - h2d0) // args.steps + q.nbytes
+    d2h = (dev.stat(engine.STAT_D2H_BYTES) - d2h0) // args.steps
+    e2e_value = nq * args.steps / e2e_s
+    assert res is not None and int(res[2].min()) == k, "e2e step returned incomplete top-k lists"
+
+    # ---- roofline of the dominant kernel (fas_scan_kernel) ------------------------------------------
+    rec_bytes = world.canonical_record_bytes()
+    b_shard = int(rec_bytes[lo:hi].sum())             # canonical bytes of this rank's candidate shard
+    alg_bytes_per_launch = nq * b_shard / max(scan_launches, 1)
+    scan_s = scan_ns / 1e9 / max(scan_launches, 1)
+    peak, peak_src = measured_peak_hbm()
+    achieved = alg_bytes_per_launch / scan_s / 1e9 if scan_s > 0 else 0.0
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "kernel": "fas_scan_kernel<true,0,false>", "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": alg_bytes_per_launch, "launch_ms": scan_s * 1e3,
+                "note": "algorithmic bytes = queries x canonical record bytes of the shard (SURVEY 8d); cross-query reuse of a "
+                        "streamed record is not credited, so this can exceed the physical DRAM fraction (see profiles/)"}
+
+    out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world_size, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+           "dtype": "f64", "data": "synthetic", "config": config, "clocks": clocks,
+           "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                   "ms_per_step": e2e_s / args.steps * 1e3},
+           "gpu_launches": int(launches), "roofline": roofline}
+
+    if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
+        dev.close()
+        base, _ = cpu_reference_run(world, n, min(args.cpu_sample_users, n), 8, 1, 0, threads)
+        out["cpu_baseline"] = base
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    if world_size > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -112,6 +112,17 @@ int pk_pair_overlap(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t*
 int pk_fullscan_topk(pk_store* s, int nq, const int32_t* q_uid, int k, int exclude_mode,
                      int32_t* out_id, float* out_score, int32_t* out_cnt);
 
+/* The same call in three stages, for callers that pipeline batches or time the device work alone:
+ *   prepare  host planning (queries -> groups of 32 -> work items) and upload of the plan
+ *   execute  query-table build, scan and merge kernels; asynchronous on the store's stream; may be
+ *            repeated (it recomputes everything from device-resident inputs)
+ *   fetch    synchronise, copy the merged keys to the host and decode them
+ *   keys     asynchronous device-to-device copy of the merged keys ([nq][k] uint64) into d_keys */
+int pk_fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclude_mode);
+int pk_fullscan_execute(pk_store* s);
+int pk_fullscan_fetch(pk_store* s, int32_t* out_id, float* out_score, int32_t* out_cnt);
+int pk_fullscan_keys(pk_store* s, uint64_t* d_keys);
+
 /* Batched form of the reference's recommend calls (include/recommender.h:24-28):
  *   PK_MODE_GRAPH  recommend_graph_registration == recommend_by_interest (src/recommender_graph.cpp:33-103,224-227)
  *   PK_MODE_COLLAB recommend_collaborative (src/recommender_graph.cpp:105-222)
@@ -150,7 +161,9 @@ enum {
     PK_STAT_SCAN_KERNEL_NS = 3,    /* device time of the scan kernel(s) of the last scoring call (CUDA events) */
     PK_STAT_SCAN_LAUNCHES = 4,     /* scan kernel launches of the last scoring call */
     PK_STAT_GROUPS = 5,            /* query groups of the last scoring call */
-    PK_STAT_SHARD_RECORD_BYTES = 6 /* bytes of the packed records inside the candidate shard */
+    PK_STAT_SHARD_RECORD_BYTES = 6,/* bytes of the packed records inside the candidate shard */
+    PK_STAT_H2D_BYTES = 7,         /* host-to-device bytes copied by this store since creation */
+    PK_STAT_D2H_BYTES = 8          /* device-to-host result bytes copied since creation */
 };
 int64_t pk_stat(pk_store* s, int which);
 

@@ -96,6 +96,21 @@ double h_sigmoid(double x) {
 
 }  // namespace
 
+struct FullscanJob {
+    bool valid = false;
+    int nq = 0, k = 0, K = 0, Kp = 0, exclude = 0, n_groups = 0;
+    bool with_excl = false;
+    size_t n_sm = 0, n_gl = 0;
+    uint32_t max_smem_arena = 0;
+    uint64_t arena_bytes = 0;
+    int64_t pairs = 0;
+    DevBuf<GroupDesc> groups;
+    DevBuf<WorkItem> items;
+    DevBuf<uint8_t> arena;
+    DevBuf<int32_t> excl, q_slot0, q_nl, q_lane;
+    DevBuf<uint64_t> keys_a, keys_b;
+};
+
 struct pk_store {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -159,6 +174,9 @@ struct pk_store {
     DevBuf<uint32_t> d_u32a;
     DevBuf<int> d_flag;
     DevBuf<ClubEdge> d_edges;
+    FullscanJob job;
+    bool scan_time_pending = false;
+    int64_t stat_h2d = 0, stat_d2h = 0;
     int64_t last_idf_n = 0;
 
     // ---- stats ------------------------------------------------------------------------------------
@@ -193,6 +211,7 @@ template <class T>
 int upload(pk_store* s, DevBuf<T>& buf, const T* src, size_t n) {
     TRY(buf.reserve(std::max<size_t>(n, 1)));
     if (n) CK(cudaMemcpyAsync(buf.p, src, n * sizeof(T), cudaMemcpyHostToDevice, s->stream));
+    s->stat_h2d += (int64_t)(n * sizeof(T));
     return PK_OK;
 }
 template <class T>
@@ -412,12 +431,6 @@ uint32_t scan_fixed_smem(int Kp) {
     return norm + 32u * Kp * 8u + 32u * 8u + 32u * 4u + 16u;
 }
 
-struct Launcher {
-    pk_store* s;
-    Plan* plan;
-    std::vector<WorkItem> items_sm, items_gl;
-};
-
 int upload_plan(pk_store* s, Plan& plan, bool with_excl) {
     uint64_t off = 0;
     for (auto& g : plan.groups) {
@@ -442,42 +455,69 @@ int upload_plan(pk_store* s, Plan& plan, bool with_excl) {
 }
 
 template <int EPI, bool FIELDS>
-int launch_scan_t(pk_store* s, ScanParams P, const std::vector<WorkItem>& items, bool sm, uint32_t smem_bytes) {
-    if (items.empty()) return PK_OK;
-    TRY(upload(s, s->d_items, items));
-    P.items = s->d_items.p;
-    CK(cudaEventRecord(s->ev0, s->stream));
+int launch_scan_t(pk_store* s, ScanParams P, const WorkItem* d_items, size_t n_items, bool sm, uint32_t smem_bytes) {
+    if (n_items == 0) return PK_OK;
+    P.items = d_items;
     if (sm) {
         auto kern = fas_scan_kernel<true, EPI, FIELDS>;
         CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-        kern<<<(unsigned)items.size(), kScanThreads, smem_bytes, s->stream>>>(P);
+        kern<<<(unsigned)n_items, kScanThreads, smem_bytes, s->stream>>>(P);
     } else {
         auto kern = fas_scan_kernel<false, EPI, FIELDS>;
         CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-        kern<<<(unsigned)items.size(), kScanThreads, smem_bytes, s->stream>>>(P);
+        kern<<<(unsigned)n_items, kScanThreads, smem_bytes, s->stream>>>(P);
     }
     CK(cudaGetLastError());
-    CK(cudaEventRecord(s->ev1, s->stream));
-    CK(cudaStreamSynchronize(s->stream));   // d_items is reused by the next launch
-    float ms = 0.f;
-    CK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
-    s->stat_scan_ns += (int64_t)(ms * 1e6);
     ++s->stat_scan_launches;
     ++s->stat_launches;
     return PK_OK;
 }
 
-// runs the scan for items whose group fits shared memory, then for the others
+// launches the scan over device-resident items: first the n_sm items whose group tables are staged in
+// shared memory, then the n_gl items whose tables stay in global memory.  Asynchronous; the scan time is
+// read from the events by collect_scan_time() after the caller synchronised.
+template <int EPI, bool FIELDS>
+int launch_scan(pk_store* s, ScanParams P, const WorkItem* d_items, size_t n_sm, size_t n_gl, uint32_t max_smem_arena) {
+    const uint32_t fixed = scan_fixed_smem(EPI == EPI_TOPK ? P.Kp : 0);
+    CK(cudaEventRecord(s->ev0, s->stream));
+    P.smem_arena_bytes = max_smem_arena;
+    TRY((launch_scan_t<EPI, FIELDS>(s, P, d_items, n_sm, true, max_smem_arena + fixed)));
+    P.smem_arena_bytes = 0;
+    TRY((launch_scan_t<EPI, FIELDS>(s, P, d_items + n_sm, n_gl, false, fixed)));
+    CK(cudaEventRecord(s->ev1, s->stream));
+    s->scan_time_pending = true;
+    return PK_OK;
+}
+
+int collect_scan_time(pk_store* s) {
+    if (!s->scan_time_pending) return PK_OK;
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+    s->stat_scan_ns += (int64_t)((double)ms * 1e6);
+    s->scan_time_pending = false;
+    return PK_OK;
+}
+
+// orders the items (shared-memory groups first) and uploads them into `buf`
+int upload_items(pk_store* s, const Plan& plan, const std::vector<WorkItem>& items, DevBuf<WorkItem>& buf, size_t* n_sm,
+                 size_t* n_gl) {
+    std::vector<WorkItem> all;
+    all.reserve(items.size());
+    for (const auto& it : items) if (plan.groups[it.group].in_smem) all.push_back(it);
+    *n_sm = all.size();
+    for (const auto& it : items) if (!plan.groups[it.group].in_smem) all.push_back(it);
+    *n_gl = all.size() - *n_sm;
+    return upload(s, buf, all);
+}
+
+// upload + launch + synchronise (the list / pair paths)
 template <int EPI, bool FIELDS>
 int run_scan(pk_store* s, const Plan& plan, ScanParams P, const std::vector<WorkItem>& items) {
-    std::vector<WorkItem> a, b;
-    for (const auto& it : items) (plan.groups[it.group].in_smem ? a : b).push_back(it);
-    const uint32_t fixed = scan_fixed_smem(EPI == EPI_TOPK ? P.Kp : 0);
-    P.smem_arena_bytes = plan.max_smem_arena;
-    TRY((launch_scan_t<EPI, FIELDS>(s, P, a, true, plan.max_smem_arena + fixed)));
-    P.smem_arena_bytes = 0;
-    TRY((launch_scan_t<EPI, FIELDS>(s, P, b, false, fixed)));
-    return PK_OK;
+    size_t n_sm = 0, n_gl = 0;
+    TRY(upload_items(s, plan, items, s->d_items, &n_sm, &n_gl));
+    TRY((launch_scan<EPI, FIELDS>(s, P, s->d_items.p, n_sm, n_gl, plan.max_smem_arena)));
+    CK(cudaStreamSynchronize(s->stream));
+    return collect_scan_time(s);
 }
 
 ScanParams base_scan_params(pk_store* s, int K) {
@@ -523,14 +563,18 @@ int check_topk_args(pk_store* s, int nq, const int32_t* q_uid, int k) {
 }
 
 // ---- full scan ---------------------------------------------------------------------------------------
-// leaves the merged keys [nq][k] in s->d_keys_b
-int fullscan_device(pk_store* s, int nq, const int32_t* q_uid, int k, int exclude_mode) {
-    s->stat_scan_ns = 0; s->stat_scan_launches = 0; s->stat_pairs = 0; s->stat_groups = 0;
+// prepare: host planning + upload (queries -> groups -> work items); execute: arena clear, group_prep,
+// scan, merge -- all asynchronous on the store's stream, device-resident inputs only; fetch: D2H + decode.
+int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclude_mode) {
+    FullscanJob& J = s->job;
+    J.valid = false;
+    J.nq = nq; J.k = k; J.exclude = exclude_mode;
     const int K = std::max(k, 1), Kp = (K + 31) / 32 * 32;
-    TRY(s->d_keys_b.reserve((size_t)std::max(nq, 1) * K));
-    CK(cudaMemsetAsync(s->d_keys_b.p, 0, (size_t)std::max(nq, 1) * K * 8, s->stream));
+    J.K = K; J.Kp = Kp;
+    J.n_groups = 0; J.n_sm = J.n_gl = 0; J.pairs = 0;
+    TRY(J.keys_b.reserve((size_t)std::max(nq, 1) * K));
     const int64_t n_cand = s->shard_end - s->shard_begin;
-    if (nq == 0 || k == 0 || n_cand <= 0) { CK(cudaStreamSynchronize(s->stream)); return PK_OK; }
+    if (nq == 0 || k == 0 || n_cand <= 0) { J.valid = true; return PK_OK; }
 
     // group the queries that have a profile, in caller order
     Plan plan;
@@ -578,15 +622,27 @@ int fullscan_device(pk_store* s, int nq, const int32_t* q_uid, int k, int exclud
     }
     close_group();
     const int ng = (int)plan.groups.size();
-    s->stat_groups = ng;
-    if (ng == 0) { CK(cudaStreamSynchronize(s->stream)); return PK_OK; }
-    TRY(upload_plan(s, plan, exclude_mode >= PK_EXCLUDE_SELF_AND_ADJ));
+    J.n_groups = ng;
+    if (ng == 0) { J.valid = true; return PK_OK; }
+    uint64_t off = 0;
+    for (auto& gg : plan.groups) {
+        gg.arena_off = (uint32_t)off;
+        off += gg.arena_bytes;
+        if (off > 0xF0000000ull) return fail(PK_ERR_UNSUPPORTED, "query batch too large for one arena (split the batch)");
+    }
+    J.arena_bytes = off;
+    J.max_smem_arena = plan.max_smem_arena;
+    J.with_excl = exclude_mode >= PK_EXCLUDE_SELF_AND_ADJ;
+    TRY(J.arena.reserve(std::max<uint64_t>(off, 16)));
+    TRY(upload(s, J.groups, plan.groups));
+    if (J.with_excl) TRY(upload(s, J.excl, plan.excl));
 
     // work items: every group scans the whole shard, split into slices so that the grid fills the GPU
     int sm_count = 148;
     cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, s->device);
     int64_t splits = (int64_t)(sm_count * 6 + ng - 1) / ng;
     splits = std::max<int64_t>(1, std::min<int64_t>(splits, (n_cand + 1023) / 1024));
+    if (splits > 128 * 8) splits = 128 * 8;
     std::vector<WorkItem> items;
     std::vector<int32_t> g_slot0(ng);
     for (int gi = 0; gi < ng; ++gi) {
@@ -599,32 +655,63 @@ int fullscan_device(pk_store* s, int nq, const int32_t* q_uid, int k, int exclud
             it.out_slot = (int32_t)items.size();
             items.push_back(it);
         }
-        s->stat_pairs += (int64_t)plan.groups[gi].n_lanes * n_cand;
+        J.pairs += (int64_t)plan.groups[gi].n_lanes * n_cand;
     }
     for (int q = 0; q < nq; ++q) {
         if (q_nl[q] == 0) continue;
         q_slot0[q] = g_slot0[q_slot0[q]];
         q_nl[q] = (int32_t)splits;
     }
-    TRY(s->d_keys_a.reserve(items.size() * 32 * (size_t)Kp));
-    ScanParams P = base_scan_params(s, K);
-    P.exclude_mode = exclude_mode;
-    P.out_keys = s->d_keys_a.p;
-    // out_slot must index d_keys_a for both launches: keep the original slots
-    TRY((run_scan<EPI_TOPK, false>(s, plan, P, items)));
+    TRY(J.keys_a.reserve(items.size() * 32 * (size_t)Kp));
+    TRY(upload_items(s, plan, items, J.items, &J.n_sm, &J.n_gl));
+    TRY(upload(s, J.q_slot0, q_slot0));
+    TRY(upload(s, J.q_nl, q_nl));
+    TRY(upload(s, J.q_lane, q_lane));
+    CK(cudaStreamSynchronize(s->stream));
+    J.valid = true;
+    return PK_OK;
+}
 
-    TRY(upload(s, s->d_i32a, q_slot0));
-    TRY(upload(s, s->d_i32b, q_nl));
-    TRY(upload(s, s->d_i32c, q_lane));
-    MergeParams M;
-    memset(&M, 0, sizeof(M));
-    M.keys = s->d_keys_a.p; M.slot0 = s->d_i32a.p; M.n_lists_q = s->d_i32b.p; M.lane = s->d_i32c.p;
-    M.nq = nq; M.K = K; M.stride_k = Kp; M.out_keys = s->d_keys_b.p;
-    if (splits > 128 * 8) return fail(PK_ERR_UNSUPPORTED, "too many splits");
-    merge_topk_kernel<<<nq, 128, 0, s->stream>>>(M);
+int fullscan_execute(pk_store* s) {
+    FullscanJob& J = s->job;
+    if (!J.valid) return fail(PK_ERR_STATE, "pk_fullscan_prepare has not been called");
+    s->stat_scan_ns = 0; s->stat_scan_launches = 0;
+    s->stat_pairs = J.pairs; s->stat_groups = J.n_groups;
+    CK(cudaMemsetAsync(J.keys_b.p, 0, (size_t)std::max(J.nq, 1) * J.K * 8, s->stream));
+    if (J.n_groups == 0) return PK_OK;
+    CK(cudaMemsetAsync(J.arena.p, 0, std::max<uint64_t>(J.arena_bytes, 16), s->stream));
+    PrepParams PP;
+    PP.rec = s->d_rec.p; PP.rec_off = s->d_rec_off.p; PP.groups = J.groups.p; PP.arena = J.arena.p;
+    PP.excl_ids = J.with_excl ? J.excl.p : nullptr;
+    group_prep_kernel<<<(unsigned)J.n_groups, kPrepThreads, 0, s->stream>>>(PP);
     ++s->stat_launches;
     CK(cudaGetLastError());
+    ScanParams P = base_scan_params(s, J.K);
+    P.groups = J.groups.p; P.arena = J.arena.p;
+    P.exclude_mode = J.exclude;
+    P.out_keys = J.keys_a.p;
+    TRY((launch_scan<EPI_TOPK, false>(s, P, J.items.p, J.n_sm, J.n_gl, J.max_smem_arena)));
+    MergeParams M;
+    memset(&M, 0, sizeof(M));
+    M.keys = J.keys_a.p; M.slot0 = J.q_slot0.p; M.n_lists_q = J.q_nl.p; M.lane = J.q_lane.p;
+    M.nq = J.nq; M.K = J.K; M.stride_k = J.Kp; M.out_keys = J.keys_b.p;
+    merge_topk_kernel<<<J.nq, 128, 0, s->stream>>>(M);
+    ++s->stat_launches;
+    CK(cudaGetLastError());
+    return PK_OK;
+}
+
+int fullscan_fetch(pk_store* s, int32_t* out_id, float* out_score, int32_t* out_cnt) {
+    FullscanJob& J = s->job;
+    if (!J.valid) return fail(PK_ERR_STATE, "pk_fullscan_prepare has not been called");
+    if (J.nq == 0) return PK_OK;
+    if (J.k == 0) { for (int q = 0; q < J.nq; ++q) out_cnt[q] = 0; return PK_OK; }
+    std::vector<uint64_t> keys((size_t)J.nq * J.k);
+    CK(cudaMemcpyAsync(keys.data(), J.keys_b.p, keys.size() * 8, cudaMemcpyDeviceToHost, s->stream));
+    s->stat_d2h += (int64_t)keys.size() * 8;
     CK(cudaStreamSynchronize(s->stream));
+    TRY(collect_scan_time(s));
+    decode_keys(keys.data(), J.nq, J.k, out_id, out_score, out_cnt);
     return PK_OK;
 }
 
@@ -1355,30 +1442,47 @@ int pk_pair_overlap(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t*
     return PK_OK;
 }
 
-int pk_fullscan_topk(pk_store* s, int nq, const int32_t* q_uid, int k, int exclude_mode, int32_t* out_id, float* out_score,
-                     int32_t* out_cnt) {
+int pk_fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclude_mode) {
     TRY(ensure_ready(s));
     TRY(check_topk_args(s, nq, q_uid, k));
-    if (nq > 0 && (!out_cnt || (k > 0 && (!out_id || !out_score)))) return fail(PK_ERR_ARG, "null output");
     if (exclude_mode < PK_EXCLUDE_NONE || exclude_mode > PK_EXCLUDE_SELF_AND_ADJ) return fail(PK_ERR_ARG, "bad exclude_mode");
-    if (nq == 0) return PK_OK;
-    if (k == 0) { for (int q = 0; q < nq; ++q) out_cnt[q] = 0; return PK_OK; }
-    TRY(fullscan_device(s, nq, q_uid, k, exclude_mode));
-    std::vector<uint64_t> keys((size_t)nq * k);
-    CK(cudaMemcpyAsync(keys.data(), s->d_keys_b.p, keys.size() * 8, cudaMemcpyDeviceToHost, s->stream));
-    CK(cudaStreamSynchronize(s->stream));
-    decode_keys(keys.data(), nq, k, out_id, out_score, out_cnt);
+    return fullscan_prepare(s, nq, q_uid, k, exclude_mode);
+}
+
+int pk_fullscan_execute(pk_store* s) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    CK(cudaSetDevice(s->device));
+    return fullscan_execute(s);
+}
+
+int pk_fullscan_fetch(pk_store* s, int32_t* out_id, float* out_score, int32_t* out_cnt) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    if (s->job.valid && s->job.nq > 0 && (!out_cnt || (s->job.k > 0 && (!out_id || !out_score)))) return fail(PK_ERR_ARG, "null output");
+    CK(cudaSetDevice(s->device));
+    return fullscan_fetch(s, out_id, out_score, out_cnt);
+}
+
+int pk_fullscan_keys(pk_store* s, uint64_t* d_keys) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    if (!s->job.valid) return fail(PK_ERR_STATE, "pk_fullscan_prepare has not been called");
+    if (s->job.nq == 0 || s->job.k == 0) return PK_OK;
+    if (!d_keys) return fail(PK_ERR_ARG, "null d_keys");
+    CK(cudaMemcpyAsync(d_keys, s->job.keys_b.p, (size_t)s->job.nq * s->job.k * 8, cudaMemcpyDeviceToDevice, s->stream));
     return PK_OK;
 }
 
+int pk_fullscan_topk(pk_store* s, int nq, const int32_t* q_uid, int k, int exclude_mode, int32_t* out_id, float* out_score,
+                     int32_t* out_cnt) {
+    if (nq > 0 && (!out_cnt || (k > 0 && (!out_id || !out_score)))) return fail(PK_ERR_ARG, "null output");
+    TRY(pk_fullscan_prepare(s, nq, q_uid, k, exclude_mode));
+    TRY(fullscan_execute(s));
+    return fullscan_fetch(s, out_id, out_score, out_cnt);
+}
+
 int pk_fullscan_local_keys(pk_store* s, int nq, const int32_t* q_uid, int k, int exclude_mode, uint64_t* d_keys) {
-    TRY(ensure_ready(s));
-    TRY(check_topk_args(s, nq, q_uid, k));
-    if (nq > 0 && k > 0 && !d_keys) return fail(PK_ERR_ARG, "null d_keys");
-    if (nq == 0 || k == 0) return PK_OK;
-    TRY(fullscan_device(s, nq, q_uid, k, exclude_mode));
-    CK(cudaMemcpyAsync(d_keys, s->d_keys_b.p, (size_t)nq * k * 8, cudaMemcpyDeviceToDevice, s->stream));
-    return PK_OK;
+    TRY(pk_fullscan_prepare(s, nq, q_uid, k, exclude_mode));
+    TRY(fullscan_execute(s));
+    return pk_fullscan_keys(s, d_keys);
 }
 
 int pk_merge_keys(pk_store* s, const uint64_t* d_keys, int n_lists, int nq, int k, int32_t* out_id, float* out_score,
@@ -1399,6 +1503,7 @@ int pk_merge_keys(pk_store* s, const uint64_t* d_keys, int n_lists, int nq, int 
     CK(cudaGetLastError());
     std::vector<uint64_t> keys((size_t)nq * k);
     CK(cudaMemcpyAsync(keys.data(), s->d_keys_c.p, keys.size() * 8, cudaMemcpyDeviceToHost, s->stream));
+    s->stat_d2h += (int64_t)keys.size() * 8;
     CK(cudaStreamSynchronize(s->stream));
     decode_keys(keys.data(), nq, k, out_id, out_score, out_cnt);
     return PK_OK;
@@ -1439,6 +1544,7 @@ int pk_sync(pk_store* s) {
     if (!s) return fail(PK_ERR_ARG, "null store");
     CK(cudaSetDevice(s->device));
     CK(cudaStreamSynchronize(s->stream));
+    TRY(collect_scan_time(s));
     return PK_OK;
 }
 
@@ -1456,6 +1562,8 @@ int64_t pk_stat(pk_store* s, int which) {
         case PK_STAT_SHARD_RECORD_BYTES:
             if (s->h_rec_off.size() < (size_t)s->n + 1) return 0;
             return (int64_t)(s->h_rec_off[s->shard_end] - s->h_rec_off[s->shard_begin]) * 16;
+        case PK_STAT_H2D_BYTES: return s->stat_h2d;
+        case PK_STAT_D2H_BYTES: return s->stat_d2h;
         default: return -1;
     }
 }

@@ -24,11 +24,11 @@ ABI_SYMBOLS = (
     "pk_last_error", "pk_abi_version", "pk_device_count", "pk_store_create", "pk_store_destroy",
     "pk_store_load_world", "pk_store_set_shard", "pk_set_normalizers", "pk_compute_idf", "pk_set_idf",
     "pk_idf_size", "pk_get_idf", "pk_set_adj_row", "pk_pair_similarity", "pk_pair_fields", "pk_pair_overlap",
-    "pk_fullscan_topk", "pk_recommend", "pk_candidates", "pk_fullscan_local_keys", "pk_merge_keys", "pk_sync",
+    "pk_fullscan_topk", "pk_fullscan_prepare", "pk_fullscan_execute", "pk_fullscan_fetch", "pk_fullscan_keys", "pk_recommend", "pk_candidates", "pk_fullscan_local_keys", "pk_merge_keys", "pk_sync",
     "pk_stream", "pk_stat",
 )
 STAT_KERNEL_LAUNCHES, STAT_PAIRS_SCORED, STAT_STORE_BYTES, STAT_SCAN_KERNEL_NS, STAT_SCAN_LAUNCHES, STAT_GROUPS, \
-    STAT_SHARD_RECORD_BYTES = range(7)
+    STAT_SHARD_RECORD_BYTES, STAT_H2D_BYTES, STAT_D2H_BYTES = range(9)
 
 _lib = None
 
@@ -173,6 +173,22 @@ class DeviceRecommender:
         _check(self.lib, self.lib.pk_fullscan_topk(self.h, len(q), ptr(q, i32p), int(k), int(exclude_mode),
                                                    ptr(ids, i32p), ptr(sc, f32p), ptr(cnt, i32p)))
         return ids, sc, cnt
+
+    def fullscan_prepare(self, q, k, exclude_mode=EXCLUDE_SELF_AND_ADJ):
+        q = np.ascontiguousarray(q, np.int32)
+        self._job_shape = (len(q), k)
+        _check(self.lib, self.lib.pk_fullscan_prepare(self.h, len(q), ptr(q, i32p), int(k), int(exclude_mode)))
+
+    def fullscan_execute(self):
+        _check(self.lib, self.lib.pk_fullscan_execute(self.h))
+
+    def fullscan_fetch(self):
+        ids, sc, cnt = self._alloc(*self._job_shape)
+        _check(self.lib, self.lib.pk_fullscan_fetch(self.h, ptr(ids, i32p), ptr(sc, f32p), ptr(cnt, i32p)))
+        return ids, sc, cnt
+
+    def fullscan_keys(self, d_keys_ptr: int):
+        _check(self.lib, self.lib.pk_fullscan_keys(self.h, C.c_void_p(d_keys_ptr)))
 
     def recommend(self, mode, q, k, limit=10000):
         q = np.ascontiguousarray(q, np.int32)

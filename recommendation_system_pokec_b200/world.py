@@ -118,6 +118,31 @@ class World:
         return (28 + 4 * np.diff(self.clubs_ptr) + 4 * np.diff(self.friends_ptr)
                 + 8 * filled + 8 * nnz).astype(np.int64)
 
+    def head(self, m: int) -> "World":
+        """The first `m` profiles (world order) with their adjacency rows; neighbours may point at users
+        outside the slice (they then have no profile, which every implementation skips)."""
+        m = int(min(m, self.n))
+        T = self.T
+        keep_rows = np.isin(self.adj_uid, self.uid[:m])
+        idx = np.flatnonzero(keep_rows)
+        lens = np.diff(self.adj_ptr)[idx]
+        adj_ptr = np.zeros(len(idx) + 1, np.int64)
+        np.cumsum(lens, out=adj_ptr[1:])
+        if len(idx):
+            take = np.concatenate([np.arange(self.adj_ptr[i], self.adj_ptr[i + 1]) for i in idx]) if len(idx) < 64 else \
+                np.repeat(self.adj_ptr[idx] - adj_ptr[:-1], lens) + np.arange(adj_ptr[-1])
+        else:
+            take = np.zeros(0, np.int64)
+        w = World(text_columns=list(self.text_columns), uid=self.uid[:m], pub=self.pub[:m], comp=self.comp[:m],
+                  gender=self.gender[:m], age=self.age[:m], region=self.region[:m],
+                  clubs_ptr=self.clubs_ptr[:m + 1], clubs=self.clubs[:self.clubs_ptr[m]],
+                  friends_ptr=self.friends_ptr[:m + 1], friends=self.friends[:self.friends_ptr[m]],
+                  tok_ptr=self.tok_ptr[:m * T + 1], tok_id=self.tok_id[:self.tok_ptr[m * T]],
+                  tok_tf=self.tok_tf[:self.tok_ptr[m * T]], adj_uid=self.adj_uid[idx], adj_ptr=adj_ptr,
+                  adj=self.adj[take], norm_mean=self.norm_mean, norm_sd=self.norm_sd, norm_has=self.norm_has)
+        w.meta = dict(self.meta, head_of=self.n, n=m)
+        return w
+
     def save(self, path):
         d = {k: getattr(self, k) for k in self._DTYPES}
         d["text_columns"] = np.array(self.text_columns)
