@@ -18,10 +18,17 @@ from recommendation_system_pokec_b200.world import World
 HERE = os.path.dirname(os.path.abspath(__file__))
 PORT_SO = os.path.join(HERE, "libpokec_oracle.so")
 REF_SO = os.path.join(HERE, "_ref", "libpokec_ref.so")
+# the CUDA-backed drop-in `Recommender` behind the same ref_* driver (dropin/build_dropin.py); it is the
+# PRODUCT under test, loaded through this front-end only because it shares the driver's entry points
+DROPIN_SO = os.path.join(os.path.dirname(HERE), "dropin", "_build", "libpokec_dropin.so")
 
 
 def reference_available() -> bool:
     return os.path.exists(REF_SO)
+
+
+def dropin_available() -> bool:
+    return os.path.exists(DROPIN_SO)
 
 
 def ensure_built():
@@ -31,12 +38,15 @@ def ensure_built():
 
 class CpuOracle:
     def __init__(self, world: World, kind: str = "port", compute_idf: bool = True):
-        assert kind in ("port", "reference")
+        assert kind in ("port", "reference", "dropin")
+        self.dropin = kind == "dropin"
+        if self.dropin:
+            kind = "reference"          # same driver, same entry points
         self.kind = kind
         self.world = world
         self.p = "orc_" if kind == "port" else "ref_"
-        path = PORT_SO if kind == "port" else REF_SO
-        if not os.path.exists(path):
+        path = DROPIN_SO if self.dropin else (PORT_SO if kind == "port" else REF_SO)
+        if not os.path.exists(path) and not self.dropin:
             ensure_built()
         self.lib = C.CDLL(path)
         self._pw = make_pk_world(world)

@@ -8,7 +8,9 @@
 // the resulting library.
 #include "recommender.h"      // reference header, from /root/reference/include
 #include "user_profile.h"
+#ifndef PK_DROPIN_BUILD
 #include "utils.h"
+#endif
 #include "tfidf_index.h"
 
 #include "pokec_world.h"
@@ -290,6 +292,7 @@ int ref_fullscan(void* hv, int nq, const int32_t* q, int k, int exclude_mode, in
     return 0;
 }
 
+#ifndef PK_DROPIN_BUILD   // utils.cpp is outside the replaced path; the drop-in build does not link it
 // compute_column_normalizers (src/utils.cpp:155-240), seed 12345 inside the reference
 int ref_column_normalizers(void* hv, int sample_size, int comps_per_user, float* mean, float* sd) {
     auto* h = (RefHandle*)hv;
@@ -308,6 +311,7 @@ int ref_column_normalizers(void* hv, int sample_size, int comps_per_user, float*
     }
     return 0;
 }
+#endif
 
 // mutate one adjacency row behind the live Recommender (what src/test.cpp:59-73 does)
 int ref_set_adj_row(void* hv, int uid, int n, const int32_t* nb) {

@@ -1398,6 +1398,18 @@ int pk_get_idf(pk_store* s, int col, int32_t* token, float* idf, int32_t* df, in
 int pk_set_adj_row(pk_store* s, int32_t uid, const int32_t* nb, int64_t n) {
     if (!s || n < 0 || (n > 0 && !nb)) return fail(PK_ERR_ARG, "bad argument");
     if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
+    // a row equal to the loaded one needs no override (the drop-in re-sends the rows a query touches)
+    auto it = s->adj_row.find(uid);
+    if (it != s->adj_row.end()) {
+        const int64_t b = s->adj_ptr[it->second], e = s->adj_ptr[it->second + 1];
+        if (e - b == n && (n == 0 || memcmp(s->adj.data() + b, nb, (size_t)n * 4) == 0)) {
+            s->adj_override.erase(uid);
+            return PK_OK;
+        }
+    } else if (n == 0) {
+        s->adj_override.erase(uid);   // no row and an empty row enumerate the same (no) candidates
+        return PK_OK;
+    }
     s->adj_override[uid].assign(nb, nb + n);
     return PK_OK;
 }
