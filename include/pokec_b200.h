@@ -163,9 +163,22 @@ enum {
     PK_STAT_GROUPS = 5,            /* query groups of the last scoring call */
     PK_STAT_SHARD_RECORD_BYTES = 6,/* bytes of the packed records inside the candidate shard */
     PK_STAT_H2D_BYTES = 7,         /* host-to-device bytes copied by this store since creation */
-    PK_STAT_D2H_BYTES = 8          /* device-to-host result bytes copied since creation */
+    PK_STAT_D2H_BYTES = 8,         /* device-to-host result bytes copied since creation */
+    PK_STAT_PREFILTER = 9,         /* 1 when the prepared full scan runs the fp32 pre-filter + exact re-score pipeline */
+    PK_STAT_FALLBACK_QUERIES = 10, /* queries of the last fetched full scan whose shortlist was not provably complete
+                                      (they were re-run by the exact scan on every pair) */
+    PK_STAT_RESCORE_NS = 11,       /* device time of the exact re-score + fallback kernels of the last full scan */
+    PK_STAT_SHARD_LEAN_BYTES = 12, /* bytes of the lean fp32 records inside the candidate shard */
+    PK_STAT_SHORTLIST = 13,        /* shortlist length Ks of the prepared full scan (0 = no pre-filter) */
+    PK_STAT_MARGIN_E9 = 14         /* the pre-filter's error bound on a FAS value, times 1e9 */
 };
 int64_t pk_stat(pk_store* s, int which);
+
+/* Test hook of the two-stage full scan: the pre-filter's fp32 scores and the exact kernel's scores of
+ * nq <= 32 queries against the store rows [row_begin,row_end), both as [row][nq].  Their difference must
+ * stay below the bound PK_STAT_MARGIN_E9 reports; the parity tests assert it. */
+int pk_debug_prefilter(pk_store* s, int nq, const int32_t* q_uid, int64_t row_begin, int64_t row_end, float* out_approx,
+                       float* out_exact);
 
 #ifdef __cplusplus
 }

@@ -22,6 +22,7 @@
 #include "pk_layout.h"
 #include "pk_build.cuh"
 #include "pk_scan.cuh"
+#include "pk_prefilter.cuh"
 #include "pk_clubs.cuh"
 
 using namespace pk;
@@ -109,6 +110,16 @@ struct FullscanJob {
     DevBuf<uint8_t> arena;
     DevBuf<int32_t> excl, q_slot0, q_nl, q_lane;
     DevBuf<uint64_t> keys_a, keys_b;
+    // two-stage scan (pk_prefilter.cuh): pre-filter shortlists -> exact re-score -> fallback for unproven queries
+    bool lean = false;
+    int Ks = 0;
+    size_t n_pre = 0;                         // pre-filter work items
+    size_t n_rr_sm = 0, n_rr_gl = 0;          // exact re-score items (list mode over the shortlists)
+    uint32_t max_smem_lean = 0;
+    int64_t rr_pairs = 0;
+    DevBuf<WorkItem> pre_items, rr_items;
+    DevBuf<uint64_t> keys_pre, keys_short, keys_rr;
+    DevBuf<int32_t> q_group, q_flag, q_flag0, group_flag, group_flag0, short_rows, rr_slot0, rr_nl, pre_slot0, pre_nl;
 };
 
 struct pk_store {
@@ -161,6 +172,17 @@ struct pk_store {
     std::vector<uint64_t> h_rec_off;
     uint64_t store_u4 = 0;
     int64_t shard_begin = 0, shard_end = 0;
+    // lean fp32 records of the pre-filter
+    bool lean_dirty = true, tf_negative = false;
+    DevBuf<uint4> d_lrec;
+    DevBuf<uint64_t> d_lrec_off;
+    uint64_t lean_u4 = 0;
+    DevBuf<LeanNorm> d_lnorm;
+    DevBuf<float> d_tab_comp32, d_tab_age32;
+    float margin = 0.f;
+    int64_t stat_fallback = 0, stat_prefilter_ns = 0, stat_rescore_ns = 0;
+    bool rescore_time_pending = false;
+    cudaEvent_t ev2 = nullptr, ev3 = nullptr;
 
     // ---- per-call scratch (grow-only) -------------------------------------------------------------
     DevBuf<GroupDesc> d_groups;
@@ -345,6 +367,41 @@ int rebuild_norm(pk_store* s) {
                 tab[(size_t)c * dim + q] = h_sigmoid(z(f, (double)amin / (double)amax));
             }
         TRY(upload(s, which ? s->d_tab_age : s->d_tab_comp, tab));
+        std::vector<float> tab32(tab.begin(), tab.end());
+        TRY(upload(s, which ? s->d_tab_age32 : s->d_tab_comp32, tab32));
+        CK(cudaStreamSynchronize(s->stream));
+    }
+    {   // fp32 constants of the pre-filter and the bound on its error (pk_prefilter.cuh)
+        std::vector<LeanNorm> Lv(1);
+        LeanNorm& L = Lv[0];
+        memset(&L, 0, sizeof(L));
+        const double log2e = 1.4426950408889634;
+        double worst = 1.5;                 // default z = 6(s - 0.5): |d sigma / d ln s| <= 0.25 * 6
+        for (int f = 0; f < nf; ++f) {
+            double a, b;
+            if (N.use_norm[f]) {
+                a = -log2e / N.sd[f]; b = log2e * N.mean[f] / N.sd[f];
+                worst = std::max(worst, 0.25 + 0.25 * std::fabs(N.mean[f]) / N.sd[f]);
+            } else { a = -6.0 * log2e; b = 3.0 * log2e; }
+            L.fld[f] = make_float4((float)a, (float)b, (float)N.sig0[f], (float)N.sig1[f]);
+        }
+        for (int i = 0; i < 64; ++i) L.region[i] = (float)N.region[i];
+        for (int j = 0; j < kMaxT / 8; ++j)
+            for (int bits = 0; bits < 256; ++bits) {
+                double acc = 0.0;
+                for (int i = 0; i < 8; ++i)
+                    if (((bits >> i) & 1) && 8 * j + i < T) acc += N.sig0[kNumFixed + 8 * j + i];
+                L.lut[j][bits] = (float)acc;
+            }
+        L.inv_total = (float)(1.0 / (double)nf);
+        // per-field error: relative error of an fp32 cosine (<= 64 products) times the sensitivity above, plus the
+        // ex2/rcp approximations; the mean over fields cannot exceed the worst field; dFAS/dS <= 2; safety factor 2
+        const double rel_s = 4.2e-6;
+        L.margin = (float)(2.0 * 2.0 * (worst * rel_s + 5e-6));
+        L.dim_comp = N.dim_comp; L.dim_age = N.dim_age;
+        s->margin = L.margin;
+        TRY(s->d_lnorm.reserve(1));
+        CK(cudaMemcpyAsync(s->d_lnorm.p, &L, sizeof(L), cudaMemcpyHostToDevice, s->stream));
         CK(cudaStreamSynchronize(s->stream));
     }
     TRY(s->d_norm.reserve(1));
@@ -382,6 +439,27 @@ int rebuild_store(pk_store* s) {
     CK(cudaStreamSynchronize(s->stream));
     CK(cudaGetLastError());
     s->store_dirty = false;
+    s->lean_dirty = true;
+    return PK_OK;
+}
+
+// lean fp32 records of the pre-filter, derived from the packed store
+int rebuild_lean(pk_store* s) {
+    if (!s->lean_dirty) return PK_OK;
+    const int n = s->n;
+    std::vector<uint64_t> off((size_t)n + 1, 0);
+    for (int r = 0; r < n; ++r) off[r + 1] = off[r] + lean_record_u4(s->h_ncl[r], s->h_nfr[r], s->h_ntok[r]);
+    s->lean_u4 = off[n];
+    TRY(s->d_lrec.reserve(std::max<uint64_t>(s->lean_u4, 1)));
+    TRY(upload(s, s->d_lrec_off, off));
+    if (n > 0) {
+        const unsigned blocks = (unsigned)(((int64_t)n * 32 + 255) / 256);
+        lean_pack_kernel<<<blocks, 256, 0, s->stream>>>(n, s->d_rec.p, s->d_rec_off.p, s->d_lrec_off.p, s->d_lrec.p);
+        ++s->stat_launches;
+    }
+    CK(cudaStreamSynchronize(s->stream));
+    CK(cudaGetLastError());
+    s->lean_dirty = false;
     return PK_OK;
 }
 
@@ -394,6 +472,8 @@ int ensure_ready(pk_store* s) {
     return PK_OK;
 }
 
+uint32_t align16(uint32_t x) { return (x + 15u) & ~15u; }
+
 // ---- group planning --------------------------------------------------------------------------------
 
 struct Plan {
@@ -401,12 +481,12 @@ struct Plan {
     std::vector<int32_t> excl;    // concatenated exclusion ids
     uint64_t arena_bytes = 0;
     uint32_t max_smem_arena = 0;  // over groups that fit shared memory
+    uint32_t max_smem_lean = 0;   // same for the pre-filter's tables
 };
 
-uint32_t align16(uint32_t x) { return (x + 15u) & ~15u; }
-
-// lays out the tables of a group whose members are rows[0..n_lanes); excl_n = exclusion ids per lane
-void layout_group(pk_store* s, GroupDesc& g, const uint32_t* excl_n) {
+// lays out the tables of a group whose members are rows[0..n_lanes); excl_n = exclusion ids per lane.
+// with_lean adds the fp32 tables of the pre-filter in front of the block (pk_layout.h, GroupDesc).
+void layout_group(pk_store* s, GroupDesc& g, const uint32_t* excl_n, bool with_lean = false) {
     uint64_t ncl = 0, nfr = 0, ntok = 0, nex = 0;
     for (int l = 0; l < g.n_lanes; ++l) {
         const int r = g.row[l];
@@ -416,11 +496,20 @@ void layout_group(pk_store* s, GroupDesc& g, const uint32_t* excl_n) {
     }
     g.log_sc = log2_table(ncl); g.log_sf = log2_table(nfr); g.log_sa = log2_table(nex); g.log_st = log2_table(ntok);
     uint32_t off = 0;
-    g.off_nq = off; off += align16((uint32_t)s->T * 32u * 8u);
+    g.off_text2 = g.off_base = g.off_vals32 = 0;
+    if (with_lean) {
+        g.off_text2 = off; off += (8u << g.log_st);
+        g.off_base = off; off += (4u << g.log_st);
+        g.off_vals32 = off; off += align16((uint32_t)ntok * 4u);
+    }
+    g.exact_begin = off;
     g.off_clubs = off; off += (8u << g.log_sc);
     g.off_friends = off; off += (8u << g.log_sf);
     g.off_adj = off; off += (8u << g.log_sa);
-    g.off_text = align16(off); off = g.off_text + (16u << g.log_st);
+    off = align16(off);
+    g.lean_end = with_lean ? off : 0u;
+    g.off_nq = off; off += align16((uint32_t)s->T * 32u * 8u);
+    g.off_text = off; off += (16u << g.log_st);
     g.off_vals = off; off += align16((uint32_t)ntok * 8u);
     g.n_vals = (uint32_t)ntok;
     g.arena_bytes = align16(off);
@@ -468,7 +557,6 @@ int launch_scan_t(pk_store* s, ScanParams P, const WorkItem* d_items, size_t n_i
         kern<<<(unsigned)n_items, kScanThreads, smem_bytes, s->stream>>>(P);
     }
     CK(cudaGetLastError());
-    ++s->stat_scan_launches;
     ++s->stat_launches;
     return PK_OK;
 }
@@ -486,6 +574,18 @@ int launch_scan(pk_store* s, ScanParams P, const WorkItem* d_items, size_t n_sm,
     TRY((launch_scan_t<EPI, FIELDS>(s, P, d_items + n_sm, n_gl, false, fixed)));
     CK(cudaEventRecord(s->ev1, s->stream));
     s->scan_time_pending = true;
+    s->stat_scan_launches += (n_sm > 0) + (n_gl > 0);
+    return PK_OK;
+}
+
+// the same two launches without the scan-time events (re-score / fallback passes of the two-stage scan)
+template <int EPI, bool FIELDS>
+int launch_scan_plain(pk_store* s, ScanParams P, const WorkItem* d_items, size_t n_sm, size_t n_gl, uint32_t max_smem_arena) {
+    const uint32_t fixed = scan_fixed_smem(EPI == EPI_TOPK ? P.Kp : 0);
+    P.smem_arena_bytes = max_smem_arena;
+    TRY((launch_scan_t<EPI, FIELDS>(s, P, d_items, n_sm, true, max_smem_arena + fixed)));
+    P.smem_arena_bytes = 0;
+    TRY((launch_scan_t<EPI, FIELDS>(s, P, d_items + n_sm, n_gl, false, fixed)));
     return PK_OK;
 }
 
@@ -495,6 +595,11 @@ int collect_scan_time(pk_store* s) {
     CK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
     s->stat_scan_ns += (int64_t)((double)ms * 1e6);
     s->scan_time_pending = false;
+    if (s->rescore_time_pending) {
+        CK(cudaEventElapsedTime(&ms, s->ev2, s->ev3));
+        s->stat_rescore_ns = (int64_t)((double)ms * 1e6);
+        s->rescore_time_pending = false;
+    }
     return PK_OK;
 }
 
@@ -530,11 +635,22 @@ ScanParams base_scan_params(pk_store* s, int K) {
     return P;
 }
 
-void finish_group(pk_store* s, Plan& plan, GroupDesc& g, const uint32_t* excl_n, int Kp) {
-    layout_group(s, g, excl_n);
+uint32_t lean_fixed_smem(int Ks) {
+    const uint32_t norm = (uint32_t)((sizeof(LeanNorm) + 15) & ~15u);
+    return norm + 32u * Ks * 8u + 32u * 8u + 32u * 4u + 16u + (uint32_t)kPreWarps * 32u * 16u;
+}
+
+void finish_group(pk_store* s, Plan& plan, GroupDesc& g, const uint32_t* excl_n, int Kp, bool with_lean = false, int Ks = 0) {
+    layout_group(s, g, excl_n, with_lean);
     const uint32_t budget = (uint32_t)s->max_smem - scan_fixed_smem(Kp) - 256u;
-    g.in_smem = g.arena_bytes <= budget;
-    if (g.in_smem) plan.max_smem_arena = std::max(plan.max_smem_arena, g.arena_bytes);
+    g.in_smem = (g.arena_bytes - g.exact_begin) <= budget;
+    if (g.in_smem) plan.max_smem_arena = std::max(plan.max_smem_arena, g.arena_bytes - g.exact_begin);
+    g.lean_in_smem = 0;
+    if (with_lean) {
+        const uint32_t lbudget = (uint32_t)s->max_smem - lean_fixed_smem(Ks) - 256u;
+        g.lean_in_smem = g.lean_end <= lbudget;
+        if (g.lean_in_smem) plan.max_smem_lean = std::max(plan.max_smem_lean, g.lean_end);
+    }
     plan.groups.push_back(g);
 }
 
@@ -565,6 +681,20 @@ int check_topk_args(pk_store* s, int nq, const int32_t* q_uid, int k) {
 // ---- full scan ---------------------------------------------------------------------------------------
 // prepare: host planning + upload (queries -> groups -> work items); execute: arena clear, group_prep,
 // scan, merge -- all asynchronous on the store's stream, device-resident inputs only; fetch: D2H + decode.
+bool lean_usable(pk_store* s, int K, int* Ks_out) {
+    const char* e = getenv("POKEC_B200_NO_PREFILTER");
+    if (e && e[0] == '1') return false;
+    if (s->tf_negative) return false;
+    for (int t = 0; t < s->T; ++t)
+        if (s->col_state[t] == 2)
+            for (float v : s->custom_idf[t]) if (!(v >= 0.0f)) return false;   // negative weights break the error bound
+    int Ks = (2 * K + 28 + 31) / 32 * 32;
+    if (Ks > kMaxK) Ks = kMaxK;
+    if (Ks < K + 16) return false;
+    *Ks_out = Ks;
+    return true;
+}
+
 int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclude_mode) {
     FullscanJob& J = s->job;
     J.valid = false;
@@ -572,13 +702,17 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
     const int K = std::max(k, 1), Kp = (K + 31) / 32 * 32;
     J.K = K; J.Kp = Kp;
     J.n_groups = 0; J.n_sm = J.n_gl = 0; J.pairs = 0;
+    J.lean = false; J.Ks = 0; J.n_pre = 0; J.n_rr_sm = J.n_rr_gl = 0; J.rr_pairs = 0;
     TRY(J.keys_b.reserve((size_t)std::max(nq, 1) * K));
     const int64_t n_cand = s->shard_end - s->shard_begin;
     if (nq == 0 || k == 0 || n_cand <= 0) { J.valid = true; return PK_OK; }
+    int Ks = 0;
+    const bool lean = lean_usable(s, K, &Ks);
+    if (lean) TRY(rebuild_lean(s));
 
     // group the queries that have a profile, in caller order
     Plan plan;
-    std::vector<int32_t> q_slot0(nq, 0), q_nl(nq, 0), q_lane(nq, 0);
+    std::vector<int32_t> q_slot0(nq, 0), q_nl(nq, 0), q_lane(nq, 0), q_group(nq, -1);
     GroupDesc g;
     std::vector<uint32_t> excl_n(32, 0);
     auto reset = [&]() {
@@ -589,10 +723,11 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
     };
     reset();
     const uint32_t budget = (uint32_t)s->max_smem - scan_fixed_smem(Kp) - 256u;
+    const uint32_t lbudget = lean ? (uint32_t)s->max_smem - lean_fixed_smem(Ks) - 256u : 0u;
     auto close_group = [&]() {
         if (g.n_lanes == 0) return;
         for (int l = g.n_lanes; l < 32; ++l) g.adj_begin[l + 1] = g.adj_begin[g.n_lanes];
-        finish_group(s, plan, g, excl_n.data(), Kp);
+        finish_group(s, plan, g, excl_n.data(), Kp, lean, Ks);
         reset();
     };
     for (int q = 0; q < nq; ++q) {
@@ -601,21 +736,21 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
         const int32_t *ab = nullptr, *ae = nullptr;
         uint32_t nex = 0;
         if (exclude_mode >= PK_EXCLUDE_SELF_AND_ADJ && s->adj_of(q_uid[q], &ab, &ae)) nex = (uint32_t)(ae - ab);
-        if (g.n_lanes > 0) {   // would adding this query overflow the shared-memory budget?
+        if (g.n_lanes > 0) {   // would adding this query overflow a shared-memory budget?
             GroupDesc t = g;
             t.row[t.n_lanes] = r;
             std::vector<uint32_t> en = excl_n;
             en[t.n_lanes] = nex;
             ++t.n_lanes;
-            layout_group(s, t, en.data());
-            if (t.arena_bytes > budget) close_group();
+            layout_group(s, t, en.data(), lean);
+            if (t.arena_bytes - t.exact_begin > budget || (lean && t.lean_end > lbudget)) close_group();
         }
         const int l = g.n_lanes;
         g.row[l] = r; g.qidx[l] = q; excl_n[l] = nex;
         if (nex) plan.excl.insert(plan.excl.end(), ab, ae);
         g.adj_begin[l + 1] = (int32_t)plan.excl.size();
         q_lane[q] = l;
-        q_slot0[q] = (int32_t)plan.groups.size();   // group index for now
+        q_group[q] = (int32_t)plan.groups.size();
         q_nl[q] = 1;
         ++g.n_lanes;
         if (g.n_lanes == 32) close_group();
@@ -632,12 +767,14 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
     }
     J.arena_bytes = off;
     J.max_smem_arena = plan.max_smem_arena;
+    J.max_smem_lean = plan.max_smem_lean;
     J.with_excl = exclude_mode >= PK_EXCLUDE_SELF_AND_ADJ;
     TRY(J.arena.reserve(std::max<uint64_t>(off, 16)));
     TRY(upload(s, J.groups, plan.groups));
     if (J.with_excl) TRY(upload(s, J.excl, plan.excl));
 
-    // work items: every group scans the whole shard, split into slices so that the grid fills the GPU
+    // exact work items: every group scans the whole shard, split into slices so that the grid fills the GPU
+    // (the whole scan without the pre-filter; with it, only the CTAs of groups that failed the shortlist check run)
     int sm_count = 148;
     cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, s->device);
     int64_t splits = (int64_t)(sm_count * 6 + ng - 1) / ng;
@@ -659,7 +796,7 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
     }
     for (int q = 0; q < nq; ++q) {
         if (q_nl[q] == 0) continue;
-        q_slot0[q] = g_slot0[q_slot0[q]];
+        q_slot0[q] = g_slot0[q_group[q]];
         q_nl[q] = (int32_t)splits;
     }
     TRY(J.keys_a.reserve(items.size() * 32 * (size_t)Kp));
@@ -667,15 +804,94 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
     TRY(upload(s, J.q_slot0, q_slot0));
     TRY(upload(s, J.q_nl, q_nl));
     TRY(upload(s, J.q_lane, q_lane));
+
+    if (lean) {
+        J.lean = true; J.Ks = Ks;
+        // pre-filter items (same slicing), groups whose lean tables do not fit shared memory go straight to the
+        // exact full scan (flag preset)
+        std::vector<WorkItem> pre;
+        std::vector<int32_t> pre_slot0(nq, 0), pre_nl(nq, 0), gflag0(ng, 0), qflag0(nq, 0), gp0(ng, 0);
+        for (int gi = 0; gi < ng; ++gi) {
+            gp0[gi] = (int32_t)pre.size();
+            if (!plan.groups[gi].lean_in_smem) { gflag0[gi] = 1; continue; }
+            for (int64_t sp = 0; sp < splits; ++sp) {
+                WorkItem it = items[(size_t)g_slot0[gi] + sp];
+                it.out_slot = (int32_t)pre.size();
+                pre.push_back(it);
+            }
+        }
+        // exact re-score items: the 32 x Ks shortlist rows of each group, in list mode
+        const int rr_splits = 4;
+        std::vector<WorkItem> rr;
+        std::vector<int32_t> rr_slot0(nq, 0), rr_nl(nq, 0), gr0(ng, 0);
+        for (int gi = 0; gi < ng; ++gi) {
+            gr0[gi] = (int32_t)rr.size();
+            if (gflag0[gi]) continue;
+            const int64_t base = (int64_t)gi * 32 * Ks, len = (int64_t)32 * Ks;
+            for (int sp = 0; sp < rr_splits; ++sp) {
+                WorkItem it;
+                it.group = gi;
+                it.cand_begin = (int32_t)(base + len * sp / rr_splits);
+                it.cand_end = (int32_t)(base + len * (sp + 1) / rr_splits);
+                it.out_slot = (int32_t)rr.size();
+                rr.push_back(it);
+            }
+            J.rr_pairs += (int64_t)plan.groups[gi].n_lanes * len;
+        }
+        for (int q = 0; q < nq; ++q) {
+            const int gi = q_group[q];
+            if (gi < 0) continue;
+            if (gflag0[gi]) { qflag0[q] = 1; continue; }
+            pre_slot0[q] = gp0[gi]; pre_nl[q] = (int32_t)splits;
+            rr_slot0[q] = gr0[gi]; rr_nl[q] = rr_splits;
+        }
+        J.n_pre = pre.size();
+        TRY(upload(s, J.pre_items, pre));
+        TRY(upload_items(s, plan, rr, J.rr_items, &J.n_rr_sm, &J.n_rr_gl));
+        TRY(upload(s, J.pre_slot0, pre_slot0)); TRY(upload(s, J.pre_nl, pre_nl));
+        TRY(upload(s, J.rr_slot0, rr_slot0)); TRY(upload(s, J.rr_nl, rr_nl));
+        TRY(upload(s, J.q_group, q_group));
+        TRY(upload(s, J.q_flag0, qflag0)); TRY(upload(s, J.group_flag0, gflag0));
+        TRY(J.q_flag.reserve(nq)); TRY(J.group_flag.reserve(ng));
+        TRY(J.keys_pre.reserve(std::max<size_t>(pre.size(), 1) * 32 * (size_t)Ks));
+        TRY(J.keys_short.reserve((size_t)nq * Ks));
+        TRY(J.keys_rr.reserve(std::max<size_t>(rr.size(), 1) * 32 * (size_t)Kp));
+        TRY(J.short_rows.reserve((size_t)ng * 32 * Ks));
+    }
     CK(cudaStreamSynchronize(s->stream));
     J.valid = true;
     return PK_OK;
 }
 
+int launch_prefilter(pk_store* s, const PreParams& P, size_t n_items, uint32_t lean_arena, int Ks, bool store) {
+    if (n_items == 0) return PK_OK;
+    const uint32_t smem = lean_arena + lean_fixed_smem(store ? 0 : Ks);
+    if (store) {
+        auto kern = fas_prefilter_kernel<true>;
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<(unsigned)n_items, kPreThreads, smem, s->stream>>>(P);
+    } else {
+        auto kern = fas_prefilter_kernel<false>;
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<(unsigned)n_items, kPreThreads, smem, s->stream>>>(P);
+    }
+    CK(cudaGetLastError());
+    ++s->stat_launches;
+    return PK_OK;
+}
+
+PreParams base_pre_params(pk_store* s) {
+    PreParams P;
+    memset(&P, 0, sizeof(P));
+    P.lrec = s->d_lrec.p; P.lrec_off = s->d_lrec_off.p; P.ln = s->d_lnorm.p;
+    P.tab_comp = s->d_tab_comp32.p; P.tab_age = s->d_tab_age32.p;
+    return P;
+}
+
 int fullscan_execute(pk_store* s) {
     FullscanJob& J = s->job;
     if (!J.valid) return fail(PK_ERR_STATE, "pk_fullscan_prepare has not been called");
-    s->stat_scan_ns = 0; s->stat_scan_launches = 0;
+    s->stat_scan_ns = 0; s->stat_scan_launches = 0; s->stat_prefilter_ns = 0;
     s->stat_pairs = J.pairs; s->stat_groups = J.n_groups;
     CK(cudaMemsetAsync(J.keys_b.p, 0, (size_t)std::max(J.nq, 1) * J.K * 8, s->stream));
     if (J.n_groups == 0) return PK_OK;
@@ -689,12 +905,59 @@ int fullscan_execute(pk_store* s) {
     ScanParams P = base_scan_params(s, J.K);
     P.groups = J.groups.p; P.arena = J.arena.p;
     P.exclude_mode = J.exclude;
-    P.out_keys = J.keys_a.p;
-    TRY((launch_scan<EPI_TOPK, false>(s, P, J.items.p, J.n_sm, J.n_gl, J.max_smem_arena)));
     MergeParams M;
     memset(&M, 0, sizeof(M));
-    M.keys = J.keys_a.p; M.slot0 = J.q_slot0.p; M.n_lists_q = J.q_nl.p; M.lane = J.q_lane.p;
-    M.nq = J.nq; M.K = J.K; M.stride_k = J.Kp; M.out_keys = J.keys_b.p;
+    M.lane = J.q_lane.p; M.nq = J.nq; M.K = J.K; M.out_keys = J.keys_b.p;
+
+    if (!J.lean) {   // exact arithmetic on every pair
+        P.out_keys = J.keys_a.p;
+        TRY((launch_scan<EPI_TOPK, false>(s, P, J.items.p, J.n_sm, J.n_gl, J.max_smem_arena)));
+        M.keys = J.keys_a.p; M.slot0 = J.q_slot0.p; M.n_lists_q = J.q_nl.p; M.stride_k = J.Kp;
+        merge_topk_kernel<<<J.nq, 128, 0, s->stream>>>(M);
+        ++s->stat_launches;
+        CK(cudaGetLastError());
+        return PK_OK;
+    }
+
+    // 1. pre-filter: fp32 scores of every pair, Ks best per query and slice
+    const int Ks = J.Ks;
+    CK(cudaMemcpyAsync(J.q_flag.p, J.q_flag0.p, (size_t)J.nq * 4, cudaMemcpyDeviceToDevice, s->stream));
+    CK(cudaMemcpyAsync(J.group_flag.p, J.group_flag0.p, (size_t)J.n_groups * 4, cudaMemcpyDeviceToDevice, s->stream));
+    CK(cudaMemsetAsync(J.short_rows.p, 0xFF, (size_t)J.n_groups * 32 * Ks * 4, s->stream));
+    CK(cudaMemsetAsync(J.keys_short.p, 0, (size_t)J.nq * Ks * 8, s->stream));
+    PreParams Q = base_pre_params(s);
+    Q.groups = J.groups.p; Q.items = J.pre_items.p; Q.arena = J.arena.p;
+    Q.Ks = Ks; Q.exclude_mode = J.exclude; Q.smem_arena_bytes = J.max_smem_lean; Q.out_keys = J.keys_pre.p;
+    CK(cudaEventRecord(s->ev0, s->stream));
+    TRY(launch_prefilter(s, Q, J.n_pre, J.max_smem_lean, Ks, false));
+    CK(cudaEventRecord(s->ev1, s->stream));
+    if (J.n_pre) { s->scan_time_pending = true; ++s->stat_scan_launches; }
+    // 2. merge the slices' shortlists, prove them complete (or flag the query), emit the rows to re-score
+    MergeParams MS;
+    memset(&MS, 0, sizeof(MS));
+    MS.keys = J.keys_pre.p; MS.slot0 = J.pre_slot0.p; MS.n_lists_q = J.pre_nl.p; MS.lane = J.q_lane.p;
+    MS.nq = J.nq; MS.K = Ks; MS.stride_k = Ks; MS.out_keys = J.keys_short.p;
+    merge_topk_kernel<<<J.nq, 128, 0, s->stream>>>(MS);
+    ++s->stat_launches;
+    CheckParams C;
+    C.short_keys = J.keys_short.p; C.q_group = J.q_group.p; C.q_lane = J.q_lane.p; C.cand_rows = J.short_rows.p;
+    C.q_flag = J.q_flag.p; C.group_flag = J.group_flag.p; C.nq = J.nq; C.K = J.K; C.Ks = Ks; C.margin = s->margin;
+    shortlist_check_kernel<<<J.nq, 64, 0, s->stream>>>(C);
+    ++s->stat_launches;
+    CK(cudaGetLastError());
+    // 3. exact arithmetic on the shortlists; 4. exact full scan for the groups with a flagged query
+    CK(cudaEventRecord(s->ev2, s->stream));
+    ScanParams R = P;
+    R.cand_rows = J.short_rows.p; R.out_keys = J.keys_rr.p;
+    TRY((launch_scan_plain<EPI_TOPK, false>(s, R, J.rr_items.p, J.n_rr_sm, J.n_rr_gl, J.max_smem_arena)));
+    ScanParams F = P;
+    F.out_keys = J.keys_a.p; F.group_flag = J.group_flag.p;
+    TRY((launch_scan_plain<EPI_TOPK, false>(s, F, J.items.p, J.n_sm, J.n_gl, J.max_smem_arena)));
+    CK(cudaEventRecord(s->ev3, s->stream));
+    s->rescore_time_pending = true;
+    // 5. final merge: the re-scored shortlist, or the full exact scan where the shortlist was not proven
+    M.keys = J.keys_rr.p; M.slot0 = J.rr_slot0.p; M.n_lists_q = J.rr_nl.p; M.stride_k = J.Kp;
+    M.q_flag = J.q_flag.p; M.alt_keys = J.keys_a.p; M.alt_slot0 = J.q_slot0.p; M.alt_n_lists_q = J.q_nl.p; M.alt_stride_k = J.Kp;
     merge_topk_kernel<<<J.nq, 128, 0, s->stream>>>(M);
     ++s->stat_launches;
     CK(cudaGetLastError());
@@ -709,8 +972,15 @@ int fullscan_fetch(pk_store* s, int32_t* out_id, float* out_score, int32_t* out_
     std::vector<uint64_t> keys((size_t)J.nq * J.k);
     CK(cudaMemcpyAsync(keys.data(), J.keys_b.p, keys.size() * 8, cudaMemcpyDeviceToHost, s->stream));
     s->stat_d2h += (int64_t)keys.size() * 8;
+    std::vector<int32_t> flags;
+    if (J.lean && J.n_groups > 0) {
+        flags.resize((size_t)J.nq);
+        CK(cudaMemcpyAsync(flags.data(), J.q_flag.p, flags.size() * 4, cudaMemcpyDeviceToHost, s->stream));
+    }
     CK(cudaStreamSynchronize(s->stream));
     TRY(collect_scan_time(s));
+    s->stat_fallback = 0;
+    for (int32_t f : flags) s->stat_fallback += f != 0;
     decode_keys(keys.data(), J.nq, J.k, out_id, out_score, out_cnt);
     return PK_OK;
 }
@@ -1192,6 +1462,8 @@ int pk_store_create(int device, pk_store** out) {
     cudaError_t e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreate(&s->ev0);
     if (e == cudaSuccess) e = cudaEventCreate(&s->ev1);
+    if (e == cudaSuccess) e = cudaEventCreate(&s->ev2);
+    if (e == cudaSuccess) e = cudaEventCreate(&s->ev3);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&s->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
     if (e != cudaSuccess) { delete s; return fail(PK_ERR_CUDA, "store init: %s", cudaGetErrorString(e)); }
     *out = s;
@@ -1204,6 +1476,8 @@ void pk_store_destroy(pk_store* s) {
     if (s->stream) cudaStreamSynchronize(s->stream);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->ev2) cudaEventDestroy(s->ev2);
+    if (s->ev3) cudaEventDestroy(s->ev3);
     cudaStream_t st = s->stream;
     delete s;
     if (st) cudaStreamDestroy(st);
@@ -1223,13 +1497,14 @@ int pk_store_load_world(pk_store* s, const pk_world* w) {
     // cells sorted by token id (the reference's cells are hash maps: order-free); ids must fit 26 bits
     std::vector<int32_t> tid, ttf;
     const int32_t *tok_id = w->tok_id, *tok_tf = w->tok_tf;
-    bool sorted = true;
+    bool sorted = true, tf_negative = false;
     for (int64_t c = 0; c < (int64_t)n * T; ++c) {
         const int64_t b = w->tok_ptr[c], e = w->tok_ptr[c + 1];
         if (e < b) return fail(PK_ERR_ARG, "tok_ptr not monotone");
         for (int64_t j = b; j < e; ++j) {
             if ((uint32_t)tok_id[j] >= (1u << kTokBits)) return fail(PK_ERR_UNSUPPORTED, "token id %d outside [0, 2^26)", tok_id[j]);
             if (j > b && tok_id[j] <= tok_id[j - 1]) sorted = false;
+            if (w->tok_tf[j] < 0) tf_negative = true;
         }
     }
     if (!sorted) {
@@ -1247,6 +1522,7 @@ int pk_store_load_world(pk_store* s, const pk_world* w) {
         tok_id = tid.data(); tok_tf = ttf.data();
     }
     s->n = n; s->T = T; s->nnz = nnz;
+    s->tf_negative = tf_negative;
     s->uid.assign(w->uid, w->uid + n);
     s->uid_sorted.resize(n);
     for (int i = 0; i < n; ++i) s->uid_sorted[i] = {w->uid[i], i};
@@ -1552,6 +1828,51 @@ int pk_candidates(pk_store* s, int mode, int32_t uid, int limit, int32_t* out, i
     return PK_OK;
 }
 
+int pk_debug_prefilter(pk_store* s, int nq, const int32_t* q_uid, int64_t row_begin, int64_t row_end, float* out_approx,
+                       float* out_exact) {
+    TRY(ensure_ready(s));
+    if (nq < 1 || nq > 32 || !q_uid || !out_approx || !out_exact || row_begin < 0 || row_end > s->n || row_end < row_begin)
+        return fail(PK_ERR_ARG, "bad argument");
+    TRY(rebuild_lean(s));
+    Plan plan;
+    GroupDesc g = empty_group();
+    for (int q = 0; q < nq; ++q) {
+        const int r = s->row_of(q_uid[q]);
+        if (r < 0) return fail(PK_ERR_ARG, "uid %d has no profile", q_uid[q]);
+        g.row[q] = r; g.qidx[q] = q;
+    }
+    g.n_lanes = nq;
+    finish_group(s, plan, g, nullptr, 0, true, 0);
+    if (!plan.groups[0].lean_in_smem || !plan.groups[0].in_smem) return fail(PK_ERR_UNSUPPORTED, "group tables exceed shared memory");
+    const int64_t rows = row_end - row_begin;
+    if (rows == 0) return PK_OK;
+    TRY(upload_plan(s, plan, false));
+    WorkItem it;
+    it.group = 0; it.cand_begin = (int32_t)row_begin; it.cand_end = (int32_t)row_end; it.out_slot = 0;
+    std::vector<WorkItem> items(1, it);
+    TRY(s->d_f32a.reserve((size_t)rows * 32));
+    std::vector<float> tmp((size_t)rows * 32);
+    for (int pass = 0; pass < 2; ++pass) {
+        if (pass == 0) {
+            TRY(upload(s, s->d_items, items));
+            PreParams Q = base_pre_params(s);
+            Q.groups = s->d_groups.p; Q.items = s->d_items.p; Q.arena = s->d_arena.p;
+            Q.smem_arena_bytes = plan.max_smem_lean; Q.out_f = s->d_f32a.p;
+            TRY(launch_prefilter(s, Q, 1, plan.max_smem_lean, 0, true));
+        } else {
+            ScanParams P = base_scan_params(s, 1);
+            P.out_f = s->d_f32a.p;
+            TRY((run_scan<EPI_STORE, false>(s, plan, P, items)));
+        }
+        CK(cudaMemcpyAsync(tmp.data(), s->d_f32a.p, tmp.size() * 4, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+        float* out = pass == 0 ? out_approx : out_exact;
+        for (int64_t r = 0; r < rows; ++r)
+            for (int q = 0; q < nq; ++q) out[r * nq + q] = tmp[(size_t)r * 32 + q];
+    }
+    return PK_OK;
+}
+
 int pk_sync(pk_store* s) {
     if (!s) return fail(PK_ERR_ARG, "null store");
     CK(cudaSetDevice(s->device));
@@ -1576,6 +1897,17 @@ int64_t pk_stat(pk_store* s, int which) {
             return (int64_t)(s->h_rec_off[s->shard_end] - s->h_rec_off[s->shard_begin]) * 16;
         case PK_STAT_H2D_BYTES: return s->stat_h2d;
         case PK_STAT_D2H_BYTES: return s->stat_d2h;
+        case PK_STAT_PREFILTER: return s->job.valid && s->job.lean ? 1 : 0;
+        case PK_STAT_FALLBACK_QUERIES: return s->stat_fallback;
+        case PK_STAT_RESCORE_NS: return s->stat_rescore_ns;
+        case PK_STAT_SHARD_LEAN_BYTES: {
+            if (s->lean_dirty) return 0;
+            int64_t b = 0;
+            for (int64_t r = s->shard_begin; r < s->shard_end; ++r) b += 16 * (int64_t)lean_record_u4(s->h_ncl[r], s->h_nfr[r], s->h_ntok[r]);
+            return b;
+        }
+        case PK_STAT_SHORTLIST: return s->job.valid && s->job.lean ? s->job.Ks : 0;
+        case PK_STAT_MARGIN_E9: return (int64_t)((double)s->margin * 1e9);
         default: return -1;
     }
 }

@@ -22,6 +22,15 @@
 //         tok_key[n_tok]      (t << 26) | token id, ascending inside a cell, padded to 4 words
 //         tok_w[n_tok]        double w = (double)tf * (double)idf   (idf 1.0f when the token is
 //                             missing from the column's table; w = tf when the column has no table)
+//
+// LEAN RECORD (one per user, 16-byte aligned, addressed by lrec_off[row] in uint4 units): the fp32 stream
+// the pre-filter of the full scan reads (fas_prefilter_kernel).  The tf-idf weights are stored already
+// divided by the cell's L2 norm, so a dot product of two lean cells IS the cosine (approximately).
+//
+//   word  0 uid   1 public   2 gender   3 completion   4 age   5..7 region_parts
+//         8 n_clubs   9 n_friends   10 n_tok   11 number of region parts >= 0
+//         12,13 64-bit mask of non-empty text columns   14 rsqrt(n_clubs) (float)   15 rsqrt(n_friends) (float)
+//   then  clubs[n_clubs], friends[n_friends], tok_key[n_tok], tok_wn[n_tok] (float), each padded to 4 words
 #pragma once
 #include <stdint.h>
 
@@ -41,6 +50,11 @@ __host__ __device__ inline uint32_t pad4(uint32_t x) { return (x + 3u) & ~3u; }
 // size of a packed record in uint4 units
 __host__ __device__ inline uint32_t record_u4(uint32_t n_clubs, uint32_t n_friends, uint32_t n_cells, uint32_t n_tok) {
     return kHdrU4 + pad4(n_clubs) / 4 + pad4(n_friends) / 4 + n_cells + pad4(n_tok) / 4 + (n_tok + 1) / 2;
+}
+
+constexpr int kLeanHdrWords = 16;
+__host__ __device__ inline uint32_t lean_record_u4(uint32_t n_clubs, uint32_t n_friends, uint32_t n_tok) {
+    return kLeanHdrWords / 4 + pad4(n_clubs) / 4 + pad4(n_friends) / 4 + 2 * (pad4(n_tok) / 4);
 }
 
 // sort key of the reference comparator (score desc, id asc; src/recommender_graph.cpp:97-100):
@@ -67,6 +81,16 @@ struct NormTables {
     int32_t dim_comp, dim_age;     // completion / age tables are [dim][dim], index [cand][query]
 };
 
+// fp32 constants of the pre-filter.  sigma(z_f(s)) = 1 / (1 + 2^(a[f]*s + b[f])).
+struct LeanNorm {
+    float4 fld[kMaxFields];        // {a, b, sigmoid(z(0)), sigmoid(z(1))} per field
+    float region[64];              // as NormTables::region
+    float lut[kMaxT / 8][256];     // lut[j][bits] = sum of sigmoid(z(0)) over the text columns 8j+i with bit i set
+    float inv_total;               // 1 / total_possible
+    float margin;                  // bound on |pre-filter score - exact score|
+    int32_t dim_comp, dim_age;
+};
+
 // One group of <= 32 query users = the lanes of the scoring warps.
 struct GroupDesc {
     uint32_t arena_off;     // byte offset of the group's tables in the arena (16-byte aligned)
@@ -76,6 +100,11 @@ struct GroupDesc {
     int32_t log_sc, log_sf, log_sa, log_st;        // log2 sizes of clubs / friends / adjacency / text tables
     uint32_t off_nq, off_clubs, off_friends, off_adj, off_text, off_vals;   // byte offsets inside the arena block
     uint32_t n_vals;
+    // the block is laid out [lean-only | shared set tables | exact-only]: the pre-filter stages
+    // [0, lean_end), the exact kernel [exact_begin, arena_bytes)
+    uint32_t off_text2, off_base, off_vals32;   // lean-only: {key, mask} slots, first value index per slot, normalised weights
+    uint32_t lean_end, exact_begin;
+    int32_t lean_in_smem;
     int32_t adj_begin[kLanes + 1];   // slice of the per-batch exclusion id array for each lane
     int32_t row[kLanes];             // store row of each lane's user, -1 = unused lane
     int32_t qidx[kLanes];            // caller-side query index of each lane

@@ -1,0 +1,337 @@
+// pk_prefilter.cuh -- the fp32 pre-filter of the full scan.
+//
+// The full scan asks for the top-k of 1.6 M exact FAS values per query, but only the few candidates near
+// the k-th score need the reference's fp64 arithmetic.  fas_prefilter_kernel streams the LEAN records
+// (pk_layout.h) and computes, for every (query, candidate) pair, an fp32 approximation of
+// Recommender::profile_similarity (reference src/recommender_similarity.cpp:10-124) whose distance from the
+// exact value is bounded by LeanNorm::margin.  It keeps the Ks > k best approximate scores per query.  If
+// the Ks-th approximate score lies more than 2*margin below the k-th, the exact top-k is a subset of that
+// shortlist (shortlist_check_kernel verifies this per query); the shortlist is then re-scored by the exact
+// kernel (fas_scan_kernel in list mode).  Queries that fail the check are re-run by the exact full scan.
+// The result is therefore always the exact kernel's; the pre-filter only decides which pairs it sees.
+#pragma once
+#include "pk_scan.cuh"
+
+namespace pk {
+
+constexpr int kPreThreads = 1024;
+constexpr int kPreWarps = kPreThreads / 32;
+
+// one warp per row: lean record from the packed (exact) record
+__global__ void lean_pack_kernel(int n, const uint4* __restrict__ rec, const uint64_t* __restrict__ rec_off,
+                                 const uint64_t* __restrict__ lrec_off, uint4* __restrict__ lrec) {
+    const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (row >= n) return;
+    const uint32_t* r = reinterpret_cast<const uint32_t*>(rec + rec_off[row]);
+    uint32_t* out = reinterpret_cast<uint32_t*>(lrec + lrec_off[row]);
+    const uint32_t ncl = r[8], nfr = r[9], ncells = r[10], ntok = r[11];
+    const uint32_t o_clubs = kHdrWords, o_friends = o_clubs + pad4(ncl), o_cells = o_friends + pad4(nfr),
+                   o_keys = o_cells + 4 * ncells, o_w = o_keys + pad4(ntok);
+    const uint32_t l_clubs = kLeanHdrWords, l_friends = l_clubs + pad4(ncl), l_keys = l_friends + pad4(nfr),
+                   l_w = l_keys + pad4(ntok);
+    if (lane < 8) out[lane] = r[lane];
+    if (lane == 8) out[8] = ncl;
+    if (lane == 9) out[9] = nfr;
+    if (lane == 10) out[10] = ntok;
+    if (lane == 11) out[11] = r[14];
+    if (lane == 12) out[12] = r[12];
+    if (lane == 13) out[13] = r[13];
+    if (lane == 14) out[14] = __float_as_uint(ncl ? (float)(1.0 / sqrt((double)ncl)) : 0.0f);
+    if (lane == 15) out[15] = __float_as_uint(nfr ? (float)(1.0 / sqrt((double)nfr)) : 0.0f);
+    for (uint32_t i = lane; i < pad4(ncl); i += 32) out[l_clubs + i] = r[o_clubs + i];
+    for (uint32_t i = lane; i < pad4(nfr); i += 32) out[l_friends + i] = r[o_friends + i];
+    for (uint32_t i = lane; i < pad4(ntok); i += 32) {
+        out[l_keys + i] = (i < ntok) ? r[o_keys + i] : 0xffffffffu;
+        out[l_w + i] = 0u;
+    }
+    __syncwarp();
+    const double* w = reinterpret_cast<const double*>(r + o_w);
+    uint32_t begin = 0;
+    for (uint32_t c = 0; c < ncells; ++c) {
+        const uint32_t end = r[o_cells + 4 * c + 1];
+        const double nrm = *reinterpret_cast<const double*>(r + o_cells + 4 * c + 2);
+        for (uint32_t i = begin + lane; i < end; i += 32)
+            out[l_w + i] = __float_as_uint((nrm > 0.0) ? (float)(w[i] / nrm) : 0.0f);
+        begin = end;
+    }
+}
+
+struct PreParams {
+    const uint4* lrec;
+    const uint64_t* lrec_off;
+    const GroupDesc* groups;
+    const WorkItem* items;
+    const uint8_t* arena;
+    const LeanNorm* ln;
+    const float* tab_comp;       // [dim][dim] float copies of the completion / age tables, index [cand][query]
+    const float* tab_age;
+    int Ks;                      // shortlist length (multiple of 32)
+    int exclude_mode;
+    uint32_t smem_arena_bytes;
+    uint64_t* out_keys;          // TOPK: [item.out_slot][32][Ks], key = (approx score bits, candidate ROW)
+    float* out_f;                // STORE (tests): [(item.out_slot + i)][32] approximate scores
+};
+
+__device__ __forceinline__ float lean_sigma(float4 c, float s) {
+    // 1 / (1 + 2^(a s + b)); ex2 saturates to +inf / 0, the reciprocal to 0 / 1
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(fmaf(c.x, s, c.y)));
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+    return r;
+}
+
+template <bool STORE>
+__global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const PreParams P) {
+    extern __shared__ uint4 smem_u4[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(smem_u4);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const WorkItem it = P.items[blockIdx.x];
+    const GroupDesc* gd = P.groups + it.group;
+
+    const uint32_t arena_sm = P.smem_arena_bytes;
+    LeanNorm* N = reinterpret_cast<LeanNorm*>(smem + arena_sm);
+    constexpr uint32_t kNormBytes = (sizeof(LeanNorm) + 15u) & ~15u;
+    const int Ks = STORE ? 0 : P.Ks;
+    uint64_t* lists = reinterpret_cast<uint64_t*>(smem + arena_sm + kNormBytes);   // [32][Ks]
+    uint64_t* tau = lists + 32 * Ks;
+    int* locks = reinterpret_cast<int*>(tau + 32);
+    int* next = locks + 32;
+    uint4* stage = reinterpret_cast<uint4*>(next + 4) + warp * 32;                  // per-warp hit staging
+
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(P.arena + gd->arena_off);
+        const uint32_t n16 = gd->lean_end >> 4;
+        for (uint32_t i = tid; i < n16; i += kPreThreads) smem_u4[i] = __ldg(src + i);
+        const uint4* nsrc = reinterpret_cast<const uint4*>(P.ln);
+        uint4* ndst = reinterpret_cast<uint4*>(N);
+        for (uint32_t i = tid; i < kNormBytes / 16; i += kPreThreads) ndst[i] = __ldg(nsrc + i);
+        for (int i = tid; i < 32 * Ks; i += kPreThreads) lists[i] = 0ull;
+        if (tid < 32) { tau[tid] = 0ull; locks[tid] = 0; }
+        if (tid == 0) *next = it.cand_begin;
+    }
+    __syncthreads();
+
+    const uint2* t_text = reinterpret_cast<const uint2*>(smem + gd->off_text2);
+    const uint32_t* t_base = reinterpret_cast<const uint32_t*>(smem + gd->off_base);
+    const float* vals = reinterpret_cast<const float*>(smem + gd->off_vals32);
+    const uint2* t_clubs = reinterpret_cast<const uint2*>(smem + gd->off_clubs);
+    const uint2* t_friends = reinterpret_cast<const uint2*>(smem + gd->off_friends);
+    const uint2* t_adj = reinterpret_cast<const uint2*>(smem + gd->off_adj);
+    const int log_sc = gd->log_sc, log_sf = gd->log_sf, log_sa = gd->log_sa, log_st = gd->log_st;
+
+    // ---- this lane's query ----------------------------------------------------------------------
+    const int qrow = (lane < gd->n_lanes) ? gd->row[lane] : -1;
+    const bool q_active = qrow >= 0;
+    int q_uid = 0, q_pub = -1, q_gender = -1, q_comp = 0, q_age = 0, q_r0 = -1, q_r1 = -1, q_r2 = -1, q_acnt = 0;
+    uint32_t q_ncl = 0, q_nfr = 0, q_m0 = 0, q_m1 = 0;
+    float q_rsc = 0.f, q_rsf = 0.f;
+    if (q_active) {
+        const uint4* qr = P.lrec + P.lrec_off[qrow];
+        const uint4 a = __ldg(qr), b = __ldg(qr + 1), c = __ldg(qr + 2), d = __ldg(qr + 3);
+        q_uid = (int)a.x; q_pub = (int)a.y; q_gender = (int)a.z; q_comp = (int)a.w;
+        q_age = (int)b.x; q_r0 = (int)b.y; q_r1 = (int)b.z; q_r2 = (int)b.w;
+        q_ncl = c.x; q_nfr = c.y; q_acnt = (int)c.w;
+        q_m0 = d.x; q_m1 = d.y; q_rsc = __uint_as_float(d.z); q_rsf = __uint_as_float(d.w);
+    }
+    const uint32_t lanebit = 1u << lane, lane_lt = lanebit - 1u;
+    const int dim_comp = N->dim_comp, dim_age = N->dim_age;
+    const float inv_total = N->inv_total;
+
+    constexpr int kChunk = 4;
+    for (;;) {
+        int c0 = 0;
+        if (lane == 0) c0 = atomicAdd(next, kChunk);
+        c0 = __shfl_sync(kFull, c0, 0);
+        if (c0 >= it.cand_end) break;
+        const int c1 = min(c0 + kChunk, it.cand_end);
+        uint64_t offv = 0;
+        if (c0 + lane < c1) offv = __ldg(P.lrec_off + c0 + lane);
+        for (int ci = c0; ci < c1; ++ci) {
+            const uint64_t off = __shfl_sync(kFull, offv, ci - c0);
+            const uint4* cr = P.lrec + off;
+            const uint32_t* cw = reinterpret_cast<const uint32_t*>(cr);
+            const uint4 h0 = __ldg(cr), h1 = __ldg(cr + 1), h2 = __ldg(cr + 2), h3 = __ldg(cr + 3);
+            const int c_uid = (int)h0.x, c_pub = (int)h0.y, c_gender = (int)h0.z, c_comp = (int)h0.w;
+            const int c_age = (int)h1.x, c_r0 = (int)h1.y, c_r1 = (int)h1.z, c_r2 = (int)h1.w;
+            const uint32_t c_ncl = h2.x, c_nfr = h2.y, c_ntok = h2.z;
+            const int c_bcnt = (int)h2.w;
+            const uint32_t o_clubs = kLeanHdrWords, o_friends = o_clubs + pad4(c_ncl), o_keys = o_friends + pad4(c_nfr),
+                           o_w = o_keys + pad4(c_ntok);
+
+            // text columns present on both sides: every one contributes sigma(z(0)) unless a token matches
+            const uint32_t b0 = q_m0 & h3.x, b1 = q_m1 & h3.y;
+            float sum = N->lut[0][b0 & 255u] + N->lut[1][(b0 >> 8) & 255u] + N->lut[2][(b0 >> 16) & 255u] + N->lut[3][b0 >> 24];
+            if (q_m1 | h3.y)
+                sum += N->lut[4][b1 & 255u] + N->lut[5][(b1 >> 8) & 255u] + N->lut[6][(b1 >> 16) & 255u] + N->lut[7][b1 >> 24];
+            int used = __popc(b0) + __popc(b1);
+
+            // fixed scalar fields (src/recommender_similarity.cpp:38-77)
+            if (q_pub >= 0 && c_pub >= 0) { const float4 f = N->fld[0]; sum += (q_pub == c_pub) ? f.w : f.z; ++used; }
+            if (q_gender >= 0 && c_gender >= 0) { const float4 f = N->fld[1]; sum += (q_gender == c_gender) ? f.w : f.z; ++used; }
+            if (q_comp > 0 && c_comp > 0) {
+                float sg;
+                if (q_comp < dim_comp && c_comp < dim_comp) sg = __ldg(P.tab_comp + c_comp * dim_comp + q_comp);
+                else sg = lean_sigma(N->fld[2], (float)min(q_comp, c_comp) / (float)max(q_comp, c_comp));
+                sum += sg; ++used;
+            }
+            if (q_age > 0 && c_age > 0) {
+                float sg;
+                if (q_age < dim_age && c_age < dim_age) sg = __ldg(P.tab_age + c_age * dim_age + q_age);
+                else sg = lean_sigma(N->fld[3], (float)min(q_age, c_age) / (float)max(q_age, c_age));
+                sum += sg; ++used;
+            }
+            if (q_acnt > 0 && c_bcnt > 0) {
+                const int matches = (int)(q_r0 >= 0 && q_r0 == c_r0) + (int)(q_r1 >= 0 && q_r1 == c_r1) + (int)(q_r2 >= 0 && q_r2 == c_r2);
+                sum += N->region[(q_acnt * 4 + c_bcnt) * 4 + matches];
+                ++used;
+            }
+
+            // clubs / friends (:79-91)
+            #pragma unroll
+            for (int which = 0; which < 2; ++which) {
+                const uint32_t c_n = which ? c_nfr : c_ncl;
+                if (c_n == 0) continue;                               // warp-uniform
+                const uint32_t eo = which ? o_friends : o_clubs;
+                const uint2* tab = which ? t_friends : t_clubs;
+                const int lg = which ? log_sf : log_sc;
+                int inter = 0;
+                for (uint32_t e0 = 0; e0 < c_n; e0 += 32) {
+                    const uint32_t i = e0 + lane;
+                    uint32_t m = 0;
+                    if (i < c_n) m = probe_set(tab, lg, __ldg(cw + eo + i));
+                    uint32_t hits = __ballot_sync(kFull, m != 0u);
+                    while (hits) {
+                        const int j = __ffs(hits) - 1;
+                        hits &= hits - 1;
+                        const uint32_t mj = __shfl_sync(kFull, m, j);
+                        inter += (mj & lanebit) ? 1 : 0;
+                    }
+                }
+                const uint32_t q_n = which ? q_nfr : q_ncl;
+                if (q_n > 0) {
+                    const float4 f = N->fld[5 + which];
+                    float sg = f.z;
+                    if (inter > 0) sg = lean_sigma(f, (float)inter * (which ? q_rsf : q_rsc) * __uint_as_float(which ? h3.w : h3.z));
+                    sum += sg; ++used;
+                }
+            }
+
+            // text columns (:93-114): the lean weights are already divided by the cell norms
+            if (c_ntok > 0) {
+                const uint32_t* keys = cw + o_keys;
+                const float* tokw = reinterpret_cast<const float*>(cw + o_w);
+                float acc = 0.f;
+                int cur = -1;                                         // warp-uniform: column of the open cell
+                for (uint32_t cb = 0; cb < c_ntok; cb += 32) {
+                    const uint32_t i = cb + lane;
+                    uint32_t m = 0, slot = 0, key = 0;
+                    if (i < c_ntok) {
+                        key = __ldg(keys + i);
+                        const uint32_t msk = (1u << log_st) - 1u;
+                        slot = hash_u32(key, log_st);
+                        for (;;) {
+                            const uint2 e = t_text[slot];
+                            if (e.y == 0u) break;
+                            if (e.x == key) { m = e.y; break; }
+                            slot = (slot + 1) & msk;
+                        }
+                    }
+                    uint32_t hitb = __ballot_sync(kFull, m != 0u);
+                    if (hitb == 0u) continue;
+                    if (m) stage[lane] = make_uint4(m, t_base[slot], __float_as_uint(__ldg(tokw + i)), key >> kTokBits);
+                    __syncwarp();
+                    while (hitb) {
+                        const int j = __ffs(hitb) - 1;
+                        hitb &= hitb - 1;
+                        const uint4 h = stage[j];
+                        if ((int)h.w != cur) {
+                            if (cur >= 0 && acc != 0.f) { const float4 f = N->fld[kNumFixed + cur]; sum += lean_sigma(f, acc) - f.z; }
+                            acc = 0.f;
+                            cur = (int)h.w;
+                        }
+                        if (h.x & lanebit) acc = fmaf(vals[h.y + __popc(h.x & lane_lt)], __uint_as_float(h.z), acc);
+                    }
+                    __syncwarp();
+                }
+                if (cur >= 0 && acc != 0.f) { const float4 f = N->fld[kNumFixed + cur]; sum += lean_sigma(f, acc) - f.z; }
+            }
+
+            float fas = 0.f;
+            if (used > 0) {
+                const float S = __fdividef(sum, (float)used);
+                const float F = (float)used * inv_total;
+                fas = __fdividef(2.0f * S * F, S + F);
+                fas = fmaxf(fas, 0.f);
+            }
+
+            if (STORE) {
+                P.out_f[(size_t)(it.out_slot + (ci - it.cand_begin)) * 32 + lane] = q_active ? fas : -1.0f;
+            } else {
+                const uint64_t key = make_key(__float_as_uint(fas), ci);
+                const uint64_t tl = reinterpret_cast<volatile uint64_t*>(tau)[lane];
+                uint32_t pass = __ballot_sync(kFull, q_active && key > tl);
+                if (pass) {
+                    // exclusions only matter for the few candidates that reach a list
+                    bool ok = true;
+                    if (P.exclude_mode >= PK_EXCLUDE_SELF && c_uid == q_uid) ok = false;
+                    if (P.exclude_mode >= PK_EXCLUDE_SELF_AND_ADJ) {
+                        const uint32_t mx = probe_set(t_adj, log_sa, (uint32_t)c_uid);
+                        if (mx & lanebit) ok = false;
+                    }
+                    pass &= __ballot_sync(kFull, ok);
+                    while (pass) {
+                        const int j = __ffs(pass) - 1;
+                        pass &= pass - 1;
+                        const uint64_t kj = __shfl_sync(kFull, key, j);
+                        topk_insert(lists + j * Ks, Ks, Ks, kj, locks + j, reinterpret_cast<volatile uint64_t*>(tau) + j, lane);
+                    }
+                }
+            }
+        }
+    }
+
+    if (!STORE) {
+        __syncthreads();
+        uint64_t* dst = P.out_keys + (size_t)it.out_slot * 32 * Ks;
+        for (int i = tid; i < 32 * Ks; i += kPreThreads) dst[i] = lists[i];
+    }
+}
+
+// Per query: is the merged shortlist (Ks approximate keys, descending) guaranteed to contain the exact
+// top-k?  Yes when it holds every candidate (fewer than Ks entries) or when its last approximate score is
+// more than 2*margin below the k-th one.  Also writes the shortlist's candidate rows for the exact pass.
+struct CheckParams {
+    const uint64_t* short_keys;   // [nq][Ks]
+    const int32_t* q_group;       // group of each query, -1 = no profile
+    const int32_t* q_lane;
+    int32_t* cand_rows;           // [(group*32 + lane)*Ks + i], -1 = empty
+    int32_t* q_flag;              // preset by the host (groups the pre-filter cannot take); OR-ed here
+    int32_t* group_flag;
+    int nq, K, Ks;
+    float margin;
+};
+
+__global__ void shortlist_check_kernel(const CheckParams P) {
+    const int q = blockIdx.x;
+    const int g = P.q_group[q];
+    if (g < 0) return;
+    const uint64_t* keys = P.short_keys + (size_t)q * P.Ks;
+    int32_t* rows = P.cand_rows + ((size_t)g * 32 + P.q_lane[q]) * P.Ks;
+    for (int i = threadIdx.x; i < P.Ks; i += blockDim.x) {
+        const uint64_t k = keys[i];
+        rows[i] = k ? key_id(k) : -1;
+    }
+    if (threadIdx.x == 0) {
+        const uint64_t last = keys[P.Ks - 1];
+        bool complete = true;
+        if (last != 0ull) {
+            const float a_last = __uint_as_float(key_score_bits(last));
+            const float a_k = __uint_as_float(key_score_bits(keys[P.K - 1]));
+            complete = a_last < a_k - 2.0f * P.margin - 1e-7f;
+        }
+        if (!complete) { P.q_flag[q] = 1; atomicOr(P.group_flag + g, 1); }
+    }
+}
+
+}  // namespace pk

@@ -142,6 +142,28 @@ __global__ void __launch_bounds__(kPrepThreads) group_prep_kernel(const PrepPara
             }
         }
     }
+
+    // phase 4 (full scan only): the pre-filter's fp32 view of the text table -- {key, mask} slots, the first
+    // value index of each slot, and the weights divided by the query cell's L2 norm
+    if (gd.exact_begin == 0) return;
+    __syncthreads();
+    uint2* t2 = reinterpret_cast<uint2*>(base + gd.off_text2);
+    uint32_t* tbase = reinterpret_cast<uint32_t*>(base + gd.off_base);
+    float* v32 = reinterpret_cast<float*>(base + gd.off_vals32);
+    for (uint32_t sl = tid; sl < st; sl += kPrepThreads) {
+        const uint32_t key = t_text32[4 * sl], m2 = t_text32[4 * sl + 1], b0 = t_text32[4 * sl + 2];
+        t2[sl] = make_uint2(key, m2);
+        tbase[sl] = b0;
+        const uint32_t ct = key >> kTokBits;
+        uint32_t mm = m2, r = 0;
+        while (mm) {
+            const int L = __ffs(mm) - 1;
+            mm &= mm - 1;
+            const double nrm = nq[ct * 32 + L];
+            v32[b0 + r] = (nrm > 0.0) ? (float)(vals[b0 + r] / nrm) : 0.0f;
+            ++r;
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -157,7 +179,8 @@ struct ScanParams {
     const NormTables* norm;
     const double* tab_comp;      // [dim_comp][dim_comp] sigmoid(z(min/max)), index [cand][query]
     const double* tab_age;
-    const int32_t* cand_rows;    // explicit candidate rows, or null = the row index itself
+    const int32_t* cand_rows;    // explicit candidate rows (negative = skip), or null = the row index itself
+    const int32_t* group_flag;   // when set: CTAs of groups whose flag is 0 exit at once (fallback pass of the full scan)
     int T;
     int K, Kp;                   // top-k and its padding to a multiple of 32
     int exclude_mode;
@@ -220,7 +243,9 @@ __device__ __forceinline__ void topk_insert(uint64_t* list, int K, int Kp, uint6
             const bool gt = (i < K) && (vl[i] > key);
             pos += __popc(__ballot_sync(kFull, gt));
         }
-        for (int s0 = Kp - 32; s0 >= 0 && s0 + 32 > pos; s0 -= 32) {
+        // the shortlists of the lanes of a group overlap: a key that is already in the list is not inserted twice
+        const bool dup = (pos < K) && (vl[pos] == key);
+        for (int s0 = Kp - 32; !dup && s0 >= 0 && s0 + 32 > pos; s0 -= 32) {
             const int i = s0 + lane;
             const bool mv = (i > pos) && (i < K);
             uint64_t v = 0;
@@ -229,7 +254,7 @@ __device__ __forceinline__ void topk_insert(uint64_t* list, int K, int Kp, uint6
             if (mv) vl[i] = v;
             __syncwarp();
         }
-        if (lane == 0) vl[pos] = key;
+        if (lane == 0 && !dup) vl[pos] = key;
         __syncwarp();
         if (lane == 0) *tau = vl[K - 1];
     }
@@ -245,6 +270,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
     const int tid = threadIdx.x, lane = tid & 31;
     const WorkItem it = P.items[blockIdx.x];
     const GroupDesc* gd = P.groups + it.group;
+    if (P.group_flag && P.group_flag[it.group] == 0) return;   // uniform for the CTA
 
     // ---- shared memory carve-up ------------------------------------------------------------
     const uint32_t arena_sm = SM ? P.smem_arena_bytes : 0u;
@@ -258,8 +284,8 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
 
     {   // stage the group's tables and the normalizer constants
         if (SM) {
-            const uint4* src = reinterpret_cast<const uint4*>(P.arena + gd->arena_off);
-            const uint32_t n16 = gd->arena_bytes >> 4;
+            const uint4* src = reinterpret_cast<const uint4*>(P.arena + gd->arena_off + gd->exact_begin);
+            const uint32_t n16 = (gd->arena_bytes - gd->exact_begin) >> 4;
             for (uint32_t i = tid; i < n16; i += kScanThreads) smem_u4[i] = __ldg(src + i);
         }
         const uint4* nsrc = reinterpret_cast<const uint4*>(P.norm);
@@ -271,7 +297,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
     }
     __syncthreads();
 
-    const uint8_t* tb = SM ? smem : (P.arena + gd->arena_off);
+    const uint8_t* tb = SM ? (smem - gd->exact_begin) : (P.arena + gd->arena_off);
     const double* nq = reinterpret_cast<const double*>(tb + gd->off_nq);
     const uint2* t_clubs = reinterpret_cast<const uint2*>(tb + gd->off_clubs);
     const uint2* t_friends = reinterpret_cast<const uint2*>(tb + gd->off_friends);
@@ -315,6 +341,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
         const int c1 = min(c0 + kChunk, it.cand_end);
         for (int ci = c0; ci < c1; ++ci) {
             const int64_t crow = P.cand_rows ? (int64_t)P.cand_rows[ci] : (int64_t)ci;
+            if (crow < 0) continue;   // empty shortlist slot (warp-uniform)
             const uint4* cr = P.rec + P.rec_off[crow];
             const uint32_t* cw = reinterpret_cast<const uint32_t*>(cr);
             const uint4 h0 = __ldg(cr), h1 = __ldg(cr + 1), h2 = __ldg(cr + 2), h3 = __ldg(cr + 3), h4 = __ldg(cr + 4);
@@ -506,13 +533,23 @@ struct MergeParams {
     int n_lists;                // mode B
     int nq, K, stride_k;
     uint64_t* out_keys;         // [nq][K], 0-padded
+    // mode A, two-stage full scan: queries whose flag is set take their lists from the fallback pass instead
+    const int32_t* q_flag;
+    const uint64_t* alt_keys;
+    const int32_t* alt_slot0;
+    const int32_t* alt_n_lists_q;
+    int alt_stride_k;
 };
 
 __global__ void __launch_bounds__(128) merge_topk_kernel(const MergeParams P) {
     const int q = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const bool modeA = P.slot0 != nullptr;
-    const int nl = modeA ? P.n_lists_q[q] : P.n_lists;
+    const bool alt = modeA && P.q_flag != nullptr && P.q_flag[q] != 0;
+    const uint64_t* kbase = alt ? P.alt_keys : P.keys;
+    const int32_t* slot0 = alt ? P.alt_slot0 : P.slot0;
+    const int stride = alt ? P.alt_stride_k : P.stride_k;
+    const int nl = modeA ? (alt ? P.alt_n_lists_q[q] : P.n_lists_q[q]) : P.n_lists;
     __shared__ uint64_t wbest[4];
     __shared__ int wown[4];
     // thread t owns lists t, t+128, ...; head[] positions are kept in registers for up to 8 lists per thread
@@ -521,7 +558,7 @@ __global__ void __launch_bounds__(128) merge_topk_kernel(const MergeParams P) {
     #pragma unroll
     for (int i = 0; i < kOwn; ++i) head[i] = 0;
     auto list_ptr = [&](int j) -> const uint64_t* {
-        if (modeA) return P.keys + ((size_t)(P.slot0[q] + j) * 32 + P.lane[q]) * P.stride_k;
+        if (modeA) return kbase + ((size_t)(slot0[q] + j) * 32 + P.lane[q]) * stride;
         return P.keys + ((size_t)j * P.nq + q) * P.stride_k;
     };
     for (int r = 0; r < P.K; ++r) {

@@ -25,10 +25,11 @@ ABI_SYMBOLS = (
     "pk_store_load_world", "pk_store_set_shard", "pk_set_normalizers", "pk_compute_idf", "pk_set_idf",
     "pk_idf_size", "pk_get_idf", "pk_set_adj_row", "pk_pair_similarity", "pk_pair_fields", "pk_pair_overlap",
     "pk_fullscan_topk", "pk_fullscan_prepare", "pk_fullscan_execute", "pk_fullscan_fetch", "pk_fullscan_keys", "pk_recommend", "pk_candidates", "pk_fullscan_local_keys", "pk_merge_keys", "pk_sync",
-    "pk_stream", "pk_stat",
+    "pk_stream", "pk_stat", "pk_debug_prefilter",
 )
 STAT_KERNEL_LAUNCHES, STAT_PAIRS_SCORED, STAT_STORE_BYTES, STAT_SCAN_KERNEL_NS, STAT_SCAN_LAUNCHES, STAT_GROUPS, \
-    STAT_SHARD_RECORD_BYTES, STAT_H2D_BYTES, STAT_D2H_BYTES = range(9)
+    STAT_SHARD_RECORD_BYTES, STAT_H2D_BYTES, STAT_D2H_BYTES, STAT_PREFILTER, STAT_FALLBACK_QUERIES, STAT_RESCORE_NS, \
+    STAT_SHARD_LEAN_BYTES, STAT_SHORTLIST, STAT_MARGIN_E9 = range(15)
 
 _lib = None
 
@@ -230,6 +231,16 @@ class DeviceRecommender:
         _check(self.lib, self.lib.pk_merge_keys(self.h, C.c_void_p(d_keys_ptr), int(n_lists), int(nq), int(k),
                                                 ptr(ids, i32p), ptr(sc, f32p), ptr(cnt, i32p)))
         return ids, sc, cnt
+
+    def debug_prefilter(self, q, row_begin, row_end):
+        """(approx, exact) FAS of <= 32 queries against store rows [row_begin,row_end), each [rows][nq]"""
+        q = np.ascontiguousarray(q, np.int32)
+        rows = int(row_end - row_begin)
+        a = np.zeros((rows, len(q)), np.float32)
+        e = np.zeros((rows, len(q)), np.float32)
+        _check(self.lib, self.lib.pk_debug_prefilter(self.h, len(q), ptr(q, i32p), C.c_int64(row_begin), C.c_int64(row_end),
+                                                     ptr(a, f32p), ptr(e, f32p)))
+        return a, e
 
     def sync(self):
         _check(self.lib, self.lib.pk_sync(self.h))

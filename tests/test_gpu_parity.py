@@ -274,3 +274,66 @@ def test_vs_compiled_reference(small_world, oracle_libs):
         ref.set_adj_row(u, row[: len(row) // 2])
         assert_topk_equal(dev.recommend(MODE_COLLAB, q[:4], 20, 1000), ref.recommend(MODE_COLLAB, q[:4], 20, 1000), "collab after set_adj_row")
     dev.close()
+
+
+# ---- two-stage full scan (pk_prefilter.cuh): fp32 pre-filter -> exact re-score -> exact fallback -------------
+
+def _no_norm_world():
+    w = make_test_world(n=2000, seed=41)
+    w.set_normalizers(w.norm_mean, w.norm_sd, np.zeros(w.n_fields, np.uint8))   # every field uses z = 6(s - 0.5)
+    return w
+
+
+@pytest.mark.parametrize("which", ["normalized", "default_z", "gaps"])
+def test_prefilter_error_within_its_bound(which, small_world, gap_world, oracle_libs):
+    """|fp32 pre-filter score - exact score| must stay below the bound the shortlist proof relies on"""
+    from recommendation_system_pokec_b200.engine import DeviceRecommender, STAT_MARGIN_E9
+    w = {"normalized": small_world, "default_z": _no_norm_world(), "gaps": gap_world}[which]
+    dev = DeviceRecommender(w)
+    worst = 0.0
+    for seed in (1, 2, 3):
+        q = sample_queries(w, 32, seed=seed)
+        approx, exact = dev.debug_prefilter(q, 0, w.n)
+        worst = max(worst, float(np.abs(approx.astype(np.float64) - exact).max()))
+    margin = dev.stat(STAT_MARGIN_E9) / 1e9
+    assert 0 < margin < 1e-3
+    assert worst <= margin / 2, f"pre-filter error {worst:.3e} vs bound {margin:.3e}"
+    dev.close()
+
+
+def test_fullscan_with_and_without_prefilter_identical(env, monkeypatch):
+    from recommendation_system_pokec_b200.engine import STAT_PREFILTER, STAT_SHORTLIST
+    w, dev, orc = env
+    q = sample_queries(w, 150, seed=21)
+    for k in (50, 5, 100):
+        monkeypatch.delenv("POKEC_B200_NO_PREFILTER", raising=False)
+        two_stage = dev.fullscan(q, k, EXCLUDE_SELF_AND_ADJ)
+        assert dev.stat(STAT_PREFILTER) == 1 and dev.stat(STAT_SHORTLIST) >= k + 16
+        monkeypatch.setenv("POKEC_B200_NO_PREFILTER", "1")
+        exact = dev.fullscan(q, k, EXCLUDE_SELF_AND_ADJ)
+        assert dev.stat(STAT_PREFILTER) == 0
+        for x, y in zip(two_stage, exact):
+            assert np.array_equal(x, y), f"k={k}"
+    monkeypatch.delenv("POKEC_B200_NO_PREFILTER", raising=False)
+    # k too large for a shortlist with slack: the exact scan is used directly
+    dev.fullscan(q[:4], 250, EXCLUDE_SELF)
+    assert dev.stat(STAT_PREFILTER) == 0
+
+
+def test_fullscan_tie_heavy_world_falls_back_to_exact(oracle_libs):
+    """few fields and tiny vocabularies: thousands of candidates tie at the k-th score, the shortlist cannot be
+    proven complete, and the flagged queries must come out of the exact full scan -- identical to the oracle"""
+    from oracle.oracle import CpuOracle
+    from recommendation_system_pokec_b200.engine import DeviceRecommender, STAT_FALLBACK_QUERIES, STAT_PREFILTER
+    w = make_test_world(n=4000, seed=5, T=2, pairs=800)
+    # strip the distinguishing fields: no clubs / friends similarity, coarse ages
+    w.age[:] = 20 + (w.age % 3)
+    w.comp[:] = 50
+    dev, orc = DeviceRecommender(w), CpuOracle(w, "port")
+    q = sample_queries(w, 40, seed=2)
+    got = dev.fullscan(q, 50, EXCLUDE_SELF)
+    assert dev.stat(STAT_PREFILTER) == 1
+    assert dev.stat(STAT_FALLBACK_QUERIES) > 0, "the world was meant to defeat the shortlist proof"
+    assert_topk_equal(got, orc.fullscan(q, 50, EXCLUDE_SELF, nthreads=8), "tie-heavy fullscan")
+    dev.close()
+    orc.close()
