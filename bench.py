@@ -278,8 +278,10 @@ def main():
     scan_s = scan_ns / 1e9 / max(scan_launches, 1)
     peak, peak_src = measured_peak_hbm()
     achieved = alg_bytes_per_launch / scan_s / 1e9 if scan_s > 0 else 0.0
+    two_stage = dev.stat(engine.STAT_PREFILTER) == 1
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "fas_scan_kernel<true,0,false>", "peak_source": peak_src,
+                "traffic": None, "kernel": "fas_prefilter_kernel<false>" if two_stage else "fas_scan_kernel<true,0,false>",
+                "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes_per_launch, "launch_ms": scan_s * 1e3,
                 "note": "algorithmic bytes = queries x canonical record bytes of the shard (SURVEY 8d); cross-query reuse of a "
                         "streamed record is not credited, so this can exceed the physical DRAM fraction (see profiles/)"}
@@ -289,7 +291,13 @@ def main():
            "dtype": "f64", "data": "synthetic", "config": config, "clocks": clocks,
            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                    "ms_per_step": e2e_s / args.steps * 1e3},
-           "gpu_launches": int(launches), "roofline": roofline}
+           "gpu_launches": int(launches), "roofline": roofline,
+           "pipeline": {"two_stage": two_stage, "shortlist": dev.stat(engine.STAT_SHORTLIST),
+                        "prefilter_margin": dev.stat(engine.STAT_MARGIN_E9) / 1e9,
+                        "fallback_queries_last_step": dev.stat(engine.STAT_FALLBACK_QUERIES),
+                        "rescore_and_fallback_ms": dev.stat(engine.STAT_RESCORE_NS) / 1e6,
+                        "lean_record_bytes_shard": dev.stat(engine.STAT_SHARD_LEAN_BYTES),
+                        "exact_record_bytes_shard": dev.stat(engine.STAT_SHARD_RECORD_BYTES)}}
 
     if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
         dev.close()

@@ -561,7 +561,10 @@ __global__ void __launch_bounds__(128) merge_topk_kernel(const MergeParams P) {
         if (modeA) return kbase + ((size_t)(slot0[q] + j) * 32 + P.lane[q]) * stride;
         return P.keys + ((size_t)j * P.nq + q) * P.stride_k;
     };
-    for (int r = 0; r < P.K; ++r) {
+    // Keys are unique per (score, id) except across the slices of a re-scored shortlist, whose lanes' lists
+    // overlap: a key equal to the one just emitted is consumed without being emitted again.
+    uint64_t prev = 0ull;
+    for (int r = 0; r < P.K;) {
         uint64_t best = 0ull;
         int own = -1;
         #pragma unroll
@@ -591,7 +594,12 @@ __global__ void __launch_bounds__(128) merge_topk_kernel(const MergeParams P) {
             for (int i = 0; i < kOwn; ++i)
                 if (i == own) ++head[i];
         }
-        if (tid == 0) P.out_keys[(size_t)q * P.K + r] = gb;
+        const bool dup = gb != 0ull && gb == prev;
+        if (!dup) {
+            if (tid == 0) P.out_keys[(size_t)q * P.K + r] = gb;
+            prev = gb;
+            ++r;
+        }
         __syncthreads();
     }
 }
