@@ -31,6 +31,7 @@ sys.path.insert(0, ROOT)
 
 from recommendation_system_pokec_b200.synth import make_world, sample_normalizers, sample_queries, POKEC_N  # noqa: E402
 from recommendation_system_pokec_b200.cabi import EXCLUDE_SELF_AND_ADJ  # noqa: E402
+from recommendation_system_pokec_b200.sharding import shard_rows  # noqa: E402
 
 METRIC = "query-users/sec, FAS top-50 full scan vs 1.63M users"
 UNIT = "query-users/s"
@@ -190,7 +191,7 @@ def main():
     n = world.n
     t0 = time.time()
     dev = DeviceRecommender(world, device=local_rank)
-    lo, hi = n * rank // world_size, n * (rank + 1) // world_size
+    lo, hi = shard_rows(n, rank, world_size)
     dev.set_shard(lo, hi)
     q = sample_queries(world, args.queries, seed=2)
     nq, k = len(q), args.topk

@@ -11,7 +11,7 @@
 // It is NOT part of the product: only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
 // --impl reference legs may load it.  It is pinned against the compiled reference itself
 // (oracle/_ref/libpokec_ref.so, built from /root/reference by oracle/build_oracle.py) in
-// tests/test_oracle_vs_ref.py and against the committed fixtures in tests/golden/.
+// tests/test_oracle_cpu.py and against the committed fixtures in tests/golden/.
 //
 // Known, documented deviation: double sums over hash-map iteration order (src/recommender.cpp:75-113)
 // are taken in ascending token order here.  With >= 3 addends the double can differ in the last bit,

@@ -1,0 +1,51 @@
+"""Multi-GPU plumbing of the full scan: one process per GPU, candidate rows partitioned by row
+(= uid) range, every rank scans its shard for the whole query batch, the per-rank top-k lists travel as packed
+64-bit sort keys through ONE all-gather, and every rank merges them with the reference comparator
+(score desc, uid asc; reference src/recommender_graph.cpp:97-100).
+
+The key layout is csrc/pk_layout.h:make_key; the numpy forms below are the host mirror used for decoding and by
+the CPU (gloo) tests of this plumbing.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def shard_rows(n: int, rank: int, world_size: int):
+    """rows [lo, hi) of rank `rank`: contiguous, balanced to within one row, covering [0, n)"""
+    return n * rank // world_size, n * (rank + 1) // world_size
+
+
+def pack_keys(ids, scores):
+    """(float32 score >= 0, int32 id) -> uint64 key; larger key = better under the reference comparator"""
+    ids = np.asarray(ids, np.int32)
+    sb = np.ascontiguousarray(scores, np.float32).view(np.uint32).astype(np.uint64)
+    low = (~(ids.view(np.uint32) ^ np.uint32(0x80000000))).astype(np.uint64)
+    return (sb << np.uint64(33)) | (low << np.uint64(1)) | np.uint64(1)
+
+
+def unpack_keys(keys):
+    """uint64 keys (0 = empty slot) -> (ids, scores, valid)"""
+    keys = np.asarray(keys, np.uint64)
+    valid = keys != 0
+    sb = (keys >> np.uint64(33)).astype(np.uint32)
+    low = ((keys >> np.uint64(1)) & np.uint64(0xFFFFFFFF)).astype(np.uint32)
+    ids = ((~low) ^ np.uint32(0x80000000)).view(np.int32)
+    return np.where(valid, ids, -1).astype(np.int32), np.where(valid, sb.view(np.float32), 0).astype(np.float32), valid
+
+
+def merge_key_lists(lists, k):
+    """[n_lists, nq, k] keys -> [nq, k] best keys (descending, 0-padded): the host statement of pk_merge_keys"""
+    lists = np.asarray(lists, np.uint64)
+    n_lists, nq, kk = lists.shape
+    flat = np.transpose(lists, (1, 0, 2)).reshape(nq, n_lists * kk)
+    return np.sort(flat, axis=1)[:, ::-1][:, :k].copy()
+
+
+def all_gather_keys(local_keys, world_size):
+    """torch.distributed all-gather of a [nq, k] int64/uint64 key tensor -> [world_size, nq, k]"""
+    import torch
+    import torch.distributed as dist
+    out = torch.zeros((world_size,) + tuple(local_keys.shape), dtype=local_keys.dtype, device=local_keys.device)
+    dist.all_gather_into_tensor(out.view(-1), local_keys.reshape(-1).contiguous())
+    return out

@@ -337,3 +337,30 @@ def test_fullscan_tie_heavy_world_falls_back_to_exact(oracle_libs):
     assert_topk_equal(got, orc.fullscan(q, 50, EXCLUDE_SELF, nthreads=8), "tie-heavy fullscan")
     dev.close()
     orc.close()
+
+
+def test_cuda_path_vs_golden_fixtures(oracle_libs):
+    """the CUDA path against the committed outputs of the unmodified reference (tests/golden/make_golden.py)"""
+    import os
+    from recommendation_system_pokec_b200.engine import DeviceRecommender
+    from recommendation_system_pokec_b200.world import World
+    gdir = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    w = World.load(os.path.join(gdir, "world_small.npz"))
+    g = np.load(os.path.join(gdir, "golden_small.npz"))
+    dev = DeviceRecommender(w)
+    a, b, q = g["pair_a"], g["pair_b"], g["queries"]
+    assert np.array_equal(bits(dev.pair_fields(a, b)), bits(g["pair_fields"]))
+    assert_scores_close(dev.pair_similarity(a, b), g["pair_fas"], "pair FAS vs golden")
+    for col in (0, 2, 22, 32, 48):
+        tok, idf, _ = dev.get_idf(col)
+        assert np.array_equal(tok, g[f"idf_tok_{col}"]) and np.array_equal(bits(idf), bits(g[f"idf_val_{col}"]))
+    for name, mode, limit in (("graph", MODE_GRAPH, 5000), ("graph_l25", MODE_GRAPH, 25), ("collab", MODE_COLLAB, 5000),
+                              ("collab_l40", MODE_COLLAB, 40), ("clubs", MODE_CLUBS, 5000)):
+        assert_topk_equal(dev.recommend(mode, q, 20, limit), (g[f"{name}_id"], g[f"{name}_score"], g[f"{name}_cnt"]), f"golden {name}")
+    for ex in (0, 1, 2):
+        assert_topk_equal(dev.fullscan(q, 30, ex), (g[f"fullscan{ex}_id"], g[f"fullscan{ex}_score"], g[f"fullscan{ex}_cnt"]), f"golden fullscan {ex}")
+    dev.compute_idf(double_log=True)
+    for col in (0, 22):
+        tok, idf, _ = dev.get_idf(col)
+        assert np.array_equal(bits(idf), bits(g[f"idf_dbl_{col}"]))
+    dev.close()

@@ -1,0 +1,110 @@
+"""Pins the CPU restatement (oracle/fas_oracle.cpp) before anything trusts it:
+
+  * against the golden fixtures of tests/golden/ -- outputs of the UNMODIFIED compiled reference, generated
+    by tests/golden/make_golden.py (runs everywhere, including the GPU box where /root/reference is absent);
+  * against the compiled reference itself on larger seeded samples, where oracle/_ref/libpokec_ref.so exists.
+
+Contract: ids / counts / idf bits / per-field floats bit-exact; final scores bit-exact up to the
+documented 1-ulp flips of order-dependent double sums (counted and bounded)."""
+import os
+
+import numpy as np
+import pytest
+
+from recommendation_system_pokec_b200.cabi import MODE_GRAPH, MODE_COLLAB, MODE_CLUBS
+from recommendation_system_pokec_b200.synth import sample_queries
+from recommendation_system_pokec_b200.world import World
+from tests.conftest import make_test_world
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def bits(x):
+    return np.ascontiguousarray(x, np.float32).view(np.int32)
+
+
+def ulp_diff(a, b):
+    return np.abs(bits(a).astype(np.int64) - bits(b).astype(np.int64))
+
+
+def check_scores(got, want, what, max_flips=1):
+    d = ulp_diff(got, want)
+    assert int(d.max(initial=0)) <= 1, f"{what}: {int(d.max())} ulps"
+    assert int((d != 0).sum()) <= max_flips, f"{what}: {int((d != 0).sum())} one-ulp flips"
+
+
+def check_topk(got, want, what):
+    assert np.array_equal(got[2], want[2]), f"{what}: counts"
+    assert np.array_equal(got[0], want[0]), f"{what}: ids"
+    check_scores(got[1], want[1], what)
+
+
+@pytest.fixture(scope="module")
+def golden(oracle_libs):
+    from oracle.oracle import CpuOracle
+    w = World.load(os.path.join(GOLDEN, "world_small.npz"))
+    g = np.load(os.path.join(GOLDEN, "golden_small.npz"))
+    orc = CpuOracle(w, "port")
+    yield w, g, orc
+    orc.close()
+
+
+def test_golden_pairs(golden):
+    w, g, orc = golden
+    a, b = g["pair_a"], g["pair_b"]
+    assert np.array_equal(bits(orc.pair_fields(a, b)), bits(g["pair_fields"]))
+    check_scores(orc.pair_similarity(a, b), g["pair_fas"], "pair FAS vs golden")
+    assert (g["pair_fields"][:, 1:3] > 0).sum() > 20      # the fixture holds real club / friend overlaps
+
+
+def test_golden_idf(golden):
+    w, g, orc = golden
+    for col in (0, 2, 22, 32, 48):
+        tok = g[f"idf_tok_{col}"]
+        assert orc.idf_size(col) == len(tok)
+        val, has = orc.idf_lookup(col, tok)
+        assert has.all() and np.array_equal(bits(val), bits(g[f"idf_val_{col}"]))
+    orc.compute_idf(double_log=True)            # TFIDFIndex::build variant
+    try:
+        for col in (0, 2, 22, 32, 48):
+            val, has = orc.idf_lookup(col, g[f"idf_tok_{col}"])
+            assert has.all() and np.array_equal(bits(val), bits(g[f"idf_dbl_{col}"]))
+    finally:
+        orc.compute_idf()
+
+
+@pytest.mark.parametrize("name,mode,limit", [("graph", MODE_GRAPH, 5000), ("graph_l25", MODE_GRAPH, 25),
+                                             ("collab", MODE_COLLAB, 5000), ("collab_l40", MODE_COLLAB, 40),
+                                             ("clubs", MODE_CLUBS, 5000)])
+def test_golden_recommend(golden, name, mode, limit):
+    w, g, orc = golden
+    got = orc.recommend(mode, g["queries"], 20, limit, nthreads=4)
+    check_topk(got, (g[f"{name}_id"], g[f"{name}_score"], g[f"{name}_cnt"]), name)
+    assert g[f"{name}_cnt"].max() > 0
+
+
+@pytest.mark.parametrize("ex", [0, 1, 2])
+def test_golden_fullscan(golden, ex):
+    w, g, orc = golden
+    got = orc.fullscan(g["queries"], 30, ex, nthreads=4)
+    check_topk(got, (g[f"fullscan{ex}_id"], g[f"fullscan{ex}_score"], g[f"fullscan{ex}_cnt"]), f"fullscan exclude={ex}")
+
+
+def test_port_vs_compiled_reference(oracle_libs):
+    """larger differential run against the reference itself (this container only)"""
+    from oracle.oracle import CpuOracle, reference_available
+    if not reference_available():
+        pytest.skip("oracle/_ref/libpokec_ref.so not present")
+    w = make_test_world(n=2500, seed=13)
+    port, ref = CpuOracle(w, "port"), CpuOracle(w, "reference")
+    rng = np.random.default_rng(1)
+    a = w.uid[rng.integers(0, w.n, 20000)].astype(np.int32)
+    b = w.uid[rng.integers(0, w.n, 20000)].astype(np.int32)
+    assert np.array_equal(bits(port.pair_fields(a[:4000], b[:4000], nthreads=8)), bits(ref.pair_fields(a[:4000], b[:4000], nthreads=8)))
+    check_scores(port.pair_similarity(a, b, nthreads=8), ref.pair_similarity(a, b, nthreads=8), "pair FAS vs reference", max_flips=2)
+    q = np.concatenate([sample_queries(w, 40, seed=5), np.array([-1, 99_999_999], np.int32)])
+    for mode, limit in ((MODE_GRAPH, 5000), (MODE_GRAPH, 17), (MODE_COLLAB, 5000), (MODE_COLLAB, 33), (MODE_CLUBS, 5000)):
+        check_topk(port.recommend(mode, q, 50, limit, nthreads=8), ref.recommend(mode, q, 50, limit, nthreads=8), f"mode {mode} limit {limit}")
+    check_topk(port.fullscan(q[:12], 50, 2, nthreads=8), ref.fullscan(q[:12], 50, 2, nthreads=8), "fullscan vs reference")
+    port.close()
+    ref.close()
