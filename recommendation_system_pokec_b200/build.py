@@ -15,7 +15,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpokec_b200.so")
 SOURCES = ["pk_host.cu"]
-DEPS = ["pk_host.cu", "pk_scan.cuh", "pk_build.cuh", "pk_clubs.cuh", "pk_layout.h"]
+DEPS = ["pk_host.cu", "pk_scan.cuh", "pk_prefilter.cuh", "pk_build.cuh", "pk_clubs.cuh", "pk_layout.h"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     # the reference is built for baseline x86-64: separately rounded multiply and add
@@ -30,6 +30,22 @@ def _stale() -> bool:
     t = os.path.getmtime(LIB)
     deps = [os.path.join(CSRC, d) for d in DEPS] + [os.path.join(ROOT, "include", h) for h in ("pokec_b200.h", "pokec_world.h")]
     return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build_variant(name: str, defines) -> str:
+    """an experimental build (extra -D flags) next to the product library: libpokec_b200.<name>.so, selected at
+    run time with POKEC_B200_LIB (engine.load_library)"""
+    out = os.path.join(HERE, f"libpokec_b200.{name}.so")
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + [f"-D{d}" for d in defines] + ["-I", os.path.join(ROOT, "include"), "-I", CSRC] + \
+          [os.path.join(CSRC, s) for s in SOURCES] + ["-o", out]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        sys.stderr.write(res.stdout + res.stderr)
+        raise RuntimeError(f"nvcc failed building {out}")
+    with open(os.path.join(HERE, f"ptxas_info.{name}.txt"), "w") as f:
+        f.write(res.stderr)
+    return out
 
 
 def build(force: bool = False, verbose: bool = False) -> str:

@@ -777,7 +777,19 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
     // (the whole scan without the pre-filter; with it, only the CTAs of groups that failed the shortlist check run)
     int sm_count = 148;
     cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, s->device);
-    int64_t splits = (int64_t)(sm_count * 6 + ng - 1) / ng;
+    // one CTA per SM (shared memory holds one group's tables): the grid runs in waves of sm_count CTAs, so pick the
+    // split count (>= ~6 waves for balance) whose last wave is fullest -- 128 groups x 7 slices = 896 CTAs would
+    // leave the 7th wave 5 % full and cost 13 % of the launch, 128 x 8 = 1024 fills 6.92 waves
+    int64_t splits = 1;
+    {
+        const int64_t lo = std::max<int64_t>(1, ((int64_t)sm_count * 6 + ng - 1) / ng), hi = 2 * lo + 1;
+        double best = -1.0;
+        for (int64_t sp = lo; sp <= hi; ++sp) {
+            const int64_t ctas = sp * ng, waves = (ctas + sm_count - 1) / sm_count;
+            const double eff = (double)ctas / (double)(waves * sm_count);
+            if (eff > best + 1e-9) { best = eff; splits = sp; }
+        }
+    }
     splits = std::max<int64_t>(1, std::min<int64_t>(splits, (n_cand + 1023) / 1024));
     if (splits > 128 * 8) splits = 128 * 8;
     std::vector<WorkItem> items;

@@ -81,6 +81,17 @@ __device__ __forceinline__ float lean_sigma(float4 c, float s) {
     return r;
 }
 
+// 32 x 32 bit transpose across the warp: bit j of the result in lane l = bit l of x in lane j
+__device__ __forceinline__ uint32_t transpose32(uint32_t x, int lane) {
+    #pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) {
+        const uint32_t lo = (s == 16) ? 0x0000ffffu : (s == 8) ? 0x00ff00ffu : (s == 4) ? 0x0f0f0f0fu : (s == 2) ? 0x33333333u : 0x55555555u;
+        const uint32_t y = __shfl_xor_sync(kFull, x, s);
+        x = (lane & s) ? ((x & ~lo) | ((y >> s) & lo)) : ((x & lo) | ((y << s) & ~lo));
+    }
+    return x;
+}
+
 template <bool STORE>
 __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const PreParams P) {
     extern __shared__ uint4 smem_u4[];
@@ -201,6 +212,10 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                     uint32_t m = 0;
                     if (i < c_n) m = probe_set(tab, lg, __ldg(cw + eo + i));
                     uint32_t hits = __ballot_sync(kFull, m != 0u);
+                    if (__popc(hits) > 4) {                           // many shared elements: count my bit column-wise
+                        inter += __popc(transpose32(m, lane));
+                        hits = 0u;
+                    }
                     while (hits) {
                         const int j = __ffs(hits) - 1;
                         hits &= hits - 1;
@@ -222,7 +237,7 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                 const uint32_t* keys = cw + o_keys;
                 const float* tokw = reinterpret_cast<const float*>(cw + o_w);
                 float acc = 0.f;
-                int cur = -1;                                         // warp-uniform: column of the open cell
+                int cur = -1;                                         // per lane: column of the open cell of MY query
                 for (uint32_t cb = 0; cb < c_ntok; cb += 32) {
                     const uint32_t i = cb + lane;
                     uint32_t m = 0, slot = 0, key = 0;
@@ -237,24 +252,25 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                             slot = (slot + 1) & msk;
                         }
                     }
-                    uint32_t hitb = __ballot_sync(kFull, m != 0u);
-                    if (hitb == 0u) continue;
+                    if (__ballot_sync(kFull, m != 0u) == 0u) continue;
                     if (m) stage[lane] = make_uint4(m, t_base[slot], __float_as_uint(__ldg(tokw + i)), key >> kTokBits);
+                    // bit j of `mine` = "token j of this chunk belongs to MY query": each lane walks only its own hits
+                    uint32_t mine = transpose32(m, lane);
                     __syncwarp();
-                    while (hitb) {
-                        const int j = __ffs(hitb) - 1;
-                        hitb &= hitb - 1;
+                    while (mine) {
+                        const int j = __ffs(mine) - 1;
+                        mine &= mine - 1;
                         const uint4 h = stage[j];
                         if ((int)h.w != cur) {
-                            if (cur >= 0 && acc != 0.f) { const float4 f = N->fld[kNumFixed + cur]; sum += lean_sigma(f, acc) - f.z; }
+                            if (acc != 0.f) { const float4 f = N->fld[kNumFixed + cur]; sum += lean_sigma(f, acc) - f.z; }
                             acc = 0.f;
                             cur = (int)h.w;
                         }
-                        if (h.x & lanebit) acc = fmaf(vals[h.y + __popc(h.x & lane_lt)], __uint_as_float(h.z), acc);
+                        acc = fmaf(vals[h.y + __popc(h.x & lane_lt)], __uint_as_float(h.z), acc);
                     }
                     __syncwarp();
                 }
-                if (cur >= 0 && acc != 0.f) { const float4 f = N->fld[kNumFixed + cur]; sum += lean_sigma(f, acc) - f.z; }
+                if (acc != 0.f) { const float4 f = N->fld[kNumFixed + cur]; sum += lean_sigma(f, acc) - f.z; }
             }
 
             float fas = 0.f;

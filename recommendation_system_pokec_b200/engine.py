@@ -42,10 +42,12 @@ def load_library():
     """dlopen the in-tree CUDA library.  No fallback: a missing build is an error."""
     global _lib
     if _lib is None:
-        if not os.path.exists(LIB_PATH):
-            raise PokecError(f"{LIB_PATH} is missing: run `python -m recommendation_system_pokec_b200.build` "
+        # POKEC_B200_LIB: another build of the same CUDA library (kernel A/B experiments, tools/variants.py)
+        path = os.environ.get("POKEC_B200_LIB") or LIB_PATH
+        if not os.path.exists(path):
+            raise PokecError(f"{path} is missing: run `python -m recommendation_system_pokec_b200.build` "
                              "(there is no CPU implementation of the scoring path)")
-        lib = C.CDLL(LIB_PATH)
+        lib = C.CDLL(path)
         lib.pk_last_error.restype = C.c_char_p
         lib.pk_stat.restype = C.c_int64
         lib.pk_stat.argtypes = [C.c_void_p, C.c_int]
