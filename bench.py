@@ -37,8 +37,15 @@ METRIC = "query-users/sec, FAS top-50 full scan vs 1.63M users"
 UNIT = "query-users/s"
 
 
+_RESULT_FD = 1
+
+
 def log(*a):
     print(*a, file=sys.stderr, flush=True)
+
+
+def emit(obj):
+    os.write(_RESULT_FD, (json.dumps(obj) + "\n").encode())
 
 
 def measured_peak_hbm():
@@ -136,6 +143,12 @@ def cpu_reference_run(world, n_full, sample_users, q_per_thread, steps, warmup, 
 
 
 def main():
+    # stdout carries exactly ONE JSON line: libraries that print to fd 1 (NCCL's version banner under torchrun)
+    # are sent to stderr, the result line goes to a private copy of the original stdout
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
@@ -172,7 +185,7 @@ def main():
                "cpu_baseline": base,
                "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                "gpu_launches": 0}
-        print(json.dumps(out), flush=True)
+        emit(out)
         return 0
 
     # ------------------------------------------------------------------ our arm (CUDA)
@@ -305,7 +318,7 @@ def main():
         base, _ = cpu_reference_run(world, n, min(args.cpu_sample_users, n), 8, 1, 0, threads)
         out["cpu_baseline"] = base
     if rank == 0:
-        print(json.dumps(out), flush=True)
+        emit(out)
     if world_size > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -120,6 +120,7 @@ struct FullscanJob {
     DevBuf<WorkItem> pre_items, rr_items;
     DevBuf<uint64_t> keys_pre, keys_short, keys_rr;
     DevBuf<int32_t> q_group, q_flag, q_flag0, group_flag, group_flag0, short_rows, rr_slot0, rr_nl, pre_slot0, pre_nl;
+    DevBuf<int32_t> lean_fail;                // [group] the pre-filter's token table could not be built -> exact scan
 };
 
 struct pk_store {
@@ -496,10 +497,11 @@ void layout_group(pk_store* s, GroupDesc& g, const uint32_t* excl_n, bool with_l
     }
     g.log_sc = log2_table(ncl); g.log_sf = log2_table(nfr); g.log_sa = log2_table(nex); g.log_st = log2_table(ntok);
     uint32_t off = 0;
-    g.off_text2 = g.off_base = g.off_vals32 = 0;
+    g.off_text2 = g.off_base = g.off_vals32 = 0; g.log_cb = 0;
     if (with_lean) {
-        g.off_text2 = off; off += (8u << g.log_st);
-        g.off_base = off; off += (4u << g.log_st);
+        g.log_cb = std::max(1, g.log_st - 1);
+        g.off_text2 = off; off += (16u << g.log_cb);
+        g.off_base = off; off += align16((uint32_t)ntok * 8u);
         g.off_vals32 = off; off += align16((uint32_t)ntok * 4u);
     }
     g.exact_begin = off;
@@ -536,6 +538,7 @@ int upload_plan(pk_store* s, Plan& plan, bool with_excl) {
         PrepParams P;
         P.rec = s->d_rec.p; P.rec_off = s->d_rec_off.p; P.groups = s->d_groups.p; P.arena = s->d_arena.p;
         P.excl_ids = with_excl ? s->d_excl.p : nullptr;
+        P.lean_fail = nullptr;
         group_prep_kernel<<<(unsigned)plan.groups.size(), kPrepThreads, 0, s->stream>>>(P);
         ++s->stat_launches;
         CK(cudaGetLastError());
@@ -911,6 +914,12 @@ int fullscan_execute(pk_store* s) {
     PrepParams PP;
     PP.rec = s->d_rec.p; PP.rec_off = s->d_rec_off.p; PP.groups = J.groups.p; PP.arena = J.arena.p;
     PP.excl_ids = J.with_excl ? J.excl.p : nullptr;
+    PP.lean_fail = nullptr;
+    if (J.lean) {
+        TRY(J.lean_fail.reserve((size_t)J.n_groups));
+        CK(cudaMemsetAsync(J.lean_fail.p, 0, (size_t)J.n_groups * 4, s->stream));
+        PP.lean_fail = J.lean_fail.p;
+    }
     group_prep_kernel<<<(unsigned)J.n_groups, kPrepThreads, 0, s->stream>>>(PP);
     ++s->stat_launches;
     CK(cudaGetLastError());
@@ -953,7 +962,7 @@ int fullscan_execute(pk_store* s) {
     ++s->stat_launches;
     CheckParams C;
     C.short_keys = J.keys_short.p; C.q_group = J.q_group.p; C.q_lane = J.q_lane.p; C.cand_rows = J.short_rows.p;
-    C.q_flag = J.q_flag.p; C.group_flag = J.group_flag.p; C.nq = J.nq; C.K = J.K; C.Ks = Ks; C.margin = s->margin;
+    C.q_flag = J.q_flag.p; C.group_flag = J.group_flag.p; C.lean_fail = J.lean_fail.p; C.nq = J.nq; C.K = J.K; C.Ks = Ks; C.margin = s->margin;
     shortlist_check_kernel<<<J.nq, 64, 0, s->stream>>>(C);
     ++s->stat_launches;
     CK(cudaGetLastError());

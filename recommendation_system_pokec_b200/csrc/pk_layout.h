@@ -102,7 +102,11 @@ struct GroupDesc {
     uint32_t n_vals;
     // the block is laid out [lean-only | shared set tables | exact-only]: the pre-filter stages
     // [0, lean_end), the exact kernel [exact_begin, arena_bytes)
-    uint32_t off_text2, off_base, off_vals32;   // lean-only: {key, mask} slots, first value index per slot, normalised weights
+    // lean-only: the pre-filter's token table -- a 2-choice cuckoo table of 2^log_cb buckets x 2 slots {key, entry + 1}
+    // (off_text2; probed with two independent 128-bit loads, no probe loop), the entries {query mask, first value index}
+    // (off_base) and the normalised fp32 weights (off_vals32)
+    uint32_t off_text2, off_base, off_vals32;
+    int32_t log_cb;
     uint32_t lean_end, exact_begin;
     int32_t lean_in_smem;
     int32_t adj_begin[kLanes + 1];   // slice of the per-batch exclusion id array for each lane

@@ -87,7 +87,12 @@ __device__ __forceinline__ uint32_t transpose32(uint32_t x, int lane) {
     for (int s = 16; s >= 1; s >>= 1) {
         const uint32_t lo = (s == 16) ? 0x0000ffffu : (s == 8) ? 0x00ff00ffu : (s == 4) ? 0x0f0f0f0fu : (s == 2) ? 0x33333333u : 0x55555555u;
         const uint32_t y = __shfl_xor_sync(kFull, x, s);
-        x = (lane & s) ? ((x & ~lo) | ((y >> s) & lo)) : ((x & lo) | ((y << s) & ~lo));
+        // upper half of a 2s x 2s block keeps its low columns and takes the partner's shifted up by s (lower half:
+        // the mirror image).  A rotate serves both shifts: the wrapped bits fall into the kept columns and are masked.
+        const bool up = (lane & s) != 0;
+        const uint32_t keep = up ? ~lo : lo;
+        const uint32_t rot = __funnelshift_l(y, y, up ? 32 - s : s);
+        x = (x & keep) | (rot & ~keep);
     }
     return x;
 }
@@ -123,13 +128,13 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
     }
     __syncthreads();
 
-    const uint2* t_text = reinterpret_cast<const uint2*>(smem + gd->off_text2);
-    const uint32_t* t_base = reinterpret_cast<const uint32_t*>(smem + gd->off_base);
+    const uint4* t_ck = reinterpret_cast<const uint4*>(smem + gd->off_text2);      // cuckoo buckets {key, entry+1} x 2
+    const uint2* t_ent = reinterpret_cast<const uint2*>(smem + gd->off_base);      // entries {query mask, first value}
     const float* vals = reinterpret_cast<const float*>(smem + gd->off_vals32);
     const uint2* t_clubs = reinterpret_cast<const uint2*>(smem + gd->off_clubs);
     const uint2* t_friends = reinterpret_cast<const uint2*>(smem + gd->off_friends);
     const uint2* t_adj = reinterpret_cast<const uint2*>(smem + gd->off_adj);
-    const int log_sc = gd->log_sc, log_sf = gd->log_sf, log_sa = gd->log_sa, log_st = gd->log_st;
+    const int log_sc = gd->log_sc, log_sf = gd->log_sf, log_sa = gd->log_sa, log_cb = gd->log_cb;
 
     // ---- this lane's query ----------------------------------------------------------------------
     const int qrow = (lane < gd->n_lanes) ? gd->row[lane] : -1;
@@ -149,7 +154,11 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
     const int dim_comp = N->dim_comp, dim_age = N->dim_age;
     const float inv_total = N->inv_total;
 
+#ifdef PK_PRE_CHUNK
+    constexpr int kChunk = PK_PRE_CHUNK;
+#else
     constexpr int kChunk = 4;
+#endif
     for (;;) {
         int c0 = 0;
         if (lane == 0) c0 = atomicAdd(next, kChunk);
@@ -161,6 +170,13 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
         for (int ci = c0; ci < c1; ++ci) {
             const uint64_t off = __shfl_sync(kFull, offv, ci - c0);
             const uint4* cr = P.lrec + off;
+#ifdef PK_PREFETCH_L1
+            {   // pull the next record of the chunk (<= PK_PREFETCH_L1 lines of 128 B) into L1 while this one is scored
+                const uint64_t offn = __shfl_sync(kFull, offv, (ci + 1 - c0) & 31);
+                if (ci + 1 < c1 && lane < PK_PREFETCH_L1)
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(P.lrec + offn + lane * 8));
+            }
+#endif
             const uint32_t* cw = reinterpret_cast<const uint32_t*>(cr);
             const uint4 h0 = __ldg(cr), h1 = __ldg(cr + 1), h2 = __ldg(cr + 2), h3 = __ldg(cr + 3);
             const int c_uid = (int)h0.x, c_pub = (int)h0.y, c_gender = (int)h0.z, c_comp = (int)h0.w;
@@ -240,20 +256,21 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                 int cur = -1;                                         // per lane: column of the open cell of MY query
                 for (uint32_t cb = 0; cb < c_ntok; cb += 32) {
                     const uint32_t i = cb + lane;
-                    uint32_t m = 0, slot = 0, key = 0;
+                    uint32_t m = 0, id = 0, key = 0;
                     if (i < c_ntok) {
+                        // 2-choice cuckoo probe: both buckets are read unconditionally (two independent LDS.128), a key
+                        // lives in at most one slot and empty slots carry entry 0, so the matches can simply be OR-ed
                         key = __ldg(keys + i);
-                        const uint32_t msk = (1u << log_st) - 1u;
-                        slot = hash_u32(key, log_st);
-                        for (;;) {
-                            const uint2 e = t_text[slot];
-                            if (e.y == 0u) break;
-                            if (e.x == key) { m = e.y; break; }
-                            slot = (slot + 1) & msk;
-                        }
+                        const uint4 e1 = t_ck[hash_u32(key, log_cb)], e2 = t_ck[hash2_u32(key, log_cb)];
+                        id = ((e1.x == key) ? e1.y : 0u) | ((e1.z == key) ? e1.w : 0u) | ((e2.x == key) ? e2.y : 0u) |
+                             ((e2.z == key) ? e2.w : 0u);
                     }
-                    if (__ballot_sync(kFull, m != 0u) == 0u) continue;
-                    if (m) stage[lane] = make_uint4(m, t_base[slot], __float_as_uint(__ldg(tokw + i)), key >> kTokBits);
+                    if (__ballot_sync(kFull, id != 0u) == 0u) continue;
+                    if (id) {
+                        const uint2 en = t_ent[id - 1u];
+                        m = en.x;
+                        stage[lane] = make_uint4(m, en.y, __float_as_uint(__ldg(tokw + i)), key >> kTokBits);
+                    }
                     // bit j of `mine` = "token j of this chunk belongs to MY query": each lane walks only its own hits
                     uint32_t mine = transpose32(m, lane);
                     __syncwarp();
@@ -324,6 +341,7 @@ struct CheckParams {
     int32_t* cand_rows;           // [(group*32 + lane)*Ks + i], -1 = empty
     int32_t* q_flag;              // preset by the host (groups the pre-filter cannot take); OR-ed here
     int32_t* group_flag;
+    const int32_t* lean_fail;     // [group] the group's pre-filter table was not built (group_prep_kernel): nothing is proven
     int nq, K, Ks;
     float margin;
 };
@@ -346,6 +364,7 @@ __global__ void shortlist_check_kernel(const CheckParams P) {
             const float a_k = __uint_as_float(key_score_bits(keys[P.K - 1]));
             complete = a_last < a_k - 2.0f * P.margin - 1e-7f;
         }
+        if (P.lean_fail[g]) complete = false;
         if (!complete) { P.q_flag[q] = 1; atomicOr(P.group_flag + g, 1); }
     }
 }

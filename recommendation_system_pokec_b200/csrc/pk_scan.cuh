@@ -51,12 +51,36 @@ __device__ __forceinline__ void table_insert(unsigned long long* slot0, uint32_t
     }
 }
 
+// Second hash of the pre-filter's 2-choice token table (the first is hash_u32).
+__device__ __forceinline__ uint32_t hash2_u32(uint32_t key, int log_size) {
+    return ((key ^ (key >> 15)) * 0x85EBCA6Bu) >> (32 - log_size);
+}
+
+// Concurrent cuckoo insertion of {key, val} (val != 0) into 2^log_nb buckets of two 64-bit slots; a slot is
+// empty iff it is 0.  Every thread always holds exactly one homeless item, so concurrent evictions lose nothing.
+// Returns false when the eviction chain does not end (the caller then routes the group to the exact scan).
+__device__ __forceinline__ bool cuckoo_insert(unsigned long long* tab, int log_nb, uint32_t key, uint32_t val) {
+    unsigned long long cur = (unsigned long long)key | ((unsigned long long)val << 32);
+    uint32_t b = hash_u32(key, log_nb);
+    for (int it = 0; it < 256; ++it) {
+        unsigned long long* p = tab + 2 * (size_t)b;
+        if (atomicCAS(p, 0ull, cur) == 0ull) return true;
+        if (atomicCAS(p + 1, 0ull, cur) == 0ull) return true;
+        cur = atomicExch(p + (it & 1), cur);
+        const uint32_t k = (uint32_t)cur;
+        const uint32_t a = hash_u32(k, log_nb), c = hash2_u32(k, log_nb);
+        b = (b == a) ? c : a;
+    }
+    return false;
+}
+
 struct PrepParams {
     const uint4* rec;
     const uint64_t* rec_off;
     const GroupDesc* groups;
     uint8_t* arena;               // zero-filled by the host before the launch
     const int32_t* excl_ids;      // per-batch exclusion ids (adjacency rows of the queries), may be null
+    int32_t* lean_fail;           // [group] set to 1 when the pre-filter's cuckoo table could not be built (may be null)
 };
 
 // one CTA per group
@@ -95,8 +119,8 @@ __global__ void __launch_bounds__(kPrepThreads) group_prep_kernel(const PrepPara
 
     // phase 2: base[slot] = exclusive prefix sum of popc(mask) over the text table
     __shared__ uint32_t warp_sums[kPrepThreads / 32];
-    __shared__ uint32_t running;
-    if (tid == 0) running = 0;
+    __shared__ uint32_t running, n_ent;
+    if (tid == 0) { running = 0; n_ent = 0; }
     __syncthreads();
     const uint32_t st = 1u << gd.log_st;
     uint32_t* t_text32 = reinterpret_cast<uint32_t*>(t_text);
@@ -143,17 +167,18 @@ __global__ void __launch_bounds__(kPrepThreads) group_prep_kernel(const PrepPara
         }
     }
 
-    // phase 4 (full scan only): the pre-filter's fp32 view of the text table -- {key, mask} slots, the first
-    // value index of each slot, and the weights divided by the query cell's L2 norm
+    // phase 4 (full scan only): the pre-filter's fp32 view of the text table -- a cuckoo table {key, entry + 1}, the
+    // entries {mask, first value index}, and the weights divided by the query cell's L2 norm
     if (gd.exact_begin == 0) return;
     __syncthreads();
-    uint2* t2 = reinterpret_cast<uint2*>(base + gd.off_text2);
-    uint32_t* tbase = reinterpret_cast<uint32_t*>(base + gd.off_base);
+    unsigned long long* ck = reinterpret_cast<unsigned long long*>(base + gd.off_text2);
+    uint2* ent = reinterpret_cast<uint2*>(base + gd.off_base);
     float* v32 = reinterpret_cast<float*>(base + gd.off_vals32);
     for (uint32_t sl = tid; sl < st; sl += kPrepThreads) {
         const uint32_t key = t_text32[4 * sl], m2 = t_text32[4 * sl + 1], b0 = t_text32[4 * sl + 2];
-        t2[sl] = make_uint2(key, m2);
-        tbase[sl] = b0;
+        if (m2 == 0u) continue;
+        const uint32_t idx = atomicAdd(&n_ent, 1u);
+        ent[idx] = make_uint2(m2, b0);
         const uint32_t ct = key >> kTokBits;
         uint32_t mm = m2, r = 0;
         while (mm) {
@@ -163,6 +188,7 @@ __global__ void __launch_bounds__(kPrepThreads) group_prep_kernel(const PrepPara
             v32[b0 + r] = (nrm > 0.0) ? (float)(vals[b0 + r] / nrm) : 0.0f;
             ++r;
         }
+        if (!cuckoo_insert(ck, gd.log_cb, key, idx + 1u) && P.lean_fail) P.lean_fail[blockIdx.x] = 1;
     }
 }
 
