@@ -175,6 +175,7 @@ struct pk_store {
     int64_t shard_begin = 0, shard_end = 0;
     // lean fp32 records of the pre-filter
     bool lean_dirty = true, tf_negative = false;
+    bool wide_ids = false;   // a club / friend id >= 2^31: the pre-filter's combined set table cannot tag it
     DevBuf<uint4> d_lrec;
     DevBuf<uint64_t> d_lrec_off;
     uint64_t lean_u4 = 0;
@@ -497,19 +498,22 @@ void layout_group(pk_store* s, GroupDesc& g, const uint32_t* excl_n, bool with_l
     }
     g.log_sc = log2_table(ncl); g.log_sf = log2_table(nfr); g.log_sa = log2_table(nex); g.log_st = log2_table(ntok);
     uint32_t off = 0;
-    g.off_text2 = g.off_base = g.off_vals32 = 0; g.log_cb = 0;
+    g.off_text2 = g.off_base = g.off_vals32 = g.off_sets2 = 0; g.log_cb = g.log_cs = 0;
     if (with_lean) {
         g.log_cb = std::max(1, g.log_st - 1);
         g.off_text2 = off; off += (16u << g.log_cb);
         g.off_base = off; off += align16((uint32_t)ntok * 8u);
         g.off_vals32 = off; off += align16((uint32_t)ntok * 4u);
+        g.log_cs = std::max(1, log2_table(ncl + nfr) - 1);
+        g.off_sets2 = off; off += (16u << g.log_cs);
     }
     g.exact_begin = off;
-    g.off_clubs = off; off += (8u << g.log_sc);
-    g.off_friends = off; off += (8u << g.log_sf);
     g.off_adj = off; off += (8u << g.log_sa);
     off = align16(off);
     g.lean_end = with_lean ? off : 0u;
+    g.off_clubs = off; off += (8u << g.log_sc);
+    g.off_friends = off; off += (8u << g.log_sf);
+    off = align16(off);
     g.off_nq = off; off += align16((uint32_t)s->T * 32u * 8u);
     g.off_text = off; off += (16u << g.log_st);
     g.off_vals = off; off += align16((uint32_t)ntok * 8u);
@@ -687,7 +691,7 @@ int check_topk_args(pk_store* s, int nq, const int32_t* q_uid, int k) {
 bool lean_usable(pk_store* s, int K, int* Ks_out) {
     const char* e = getenv("POKEC_B200_NO_PREFILTER");
     if (e && e[0] == '1') return false;
-    if (s->tf_negative) return false;
+    if (s->tf_negative || s->wide_ids) return false;
     for (int t = 0; t < s->T; ++t)
         if (s->col_state[t] == 2)
             for (float v : s->custom_idf[t]) if (!(v >= 0.0f)) return false;   // negative weights break the error bound
@@ -1544,6 +1548,9 @@ int pk_store_load_world(pk_store* s, const pk_world* w) {
     }
     s->n = n; s->T = T; s->nnz = nnz;
     s->tf_negative = tf_negative;
+    s->wide_ids = false;
+    for (int64_t j = 0, e = w->clubs_ptr[n]; j < e && !s->wide_ids; ++j) s->wide_ids = (w->clubs[j] >> 31) != 0;
+    for (int64_t j = 0, e = w->friends_ptr[n]; j < e && !s->wide_ids; ++j) s->wide_ids = (w->friends[j] >> 31) != 0;
     s->uid.assign(w->uid, w->uid + n);
     s->uid_sorted.resize(n);
     for (int i = 0; i < n; ++i) s->uid_sorted[i] = {w->uid[i], i};

@@ -100,13 +100,17 @@ struct GroupDesc {
     int32_t log_sc, log_sf, log_sa, log_st;        // log2 sizes of clubs / friends / adjacency / text tables
     uint32_t off_nq, off_clubs, off_friends, off_adj, off_text, off_vals;   // byte offsets inside the arena block
     uint32_t n_vals;
-    // the block is laid out [lean-only | shared set tables | exact-only]: the pre-filter stages
+    // the block is laid out [lean-only | exclusion table | exact-only]: the pre-filter stages
     // [0, lean_end), the exact kernel [exact_begin, arena_bytes)
     // lean-only: the pre-filter's token table -- a 2-choice cuckoo table of 2^log_cb buckets x 2 slots {key, entry + 1}
     // (off_text2; probed with two independent 128-bit loads, no probe loop), the entries {query mask, first value index}
     // (off_base) and the normalised fp32 weights (off_vals32)
     uint32_t off_text2, off_base, off_vals32;
     int32_t log_cb;
+    // lean-only: clubs and friends of the group's queries in ONE cuckoo table {id | set << 31, query mask}
+    // (set 0 = clubs, 1 = friends; ids are < 2^31), 2^log_cs buckets x 2 slots
+    uint32_t off_sets2;
+    int32_t log_cs;
     uint32_t lean_end, exact_begin;
     int32_t lean_in_smem;
     int32_t adj_begin[kLanes + 1];   // slice of the per-batch exclusion id array for each lane

@@ -131,10 +131,9 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
     const uint4* t_ck = reinterpret_cast<const uint4*>(smem + gd->off_text2);      // cuckoo buckets {key, entry+1} x 2
     const uint2* t_ent = reinterpret_cast<const uint2*>(smem + gd->off_base);      // entries {query mask, first value}
     const float* vals = reinterpret_cast<const float*>(smem + gd->off_vals32);
-    const uint2* t_clubs = reinterpret_cast<const uint2*>(smem + gd->off_clubs);
-    const uint2* t_friends = reinterpret_cast<const uint2*>(smem + gd->off_friends);
+    const uint4* t_sets = reinterpret_cast<const uint4*>(smem + gd->off_sets2);     // clubs + friends, cuckoo buckets
     const uint2* t_adj = reinterpret_cast<const uint2*>(smem + gd->off_adj);
-    const int log_sc = gd->log_sc, log_sf = gd->log_sf, log_sa = gd->log_sa, log_cb = gd->log_cb;
+    const int log_cs = gd->log_cs, log_sa = gd->log_sa, log_cb = gd->log_cb;
 
     // ---- this lane's query ----------------------------------------------------------------------
     const int qrow = (lane < gd->n_lanes) ? gd->row[lane] : -1;
@@ -157,7 +156,7 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
 #ifdef PK_PRE_CHUNK
     constexpr int kChunk = PK_PRE_CHUNK;
 #else
-    constexpr int kChunk = 4;
+    constexpr int kChunk = 8;
 #endif
     for (;;) {
         int c0 = 0;
@@ -214,37 +213,38 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                 ++used;
             }
 
-            // clubs / friends (:79-91)
-            #pragma unroll
-            for (int which = 0; which < 2; ++which) {
-                const uint32_t c_n = which ? c_nfr : c_ncl;
-                if (c_n == 0) continue;                               // warp-uniform
-                const uint32_t eo = which ? o_friends : o_clubs;
-                const uint2* tab = which ? t_friends : t_clubs;
-                const int lg = which ? log_sf : log_sc;
-                int inter = 0;
-                for (uint32_t e0 = 0; e0 < c_n; e0 += 32) {
+            // clubs / friends (:79-91): the record stores them back to back ([clubs padded to 4 | friends]) and the
+            // group's table holds both sets ({id | set << 31, query mask}), so one round of <= 32 elements usually
+            // covers both; a transpose of the hit masks gives every lane the hits of ITS query, counted by popc
+            if (c_ncl + c_nfr > 0) {
+                const uint32_t pcl = pad4(c_ncl), n_el = pcl + c_nfr;
+                int inter_c = 0, inter_f = 0;
+                for (uint32_t e0 = 0; e0 < n_el; e0 += 32) {
                     const uint32_t i = e0 + lane;
+                    const bool is_fr = i >= pcl;
                     uint32_t m = 0;
-                    if (i < c_n) m = probe_set(tab, lg, __ldg(cw + eo + i));
-                    uint32_t hits = __ballot_sync(kFull, m != 0u);
-                    if (__popc(hits) > 4) {                           // many shared elements: count my bit column-wise
-                        inter += __popc(transpose32(m, lane));
-                        hits = 0u;
+                    if (is_fr ? (i < n_el) : (i < c_ncl)) {
+                        const uint32_t key = __ldg(cw + o_clubs + i) | (is_fr ? 0x80000000u : 0u);
+                        const uint4 e1 = t_sets[hash_u32(key, log_cs)], e2 = t_sets[hash2_u32(key, log_cs)];
+                        m = ((e1.x == key) ? e1.y : 0u) | ((e1.z == key) ? e1.w : 0u) | ((e2.x == key) ? e2.y : 0u) |
+                            ((e2.z == key) ? e2.w : 0u);
                     }
-                    while (hits) {
-                        const int j = __ffs(hits) - 1;
-                        hits &= hits - 1;
-                        const uint32_t mj = __shfl_sync(kFull, m, j);
-                        inter += (mj & lanebit) ? 1 : 0;
-                    }
+                    if (__ballot_sync(kFull, m != 0u) == 0u) continue;
+                    const uint32_t mine = transpose32(m, lane);
+                    const uint32_t ncl_here = (pcl > e0) ? min(pcl - e0, 32u) : 0u;           // warp-uniform
+                    const uint32_t cmask = (ncl_here >= 32u) ? 0xffffffffu : ((1u << ncl_here) - 1u);
+                    inter_c += __popc(mine & cmask);
+                    inter_f += __popc(mine & ~cmask);
                 }
-                const uint32_t q_n = which ? q_nfr : q_ncl;
-                if (q_n > 0) {
-                    const float4 f = N->fld[5 + which];
-                    float sg = f.z;
-                    if (inter > 0) sg = lean_sigma(f, (float)inter * (which ? q_rsf : q_rsc) * __uint_as_float(which ? h3.w : h3.z));
-                    sum += sg; ++used;
+                if (c_ncl > 0 && q_ncl > 0) {
+                    const float4 f = N->fld[5];
+                    sum += (inter_c > 0) ? lean_sigma(f, (float)inter_c * q_rsc * __uint_as_float(h3.z)) : f.z;
+                    ++used;
+                }
+                if (c_nfr > 0 && q_nfr > 0) {
+                    const float4 f = N->fld[6];
+                    sum += (inter_f > 0) ? lean_sigma(f, (float)inter_f * q_rsf * __uint_as_float(h3.w)) : f.z;
+                    ++used;
                 }
             }
 

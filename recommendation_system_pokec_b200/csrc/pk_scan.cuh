@@ -190,6 +190,19 @@ __global__ void __launch_bounds__(kPrepThreads) group_prep_kernel(const PrepPara
         }
         if (!cuckoo_insert(ck, gd.log_cb, key, idx + 1u) && P.lean_fail) P.lean_fail[blockIdx.x] = 1;
     }
+    // clubs and friends of the queries in one cuckoo table: {id | set << 31, query mask}
+    unsigned long long* cks = reinterpret_cast<unsigned long long*>(base + gd.off_sets2);
+    for (int which = 0; which < 2; ++which) {
+        const unsigned long long* src = which ? t_friends : t_clubs;
+        const uint32_t ns = 1u << (which ? gd.log_sf : gd.log_sc);
+        for (uint32_t sl = tid; sl < ns; sl += kPrepThreads) {
+            const unsigned long long e = src[sl];
+            const uint32_t m2 = (uint32_t)(e >> 32);
+            if (m2 == 0u) continue;
+            if (!cuckoo_insert(cks, gd.log_cs, (uint32_t)e | ((uint32_t)which << 31), m2) && P.lean_fail)
+                P.lean_fail[blockIdx.x] = 1;
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
