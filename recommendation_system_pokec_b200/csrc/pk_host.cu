@@ -10,6 +10,8 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
+#include <thread>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -206,7 +208,15 @@ struct pk_store {
     // ---- stats ------------------------------------------------------------------------------------
     int64_t stat_launches = 0, stat_pairs = 0, stat_scan_ns = 0, stat_scan_launches = 0, stat_groups = 0;
 
+    // direct uid -> row / adjacency-row maps (built when the uid range is at most a few times the user count):
+    // candidate enumeration does one such lookup per neighbour, a binary search over 1.6 M uids costs ~1 us each
+    int32_t uid_lo = 0;
+    std::vector<int32_t> row_direct, adj_direct;
     int row_of(int32_t u) const {
+        if (!row_direct.empty()) {
+            const int64_t i = (int64_t)u - uid_lo;
+            return (i >= 0 && i < (int64_t)row_direct.size()) ? row_direct[(size_t)i] : -1;
+        }
         auto it = std::lower_bound(uid_sorted.begin(), uid_sorted.end(), std::make_pair(u, INT32_MIN));
         if (it == uid_sorted.end() || it->first != u) return -1;
         return it->second;
@@ -220,6 +230,14 @@ struct pk_store {
                 *e = io->second.data() + io->second.size();
                 return true;
             }
+        }
+        if (!adj_direct.empty()) {
+            const int64_t i = (int64_t)u - uid_lo;
+            const int32_t r = (i >= 0 && i < (int64_t)adj_direct.size()) ? adj_direct[(size_t)i] : -1;
+            if (r < 0) return false;
+            *b = adj.data() + adj_ptr[r];
+            *e = adj.data() + adj_ptr[r + 1];
+            return true;
         }
         auto it = adj_row.find(u);
         if (it == adj_row.end()) return false;
@@ -1010,6 +1028,28 @@ int fullscan_fetch(pk_store* s, int32_t* out_id, float* out_score, int32_t* out_
     return PK_OK;
 }
 
+// Host threads for the per-user candidate enumeration of a batch (each user is independent; the store is only
+// read).  POKEC_B200_HOST_THREADS overrides the count (1 = the calling thread only).
+template <class F>
+void parallel_for(int n, F fn) {
+    int nt = (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 32u);
+    if (const char* e = getenv("POKEC_B200_HOST_THREADS")) nt = std::max(1, atoi(e));
+    nt = std::min(nt, (n + 15) / 16);
+    if (nt <= 1) { for (int i = 0; i < n; ++i) fn(i); return; }
+    std::atomic<int> next{0};
+    auto work = [&]() {
+        for (;;) {
+            const int i0 = next.fetch_add(16);
+            if (i0 >= n) break;
+            for (int i = i0, e = std::min(n, i0 + 16); i < e; ++i) fn(i);
+        }
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < nt; ++t) th.emplace_back(work);
+    work();
+    for (auto& t : th) t.join();
+}
+
 // ---- candidate enumeration on the host (integer, order-sensitive; mirrors the reference) -----------
 
 // src/recommender_graph.cpp:10-31
@@ -1068,25 +1108,35 @@ int recommend_graph(pk_store* s, int nq, const int32_t* q_uid, int k, int limit,
     std::vector<int32_t> cand_rows;
     std::vector<WorkItem> items;
     std::vector<int32_t> q_slot0(nq, 0), q_nl(nq, 0), q_lane(nq, 0);
-    std::vector<int32_t> cands;
-    for (int q = 0; q < nq; ++q) {
+    // phase 1 (host threads): the candidate rows of every query, in the reference's order
+    std::vector<std::vector<int32_t>> q_rows((size_t)nq);
+    std::vector<int32_t> q_row((size_t)nq, -1);
+    parallel_for(nq, [&](int q) {
         const int32_t user = q_uid[q];
         const int r = s->row_of(user);
-        if (r < 0) continue;                                    // src/recommender_graph.cpp:40
+        q_row[q] = r;
+        if (r < 0) return;                                      // src/recommender_graph.cpp:40
+        std::vector<int32_t> cands;
         gather_candidates(s, user, limit, cands);
         std::unordered_set<int32_t> existing;                   // :46-49
         const int32_t *b, *e;
         if (s->adj_of(user, &b, &e)) existing.insert(b, e);
         existing.insert(user);
-        const int32_t c0 = (int32_t)cand_rows.size();
+        std::vector<int32_t>& out = q_rows[q];
         for (int32_t c : cands) {
             if (existing.count(c)) continue;
             const int rc = s->row_of(c);
             if (rc < 0) continue;                               // :54
-            cand_rows.push_back(rc);
+            out.push_back(rc);
         }
+    });
+    // phase 2: one single-lane group and one work item per query
+    for (int q = 0; q < nq; ++q) {
+        const int r = q_row[q];
+        if (r < 0 || q_rows[q].empty()) continue;
+        const int32_t c0 = (int32_t)cand_rows.size();
+        cand_rows.insert(cand_rows.end(), q_rows[q].begin(), q_rows[q].end());
         const int32_t c1 = (int32_t)cand_rows.size();
-        if (c1 == c0) continue;
         GroupDesc g = empty_group();
         g.n_lanes = 1; g.row[0] = r; g.qidx[0] = q;
         WorkItem it;
@@ -1148,11 +1198,12 @@ struct CollabUser {
 int collab_prepare(pk_store* s, int nq, const int32_t* q_uid, int limit, bool limited, std::vector<CollabUser>& users,
                    Plan& plan, std::vector<WorkItem>& items, std::vector<int32_t>& cand_rows, int64_t* out_rows) {
     int64_t rows = 0;
-    std::vector<int32_t> tmp;
-    for (int q = 0; q < nq; ++q) {
-        CollabUser u;
+    // phase 1 (host threads): friends, distinct-friend slots and the ordered candidate list of every user
+    std::vector<CollabUser> all((size_t)nq);
+    parallel_for(nq, [&](int q) {
+        CollabUser& u = all[q];
         u.q = q; u.uid = q_uid[q]; u.row = s->row_of(u.uid);
-        if (u.row < 0) continue;                                         // src/recommender_graph.cpp:130
+        if (u.row < 0) return;                                           // src/recommender_graph.cpp:130
         const int32_t *b, *e;
         if (s->adj_of(u.uid, &b, &e)) u.friends.assign(b, e);
         std::unordered_map<int32_t, int32_t> slot_of;
@@ -1163,6 +1214,7 @@ int collab_prepare(pk_store* s, int nq, const int32_t* q_uid, int limit, bool li
             if (ins.second) { u.slot_row.push_back(rf); u.slot_uid.push_back(f); }
             u.fr_slot.push_back(ins.first->second);
         }
+        std::vector<int32_t> tmp;
         collab_candidates(s, u.uid, u.friends.data(), u.friends.data() + u.friends.size(), limit, limited, tmp);
         for (int32_t c : tmp) {
             const int rc = s->row_of(c);
@@ -1170,6 +1222,11 @@ int collab_prepare(pk_store* s, int nq, const int32_t* q_uid, int limit, bool li
             u.cands.push_back(c);
             u.cand_row.push_back(rc);
         }
+    });
+    // phase 2: groups and work items, in caller order
+    for (int q = 0; q < nq; ++q) {
+        CollabUser& u = all[q];
+        if (u.row < 0) continue;
         const int nslots = (int)u.slot_row.size();
         if (nslots > 0) {
             // {user} x friends
@@ -1301,9 +1358,14 @@ int recommend_clubs(pk_store* s, int nq, const int32_t* q_uid, int k, uint64_t* 
         std::vector<ClubEdge> edges;
         std::vector<int32_t> ueb(nu + 1, 0), ucon(nu + 1, 0), urow(nu);
         std::vector<uint32_t> con_off;   // per edge: first contribution index (relative to the user)
-        for (int i = 0; i < nu; ++i) {
+        // phase 1 (host threads): every user's edge stream
+        std::vector<std::vector<ClubEdge>> u_edges((size_t)nu);
+        std::vector<std::vector<uint32_t>> u_con((size_t)nu);
+        std::vector<uint64_t> u_total((size_t)nu, 0);
+        parallel_for(nu, [&](int i) {
             const CollabUser& u = users[i];
-            urow[i] = u.row;
+            std::vector<ClubEdge>& ed = u_edges[i];
+            std::vector<uint32_t>& co = u_con[i];
             std::unordered_map<int32_t, int32_t> cand_idx;
             cand_idx.reserve(u.cands.size() * 2);
             for (size_t c = 0; c < u.cands.size(); ++c) cand_idx.emplace(u.cands[c], (int32_t)c);
@@ -1315,9 +1377,9 @@ int recommend_clubs(pk_store* s, int nq, const int32_t* q_uid, int k, uint64_t* 
                 if (sl < 0) continue;
                 ClubEdge e;
                 e.w_idx = w_index(sl); e.s_idx = -1; e.target_row = u.slot_row[sl];
-                con_off.push_back((uint32_t)con);
+                co.push_back((uint32_t)con);
                 con += s->h_ncl[e.target_row];
-                edges.push_back(e);
+                ed.push_back(e);
             }
             for (size_t fi = 0; fi < u.friends.size(); ++fi) {          // :45-64
                 const int sl = u.fr_slot[fi];
@@ -1332,12 +1394,23 @@ int recommend_clubs(pk_store* s, int nq, const int32_t* q_uid, int k, uint64_t* 
                     e.w_idx = w_index(sl);
                     e.s_idx = ((int64_t)u.mat_out0 + (int64_t)(sl >> 5) * ncand + ic->second) * 32 + (sl & 31);
                     e.target_row = u.cand_row[ic->second];
-                    con_off.push_back((uint32_t)con);
+                    co.push_back((uint32_t)std::min<uint64_t>(con, 0xffffffffull));
                     con += s->h_ncl[e.target_row];
-                    edges.push_back(e);
+                    ed.push_back(e);
                 }
             }
+            u_total[i] = con;
+        });
+        // phase 2: concatenate in user order
+        for (int i = 0; i < nu; ++i) {
+            urow[i] = users[i].row;
+            const uint64_t con = u_total[i];
             if (con > 0x7fffffffull) return fail(PK_ERR_UNSUPPORTED, "club contribution stream too large");
+            edges.insert(edges.end(), u_edges[i].begin(), u_edges[i].end());
+            con_off.insert(con_off.end(), u_con[i].begin(), u_con[i].end());
+            std::vector<ClubEdge>().swap(u_edges[i]);
+            std::vector<uint32_t>().swap(u_con[i]);
+            if (edges.size() > 0x7fffffffull) return fail(PK_ERR_UNSUPPORTED, "club batch too large (split the batch)");
             ueb[i + 1] = (int32_t)edges.size();
             // table capacity for the user's distinct clubs (power of two >= 2 * contributions)
             const int64_t capu = (int64_t)1 << log2_table(std::max<uint64_t>(con, 1));
@@ -1573,6 +1646,19 @@ int pk_store_load_world(pk_store* s, const pk_world* w) {
     s->adj_row.reserve((size_t)m * 2);
     for (int r = 0; r < m; ++r) s->adj_row[w->adj_uid[r]] = r;
     s->adj_override.clear();
+    s->row_direct.clear(); s->adj_direct.clear();
+    {
+        int64_t lo = INT64_MAX, hi = INT64_MIN;
+        for (int i = 0; i < n; ++i) { lo = std::min<int64_t>(lo, w->uid[i]); hi = std::max<int64_t>(hi, w->uid[i]); }
+        for (int r = 0; r < m; ++r) { lo = std::min<int64_t>(lo, w->adj_uid[r]); hi = std::max<int64_t>(hi, w->adj_uid[r]); }
+        if (n + m > 0 && hi - lo < 8 * (int64_t)(n + m) + 4096) {
+            s->uid_lo = (int32_t)lo;
+            s->row_direct.assign((size_t)(hi - lo + 1), -1);
+            s->adj_direct.assign((size_t)(hi - lo + 1), -1);
+            for (int i = 0; i < n; ++i) s->row_direct[(size_t)(w->uid[i] - lo)] = i;
+            for (int r = 0; r < m; ++r) s->adj_direct[(size_t)(w->adj_uid[r] - lo)] = r;
+        }
+    }
 
     TRY(upload(s, s->d_uid, w->uid, n)); TRY(upload(s, s->d_pub, w->pub, n)); TRY(upload(s, s->d_comp, w->comp, n));
     TRY(upload(s, s->d_gender, w->gender, n)); TRY(upload(s, s->d_age, w->age, n)); TRY(upload(s, s->d_region, w->region, (size_t)3 * n));

@@ -352,9 +352,12 @@ __global__ void shortlist_check_kernel(const CheckParams P) {
     if (g < 0) return;
     const uint64_t* keys = P.short_keys + (size_t)q * P.Ks;
     int32_t* rows = P.cand_rows + ((size_t)g * 32 + P.q_lane[q]) * P.Ks;
+    // only candidates whose approximate score can still reach the exact top-k (approx >= a_k - 2 margin) are re-scored
+    const float a_k0 = __uint_as_float(key_score_bits(keys[P.K - 1]));     // 0 when the list holds fewer than k entries
+    const float keep_from = a_k0 - 2.0f * P.margin - 1e-7f;
     for (int i = threadIdx.x; i < P.Ks; i += blockDim.x) {
         const uint64_t k = keys[i];
-        rows[i] = k ? key_id(k) : -1;
+        rows[i] = (k && __uint_as_float(key_score_bits(k)) >= keep_from) ? key_id(k) : -1;
     }
     if (threadIdx.x == 0) {
         const uint64_t last = keys[P.Ks - 1];
