@@ -120,7 +120,8 @@ struct FullscanJob {
     uint32_t max_smem_lean = 0;
     int64_t rr_pairs = 0;
     DevBuf<WorkItem> pre_items, rr_items;
-    DevBuf<uint64_t> keys_pre, keys_short, keys_rr;
+    DevBuf<uint64_t> keys_pre, keys_short, keys_rr, pub;
+    int n_slices = 1;
     DevBuf<int32_t> q_group, q_flag, q_flag0, group_flag, group_flag0, short_rows, rr_slot0, rr_nl, pre_slot0, pre_nl;
     DevBuf<int32_t> lean_fail;                // [group] the pre-filter's token table could not be built -> exact scan
 };
@@ -843,7 +844,7 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
     TRY(upload(s, J.q_lane, q_lane));
 
     if (lean) {
-        J.lean = true; J.Ks = Ks;
+        J.lean = true; J.Ks = Ks; J.n_slices = (int)splits;
         // pre-filter items (same slicing), groups whose lean tables do not fit shared memory go straight to the
         // exact full scan (flag preset)
         std::vector<WorkItem> pre;
@@ -971,6 +972,17 @@ int fullscan_execute(pk_store* s) {
     PreParams Q = base_pre_params(s);
     Q.groups = J.groups.p; Q.items = J.pre_items.p; Q.arena = J.arena.p;
     Q.Ks = Ks; Q.exclude_mode = J.exclude; Q.smem_arena_bytes = J.max_smem_lean; Q.out_keys = J.keys_pre.p;
+    TRY(J.pub.reserve(std::max<size_t>(J.n_pre, 1) * 32));
+    CK(cudaMemsetAsync(J.pub.p, 0, std::max<size_t>(J.n_pre, 1) * 32 * 8, s->stream));
+    {
+        // measured on B200 (profiles/): sharing the threshold pays when a slice holds few candidates (8-GPU shard:
+        // 25 k rows per slice, pre-filter 40.5 -> 35.0 ms) and costs at 204 k rows per slice (1 GPU: 226 -> 249 ms)
+        int64_t max_slice = 65536;
+        if (const char* e = getenv("POKEC_B200_PUB_MAX_SLICE")) max_slice = atoll(e);
+        const int64_t per_slice = (s->shard_end - s->shard_begin) / std::max(1, J.n_slices);
+        Q.pub = per_slice <= max_slice ? reinterpret_cast<unsigned long long*>(J.pub.p) : nullptr;
+    }
+    Q.n_slices = J.n_slices; Q.pub_rank = (Ks + J.n_slices - 1) / J.n_slices;
     CK(cudaEventRecord(s->ev0, s->stream));
     TRY(launch_prefilter(s, Q, J.n_pre, J.max_smem_lean, Ks, false));
     CK(cudaEventRecord(s->ev1, s->stream));

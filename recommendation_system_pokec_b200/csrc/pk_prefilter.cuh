@@ -69,6 +69,13 @@ struct PreParams {
     int Ks;                      // shortlist length (multiple of 32)
     int exclude_mode;
     uint32_t smem_arena_bytes;
+    // TOPK: shared shortlist threshold.  Every CTA (slice) publishes, per query, its `pub_rank`-th best key in
+    // pub[blockIdx.x][32]; the n_slices CTAs of a group are consecutive blocks.  n_slices * pub_rank >= Ks, so the
+    // minimum of a group's published keys is a lower bound of the Ks-th best key over ALL slices: a key below it
+    // cannot be in the merged shortlist, whichever slice it lives in.  (zeroed per launch; 0 = not yet published;
+    // null = off: the host enables it for small slices, where list insertions are a visible share of the work)
+    unsigned long long* pub;
+    int n_slices, pub_rank;
     uint64_t* out_keys;          // TOPK: [item.out_slot][32][Ks], key = (approx score bits, candidate ROW)
     float* out_f;                // STORE (tests): [(item.out_slot + i)][32] approximate scores
 };
@@ -79,6 +86,57 @@ __device__ __forceinline__ float lean_sigma(float4 c, float s) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(fmaf(c.x, s, c.y)));
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
     return r;
+}
+
+// Warp-cooperative insertion of `key` into one query's descending shortlist (all lanes call it with the same
+// arguments; keys are unique -- one per candidate row).  Publishes the list's `rank`-th key when it changed.
+__device__ __forceinline__ void shortlist_insert(uint64_t* list, int K, uint64_t key, int* lock, volatile uint64_t* tau,
+                                                 int lane, int rank, unsigned long long* pub) {
+    if (lane == 0) {
+        while (atomicCAS(lock, 0, 1) != 0) __nanosleep(32);
+    }
+    __syncwarp();
+    __threadfence_block();
+    volatile uint64_t* vl = list;
+    uint64_t publish = 0ull;
+    if (key > vl[K - 1]) {
+        int pos = 0;
+        for (int s0 = 0; s0 < K; s0 += 32) pos += __popc(__ballot_sync(kFull, vl[s0 + lane] > key));
+        for (int s0 = K - 32; s0 >= 0 && s0 + 32 > pos; s0 -= 32) {
+            const int i = s0 + lane;
+            const bool mv = i > pos;
+            uint64_t v = 0;
+            if (mv) v = vl[i - 1];
+            __syncwarp();
+            if (mv) vl[i] = v;
+            __syncwarp();
+        }
+        if (lane == 0) {
+            vl[pos] = key;
+            const uint64_t kth = vl[K - 1], told = *tau;
+            *tau = kth > told ? kth : told;          // never below a threshold taken from the group's other slices
+            if (pos < rank) publish = vl[rank - 1];
+        }
+    }
+    __threadfence_block();
+    __syncwarp();
+    if (lane == 0) {
+        atomicExch(lock, 0);
+        if (pub && publish != 0ull) *reinterpret_cast<volatile unsigned long long*>(pub) = publish;   // after the unlock
+    }
+}
+
+#ifndef PK_PUB_EVERY
+#define PK_PUB_EVERY 16
+#endif
+// Raises my query's threshold to the minimum of the keys the group's slices have published (PreParams::pub).
+// Kept out of line: it runs once per PK_PUB_EVERY chunks and must not cost the scoring loop any registers.
+__device__ __noinline__ void refresh_threshold(const unsigned long long* pg, int n_slices, uint64_t* tau, int lane) {
+    unsigned long long g = ~0ull;
+    for (int sl = 0; sl < n_slices; ++sl)
+        g = min(g, *reinterpret_cast<const volatile unsigned long long*>(pg + sl * 32 + lane));
+    volatile uint64_t* tv = reinterpret_cast<volatile uint64_t*>(tau);
+    if (g > tv[lane]) tv[lane] = g;
 }
 
 // 32 x 32 bit transpose across the warp: bit j of the result in lane l = bit l of x in lane j
@@ -164,6 +222,8 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
         c0 = __shfl_sync(kFull, c0, 0);
         if (c0 >= it.cand_end) break;
         const int c1 = min(c0 + kChunk, it.cand_end);
+        if (!STORE && P.pub && ((c0 / kChunk) & (PK_PUB_EVERY - 1)) == 0)
+            refresh_threshold(P.pub + (size_t)(blockIdx.x - blockIdx.x % P.n_slices) * 32, P.n_slices, tau, lane);
         uint64_t offv = 0;
         if (c0 + lane < c1) offv = __ldg(P.lrec_off + c0 + lane);
         for (int ci = c0; ci < c1; ++ci) {
@@ -317,7 +377,8 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                         const int j = __ffs(pass) - 1;
                         pass &= pass - 1;
                         const uint64_t kj = __shfl_sync(kFull, key, j);
-                        topk_insert(lists + j * Ks, Ks, Ks, kj, locks + j, reinterpret_cast<volatile uint64_t*>(tau) + j, lane);
+                        shortlist_insert(lists + j * Ks, Ks, kj, locks + j, reinterpret_cast<volatile uint64_t*>(tau) + j, lane, P.pub_rank,
+                                         P.pub ? P.pub + (size_t)blockIdx.x * 32 + j : nullptr);
                     }
                 }
             }

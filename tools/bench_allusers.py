@@ -1,0 +1,105 @@
+#!/usr/bin/env python
+"""bench_allusers.py -- BASELINE configs[4]: all-users batch scoring (every user is a query, FAS top-50 against all
+1.63 M candidates), candidates sharded by row range over the GPUs, NCCL all-gather of the per-rank keys + merge.
+
+    python tools/bench_allusers.py [--batches B] [--batch 4096]                                   # 1 GPU
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \\
+        --master-port 29533 tools/bench_allusers.py --batches B                                   # N GPUs
+
+The full sweep is ceil(1 632 803 / 4096) = 399 batches; the sustained rate is measured on a window of B consecutive
+batches (distinct query users, walked in uid order) through the public end-to-end call -- host uids in, host top-k
+out, every batch -- and extrapolated to the sweep.  Prints one JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from recommendation_system_pokec_b200.synth import make_world, sample_normalizers, POKEC_N  # noqa: E402
+from recommendation_system_pokec_b200.cabi import EXCLUDE_SELF_AND_ADJ  # noqa: E402
+from recommendation_system_pokec_b200.sharding import shard_rows  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--users", type=int, default=POKEC_N)
+    ap.add_argument("--batch", type=int, default=4096)
+    ap.add_argument("--batches", type=int, default=16)
+    ap.add_argument("--topk", type=int, default=50)
+    args = ap.parse_args()
+    fd = os.dup(1)
+    os.dup2(2, 1)                      # NCCL prints its banner on stdout
+    rank = int(os.environ.get("RANK", "0"))
+    ws = int(os.environ.get("WORLD_SIZE", "1"))
+    lr = int(os.environ.get("LOCAL_RANK", "0"))
+    import torch
+    import torch.distributed as dist
+    from recommendation_system_pokec_b200.engine import DeviceRecommender
+    torch.cuda.set_device(lr)
+    if ws > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+    w = make_world(n=args.users)
+    m, s = sample_normalizers(w, pairs=4000)
+    w.set_normalizers(m, s)
+    dev = DeviceRecommender(w, device=lr)
+    lo, hi = shard_rows(w.n, rank, ws)
+    dev.set_shard(lo, hi)
+    k, B = args.topk, args.batch
+    stream = torch.cuda.ExternalStream(dev.stream(), device=lr)
+    local = torch.zeros((B, k), dtype=torch.int64, device=f"cuda:{lr}")
+    gathered = torch.zeros((ws, B, k), dtype=torch.int64, device=f"cuda:{lr}")
+
+    def run_batch(b):
+        q = w.uid[(b * B) % w.n:(b * B) % w.n + B].astype(np.int32)
+        if len(q) < B:
+            q = np.concatenate([q, w.uid[:B - len(q)].astype(np.int32)])
+        if ws == 1:
+            return dev.fullscan(q, k, EXCLUDE_SELF_AND_ADJ)
+        dev.fullscan_local_keys(q, k, EXCLUDE_SELF_AND_ADJ, local.data_ptr())
+        with torch.cuda.stream(stream):
+            dist.all_gather_into_tensor(gathered.view(-1), local.view(-1))
+        return dev.merge_keys(gathered.data_ptr(), ws, B, k)
+
+    def barrier():
+        dev.sync()
+        torch.cuda.synchronize()
+        if ws > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    run_batch(0)
+    barrier()
+    t = time.perf_counter()
+    res = None
+    for b in range(1, args.batches + 1):
+        res = run_batch(b)
+    barrier()
+    dt = time.perf_counter() - t
+    if ws > 1:
+        tt = torch.tensor([dt], dtype=torch.float64, device=f"cuda:{lr}")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt.item())
+    rate = args.batches * B / dt
+    if rank == 0:
+        out = {"workload": "all-users FAS top-50 (BASELINE configs[4])", "n_gpus": ws, "users": w.n, "batch": B,
+               "window_batches": args.batches, "query_users_per_s": rate, "ms_per_batch": dt / args.batches * 1e3,
+               "full_sweep_batches": -(-w.n // B), "full_sweep_seconds_extrapolated": w.n / rate,
+               "pairs_per_s": rate * w.n, "complete_lists": bool(int(res[2].min()) == k)}
+        os.write(fd, (json.dumps(out) + "\n").encode())
+    if ws > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    dev.close()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -37,7 +37,12 @@ def main():
     w.set_normalizers(m, s)
     q = sample_queries(w, args.queries, seed=2)
     ref_ids = None
-    for name in args.names:
+    for spec in args.names:
+        # "name" or "name:ENV=VALUE[,ENV=VALUE]" (environment switches read by the library at prepare / execute time)
+        name, _, envs = spec.partition(":")
+        for kv in filter(None, envs.split(",")):
+            k_, _, v_ = kv.partition("=")
+            os.environ[k_] = v_
         path = engine.LIB_PATH if name == "base" else os.path.join(os.path.dirname(engine.LIB_PATH), f"libpokec_b200.{name}.so")
         os.environ["POKEC_B200_LIB"] = path
         engine._lib = None
@@ -56,7 +61,9 @@ def main():
         same = True if ref_ids is None else bool(np.array_equal(ids, ref_ids))
         if ref_ids is None:
             ref_ids = ids
-        print(json.dumps({"variant": name, "ms_per_step": dt * 1e3, "query_users_per_s": len(q) / dt,
+        for kv in filter(None, envs.split(",")):
+            os.environ.pop(kv.partition("=")[0], None)
+        print(json.dumps({"variant": spec, "shard": args.shard, "ms_per_step": dt * 1e3, "query_users_per_s": len(q) / dt,
                           "prefilter_ms": dev.stat(engine.STAT_SCAN_KERNEL_NS) / 1e6,
                           "rescore_ms": dev.stat(engine.STAT_RESCORE_NS) / 1e6,
                           "fallback_queries": dev.stat(engine.STAT_FALLBACK_QUERIES), "ids_equal_first": same}), flush=True)
