@@ -120,8 +120,11 @@ struct FullscanJob {
     uint32_t max_smem_lean = 0;
     int64_t rr_pairs = 0;
     DevBuf<WorkItem> pre_items, rr_items;
-    DevBuf<uint64_t> keys_pre, keys_short, keys_rr, pub;
-    int n_slices = 1;
+    DevBuf<uint64_t> keys_pre, keys_short, keys_rr;
+    // dynamic schedule of the pre-filter (PreParams): schedulable groups, {cursor, instances} per group
+    DevBuf<int32_t> dyn_groups, dyn_state;
+    int n_dyn = 0, n_slices = 1, sm_count = 148;
+    int64_t cand_begin = 0, cand_end = 0;     // the shard the job was planned for
     DevBuf<int32_t> q_group, q_flag, q_flag0, group_flag, group_flag0, short_rows, rr_slot0, rr_nl, pre_slot0, pre_nl;
     DevBuf<int32_t> lean_fail;                // [group] the pre-filter's token table could not be built -> exact scan
 };
@@ -844,20 +847,26 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
     TRY(upload(s, J.q_lane, q_lane));
 
     if (lean) {
-        J.lean = true; J.Ks = Ks; J.n_slices = (int)splits;
+        J.lean = true; J.Ks = Ks; J.n_slices = (int)splits; J.sm_count = sm_count;
+        J.cand_begin = s->shard_begin; J.cand_end = s->shard_end;
         // pre-filter items (same slicing), groups whose lean tables do not fit shared memory go straight to the
         // exact full scan (flag preset)
         std::vector<WorkItem> pre;
         std::vector<int32_t> pre_slot0(nq, 0), pre_nl(nq, 0), gflag0(ng, 0), qflag0(nq, 0), gp0(ng, 0);
+        std::vector<int32_t> dyn_groups;
         for (int gi = 0; gi < ng; ++gi) {
             gp0[gi] = (int32_t)pre.size();
             if (!plan.groups[gi].lean_in_smem) { gflag0[gi] = 1; continue; }
+            dyn_groups.push_back(gi);
             for (int64_t sp = 0; sp < splits; ++sp) {
                 WorkItem it = items[(size_t)g_slot0[gi] + sp];
                 it.out_slot = (int32_t)pre.size();
                 pre.push_back(it);
             }
         }
+        J.n_dyn = (int)dyn_groups.size();
+        TRY(upload(s, J.dyn_groups, dyn_groups));
+        TRY(J.dyn_state.reserve(std::max<size_t>(2 * dyn_groups.size(), 1)));
         // exact re-score items: the 32 x Ks shortlist rows of each group, in list mode
         const int rr_splits = 4;
         std::vector<WorkItem> rr;
@@ -972,19 +981,15 @@ int fullscan_execute(pk_store* s) {
     PreParams Q = base_pre_params(s);
     Q.groups = J.groups.p; Q.items = J.pre_items.p; Q.arena = J.arena.p;
     Q.Ks = Ks; Q.exclude_mode = J.exclude; Q.smem_arena_bytes = J.max_smem_lean; Q.out_keys = J.keys_pre.p;
-    TRY(J.pub.reserve(std::max<size_t>(J.n_pre, 1) * 32));
-    CK(cudaMemsetAsync(J.pub.p, 0, std::max<size_t>(J.n_pre, 1) * 32 * 8, s->stream));
-    {
-        // measured on B200 (profiles/): sharing the threshold pays when a slice holds few candidates (8-GPU shard:
-        // 25 k rows per slice, pre-filter 40.5 -> 35.0 ms) and costs at 204 k rows per slice (1 GPU: 226 -> 249 ms)
-        int64_t max_slice = 65536;
-        if (const char* e = getenv("POKEC_B200_PUB_MAX_SLICE")) max_slice = atoll(e);
-        const int64_t per_slice = (s->shard_end - s->shard_begin) / std::max(1, J.n_slices);
-        Q.pub = per_slice <= max_slice ? reinterpret_cast<unsigned long long*>(J.pub.p) : nullptr;
-    }
-    Q.n_slices = J.n_slices; Q.pub_rank = (Ks + J.n_slices - 1) / J.n_slices;
+    // shortlist instances a CTA never takes stay empty; cursors and instance counters start at 0
+    CK(cudaMemsetAsync(J.keys_pre.p, 0, std::max<size_t>(J.n_pre, 1) * 32 * (size_t)Ks * 8, s->stream));
+    CK(cudaMemsetAsync(J.dyn_state.p, 0, std::max<size_t>(2 * (size_t)J.n_dyn, 1) * 4, s->stream));
+    Q.dyn_cursor = J.dyn_state.p; Q.dyn_ninst = J.dyn_state.p + J.n_dyn; Q.dyn_groups = J.dyn_groups.p;
+    Q.n_dyn = J.n_dyn; Q.max_inst = J.n_slices;
+    Q.cand_begin = (int)J.cand_begin; Q.cand_end = (int)J.cand_end;
+    const size_t pre_grid = std::min<size_t>((size_t)J.sm_count, J.n_pre);     // one persistent CTA per SM
     CK(cudaEventRecord(s->ev0, s->stream));
-    TRY(launch_prefilter(s, Q, J.n_pre, J.max_smem_lean, Ks, false));
+    TRY(launch_prefilter(s, Q, pre_grid, J.max_smem_lean, Ks, false));
     CK(cudaEventRecord(s->ev1, s->stream));
     if (J.n_pre) { s->scan_time_pending = true; ++s->stat_scan_launches; }
     // 2. merge the slices' shortlists, prove them complete (or flag the query), emit the rows to re-score

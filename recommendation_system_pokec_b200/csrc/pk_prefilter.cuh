@@ -69,13 +69,16 @@ struct PreParams {
     int Ks;                      // shortlist length (multiple of 32)
     int exclude_mode;
     uint32_t smem_arena_bytes;
-    // TOPK: shared shortlist threshold.  Every CTA (slice) publishes, per query, its `pub_rank`-th best key in
-    // pub[blockIdx.x][32]; the n_slices CTAs of a group are consecutive blocks.  n_slices * pub_rank >= Ks, so the
-    // minimum of a group's published keys is a lower bound of the Ks-th best key over ALL slices: a key below it
-    // cannot be in the merged shortlist, whichever slice it lives in.  (zeroed per launch; 0 = not yet published;
-    // null = off: the host enables it for small slices, where list insertions are a visible share of the work)
-    unsigned long long* pub;
-    int n_slices, pub_rank;
+    // TOPK: dynamic scheduling.  The grid is one persistent CTA per SM.  A CTA picks a group (first its own, later
+    // the one with the most candidates left), takes one of the group's `max_inst` shortlist instances, claims chunks
+    // of candidates from the group's cursor until the shard is exhausted, writes its lists to
+    // out_keys[group_index * max_inst + instance] and picks again.  Far fewer list instances than a static slicing
+    // that fills the GPU (each instance pays ~Ks (1 + ln(n / Ks)) insertions), and no wave tail.
+    int* dyn_cursor;             // [n_dyn] next candidate offset inside the shard (zeroed per launch)
+    int* dyn_ninst;              // [n_dyn] instances handed out (zeroed per launch)
+    const int32_t* dyn_groups;   // [n_dyn] group index of each schedulable group
+    int n_dyn, max_inst;
+    int cand_begin, cand_end;    // the shard's row range
     uint64_t* out_keys;          // TOPK: [item.out_slot][32][Ks], key = (approx score bits, candidate ROW)
     float* out_f;                // STORE (tests): [(item.out_slot + i)][32] approximate scores
 };
@@ -89,16 +92,15 @@ __device__ __forceinline__ float lean_sigma(float4 c, float s) {
 }
 
 // Warp-cooperative insertion of `key` into one query's descending shortlist (all lanes call it with the same
-// arguments; keys are unique -- one per candidate row).  Publishes the list's `rank`-th key when it changed.
+// arguments; keys are unique -- one per candidate row).
 __device__ __forceinline__ void shortlist_insert(uint64_t* list, int K, uint64_t key, int* lock, volatile uint64_t* tau,
-                                                 int lane, int rank, unsigned long long* pub) {
+                                                 int lane) {
     if (lane == 0) {
         while (atomicCAS(lock, 0, 1) != 0) __nanosleep(32);
     }
     __syncwarp();
     __threadfence_block();
     volatile uint64_t* vl = list;
-    uint64_t publish = 0ull;
     if (key > vl[K - 1]) {
         int pos = 0;
         for (int s0 = 0; s0 < K; s0 += 32) pos += __popc(__ballot_sync(kFull, vl[s0 + lane] > key));
@@ -113,30 +115,12 @@ __device__ __forceinline__ void shortlist_insert(uint64_t* list, int K, uint64_t
         }
         if (lane == 0) {
             vl[pos] = key;
-            const uint64_t kth = vl[K - 1], told = *tau;
-            *tau = kth > told ? kth : told;          // never below a threshold taken from the group's other slices
-            if (pos < rank) publish = vl[rank - 1];
+            *tau = vl[K - 1];
         }
     }
     __threadfence_block();
     __syncwarp();
-    if (lane == 0) {
-        atomicExch(lock, 0);
-        if (pub && publish != 0ull) *reinterpret_cast<volatile unsigned long long*>(pub) = publish;   // after the unlock
-    }
-}
-
-#ifndef PK_PUB_EVERY
-#define PK_PUB_EVERY 16
-#endif
-// Raises my query's threshold to the minimum of the keys the group's slices have published (PreParams::pub).
-// Kept out of line: it runs once per PK_PUB_EVERY chunks and must not cost the scoring loop any registers.
-__device__ __noinline__ void refresh_threshold(const unsigned long long* pg, int n_slices, uint64_t* tau, int lane) {
-    unsigned long long g = ~0ull;
-    for (int sl = 0; sl < n_slices; ++sl)
-        g = min(g, *reinterpret_cast<const volatile unsigned long long*>(pg + sl * 32 + lane));
-    volatile uint64_t* tv = reinterpret_cast<volatile uint64_t*>(tau);
-    if (g > tv[lane]) tv[lane] = g;
+    if (lane == 0) atomicExch(lock, 0);
 }
 
 // 32 x 32 bit transpose across the warp: bit j of the result in lane l = bit l of x in lane j
@@ -160,9 +144,6 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
     extern __shared__ uint4 smem_u4[];
     uint8_t* smem = reinterpret_cast<uint8_t*>(smem_u4);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const WorkItem it = P.items[blockIdx.x];
-    const GroupDesc* gd = P.groups + it.group;
-
     const uint32_t arena_sm = P.smem_arena_bytes;
     LeanNorm* N = reinterpret_cast<LeanNorm*>(smem + arena_sm);
     constexpr uint32_t kNormBytes = (sizeof(LeanNorm) + 15u) & ~15u;
@@ -172,6 +153,56 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
     int* locks = reinterpret_cast<int*>(tau + 32);
     int* next = locks + 32;
     uint4* stage = reinterpret_cast<uint4*>(next + 4) + warp * 32;                  // per-warp hit staging
+    int* pick = next + 1;                                                           // {group index, instance}
+
+    for (int round = 0;; ++round) {
+    WorkItem it;
+    if (STORE) {
+        if (round > 0) break;
+        it = P.items[blockIdx.x];
+    } else {
+        // ---- pick a group and one of its shortlist instances (PreParams: dynamic scheduling) ----
+        if (warp == 0) {
+            const int n_cand = P.cand_end - P.cand_begin;
+            int g = -1, inst = -1;
+            for (int attempt = 0; attempt < 8 && g < 0; ++attempt) {
+                int best = -1, best_rem = 0;
+                if (round == 0 && attempt == 0) {
+                    best = (int)(blockIdx.x % (unsigned)P.n_dyn);     // the first pick spreads the CTAs over the groups
+                    best_rem = n_cand;
+                } else {
+                    // the group with the most candidates left that still has a free instance; joining for less than
+                    // a few thousand candidates would cost more (tables, list fill, merge) than it saves
+                    // (a group nobody has started yet is always taken, however small)
+                    for (int i = lane; i < P.n_dyn; i += 32) {
+                        const int rem = n_cand - *reinterpret_cast<volatile int*>(P.dyn_cursor + i);
+                        const int ni = *reinterpret_cast<volatile int*>(P.dyn_ninst + i);
+                        const bool worth = rem > 4096 || (ni == 0 && rem > 0);
+                        if (worth && rem > best_rem && ni < P.max_inst) { best_rem = rem; best = i; }
+                    }
+                    for (int o = 16; o >= 1; o >>= 1) {
+                        const int r2 = __shfl_xor_sync(kFull, best_rem, o), b2 = __shfl_xor_sync(kFull, best, o);
+                        if (r2 > best_rem || (r2 == best_rem && b2 > best)) { best_rem = r2; best = b2; }
+                    }
+                }
+                if (best < 0) break;
+                int i = 0;
+                if (lane == 0) i = atomicAdd(P.dyn_ninst + best, 1);
+                i = __shfl_sync(kFull, i, 0);
+                if (i < P.max_inst) { g = best; inst = i; }
+            }
+            if (lane == 0) { pick[0] = g; pick[1] = inst; }
+        }
+        __syncthreads();
+        const int gi = pick[0], inst = pick[1];
+        if (gi < 0) break;
+        it.group = P.dyn_groups[gi];
+        it.cand_begin = P.cand_begin; it.cand_end = P.cand_end;
+        it.out_slot = gi * P.max_inst + inst;
+    }
+    const GroupDesc* gd = P.groups + it.group;
+    int* const cursor = STORE ? next : P.dyn_cursor + pick[0];
+    const int cursor_base = STORE ? 0 : it.cand_begin;
 
     {
         const uint4* src = reinterpret_cast<const uint4*>(P.arena + gd->arena_off);
@@ -216,14 +247,15 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
 #else
     constexpr int kChunk = 8;
 #endif
+    // the claim of the NEXT chunk is issued before the current one is scored: the cursor of the dynamic schedule
+    // lives in global memory (shared by the CTAs working on the group) and its latency must not stall the warp
+    int c_next = 0;
+    if (lane == 0) c_next = cursor_base + atomicAdd(cursor, kChunk);
     for (;;) {
-        int c0 = 0;
-        if (lane == 0) c0 = atomicAdd(next, kChunk);
-        c0 = __shfl_sync(kFull, c0, 0);
+        const int c0 = __shfl_sync(kFull, c_next, 0);
         if (c0 >= it.cand_end) break;
+        if (lane == 0) c_next = cursor_base + atomicAdd(cursor, kChunk);
         const int c1 = min(c0 + kChunk, it.cand_end);
-        if (!STORE && P.pub && ((c0 / kChunk) & (PK_PUB_EVERY - 1)) == 0)
-            refresh_threshold(P.pub + (size_t)(blockIdx.x - blockIdx.x % P.n_slices) * 32, P.n_slices, tau, lane);
         uint64_t offv = 0;
         if (c0 + lane < c1) offv = __ldg(P.lrec_off + c0 + lane);
         for (int ci = c0; ci < c1; ++ci) {
@@ -377,8 +409,7 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                         const int j = __ffs(pass) - 1;
                         pass &= pass - 1;
                         const uint64_t kj = __shfl_sync(kFull, key, j);
-                        shortlist_insert(lists + j * Ks, Ks, kj, locks + j, reinterpret_cast<volatile uint64_t*>(tau) + j, lane, P.pub_rank,
-                                         P.pub ? P.pub + (size_t)blockIdx.x * 32 + j : nullptr);
+                        shortlist_insert(lists + j * Ks, Ks, kj, locks + j, reinterpret_cast<volatile uint64_t*>(tau) + j, lane);
                     }
                 }
             }
@@ -389,7 +420,9 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
         __syncthreads();
         uint64_t* dst = P.out_keys + (size_t)it.out_slot * 32 * Ks;
         for (int i = tid; i < 32 * Ks; i += kPreThreads) dst[i] = lists[i];
+        __syncthreads();                  // the lists and tables are re-used by the next round
     }
+    }   // round
 }
 
 // Per query: is the merged shortlist (Ks approximate keys, descending) guaranteed to contain the exact

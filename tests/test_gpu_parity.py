@@ -320,6 +320,29 @@ def test_fullscan_with_and_without_prefilter_identical(env, monkeypatch):
     assert dev.stat(STAT_PREFILTER) == 0
 
 
+def test_fullscan_more_groups_than_sms(monkeypatch):
+    """dynamic schedule of the pre-filter: 6000 queries = 188 groups > 148 persistent CTAs and a shard of fewer rows
+    than the `worth joining` threshold -- every group must still be scanned completely (groups picked in later rounds,
+    several instances per group); result identical to the exact scan on every pair, also on a sub-shard"""
+    from recommendation_system_pokec_b200.engine import DeviceRecommender, STAT_PREFILTER, STAT_FALLBACK_QUERIES
+    w = make_test_world(n=6000, seed=3, T=12, pairs=800)
+    dev = DeviceRecommender(w)
+    q = w.uid.astype(np.int32)
+    for lo, hi in ((0, w.n), (1000, 2500)):
+        dev.set_shard(lo, hi)
+        monkeypatch.delenv("POKEC_B200_NO_PREFILTER", raising=False)
+        two_stage = dev.fullscan(q, 20, EXCLUDE_SELF_AND_ADJ)
+        assert dev.stat(STAT_PREFILTER) == 1
+        monkeypatch.setenv("POKEC_B200_NO_PREFILTER", "1")
+        exact = dev.fullscan(q, 20, EXCLUDE_SELF_AND_ADJ)
+        assert dev.stat(STAT_PREFILTER) == 0
+        for x, y in zip(two_stage, exact):
+            assert np.array_equal(x, y), f"shard [{lo},{hi})"
+        assert int(two_stage[2].min()) == 20
+    monkeypatch.delenv("POKEC_B200_NO_PREFILTER", raising=False)
+    dev.close()
+
+
 def test_fullscan_tie_heavy_world_falls_back_to_exact(oracle_libs):
     """few fields and tiny vocabularies: thousands of candidates tie at the k-th score, the shortlist cannot be
     proven complete, and the flagged queries must come out of the exact full scan -- identical to the oracle"""
