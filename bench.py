@@ -170,7 +170,7 @@ def main():
               "users": args.users, "queries_per_step": args.queries, "topk": args.topk,
               "exclude": "self + existing friends (recommender_graph.cpp:46-52)",
               "l2": "inputs larger than L2 (packed store >> 126 MB)",
-              "parallelism": f"candidate rows sharded over {world_size} GPU(s), NCCL all-gather + merge" if world_size > 1
+              "parallelism": f"candidate rows sharded over {world_size} GPU(s); NCCL all-gather of the approximate shortlists, exact re-score split by query group, NCCL all-gather of the top-k keys + merge" if world_size > 1
               else "1 GPU"}
 
     # ------------------------------------------------------------------ reference arm (CPU)
@@ -217,22 +217,39 @@ def main():
     gathered = torch.zeros((world_size, nq, k), dtype=torch.int64, device=f"cuda:{local_rank}")
     local = torch.zeros((nq, k), dtype=torch.int64, device=f"cuda:{local_rank}")
 
-    def device_step():
-        dev.fullscan_execute()
+    # N > 1: the two-stage scan is split at its exchange point -- every rank pre-filters its candidate shard, the
+    # approximate shortlists are all-gathered, every rank proves the merged shortlists and re-scores (fp64) only the
+    # query groups it owns, then the per-rank [Q][k] keys are all-gathered and merged
+    ks = dev.stat(engine.STAT_SHORTLIST)
+    split = world_size > 1 and ks > 0
+    if split:
+        local_s = torch.zeros((nq, ks), dtype=torch.int64, device=f"cuda:{local_rank}")
+        gathered_s = torch.zeros((world_size, nq, ks), dtype=torch.int64, device=f"cuda:{local_rank}")
+
+    def scan_and_exchange(fetch):
+        if split:
+            dev.fullscan_execute_shortlists()
+            dev.fullscan_shortlist_keys(local_s.data_ptr())
+            with torch.cuda.stream(stream):
+                dist.all_gather_into_tensor(gathered_s.view(-1), local_s.view(-1))
+            dev.fullscan_execute_finish(gathered_s.data_ptr(), world_size, rank, world_size)
+        else:
+            dev.fullscan_execute()
         if world_size > 1:
             dev.fullscan_keys(local.data_ptr())
             with torch.cuda.stream(stream):
                 dist.all_gather_into_tensor(gathered.view(-1), local.view(-1))
-            return dev.merge_keys(gathered.data_ptr(), world_size, nq, k)
+            return dev.merge_keys(gathered.data_ptr(), world_size, nq, k, fetch=fetch)   # fetch=False: keys stay on the device
         return None
+
+    def device_step():
+        return scan_and_exchange(False)
 
     def e2e_step():
         if world_size == 1:
             return dev.fullscan(q, k, EXCLUDE_SELF_AND_ADJ)
-        dev.fullscan_local_keys(q, k, EXCLUDE_SELF_AND_ADJ, local.data_ptr())
-        with torch.cuda.stream(stream):
-            dist.all_gather_into_tensor(gathered.view(-1), local.view(-1))
-        return dev.merge_keys(gathered.data_ptr(), world_size, nq, k)
+        dev.fullscan_prepare(q, k, EXCLUDE_SELF_AND_ADJ)     # host planning + H2D of the plan, every step
+        return scan_and_exchange(True)
 
     def barrier():
         dev.sync()
@@ -293,8 +310,18 @@ def main():
     peak, peak_src = measured_peak_hbm()
     achieved = alg_bytes_per_launch / scan_s / 1e9 if scan_s > 0 else 0.0
     two_stage = dev.stat(engine.STAT_PREFILTER) == 1
+    # physical DRAM bytes of one launch of the dominant kernel, from the committed `ncu --set full` capture of this
+    # same workload (dram__bytes_read.sum + dram__bytes_write.sum); null when the run is not that workload
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            tr = json.load(f)
+        if two_stage and world_size == 1 and tr.get("users") == args.users and tr.get("queries") == args.queries:
+            traffic = tr.get("dram_bytes_per_launch")
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "fas_prefilter_kernel<false>" if two_stage else "fas_scan_kernel<true,0,false>",
+                "traffic": traffic, "kernel": "fas_prefilter_kernel<false>" if two_stage else "fas_scan_kernel<true,0,false>",
                 "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes_per_launch, "launch_ms": scan_s * 1e3,
                 "note": "algorithmic bytes = queries x canonical record bytes of the shard (SURVEY 8d); cross-query reuse of a "

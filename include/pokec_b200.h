@@ -144,9 +144,27 @@ int pk_candidates(pk_store* s, int mode, int32_t uid, int limit, int32_t* out, i
 int pk_fullscan_local_keys(pk_store* s, int nq, const int32_t* q_uid, int k, int exclude_mode, uint64_t* d_keys);
 
 /* Merges n_lists key lists ([n_lists][nq][k] on the device, e.g. the all-gathered per-rank lists)
- * into the final host result. */
+ * into the final host result.  With out_id, out_score and out_cnt all NULL only the device merge is enqueued
+ * (asynchronous on the store's stream; nothing is fetched) -- for callers that time or pipeline the device work. */
 int pk_merge_keys(pk_store* s, const uint64_t* d_keys, int n_lists, int nq, int k,
                   int32_t* out_id, float* out_score, int32_t* out_cnt);
+
+/* The two-stage full scan split at its exchange point, for N candidate shards (one rank each) that share the
+ * exact re-score instead of each re-scoring its own shortlist:
+ *   execute_shortlists  table build + fp32 pre-filter of the shard: the shard's approximate top-Ks per query
+ *                       (without the pre-filter -- pk_stat(PK_STAT_SHORTLIST) == 0 -- the whole exact scan runs here)
+ *   shortlist_keys      asynchronous copy of those [nq][Ks] keys (Ks = pk_stat(PK_STAT_SHORTLIST)) into d_short,
+ *                       the buffer the caller all-gathers
+ *   execute_finish      merges n_lists gathered shortlists ([n_lists][nq][Ks] on the device; NULL = the local one),
+ *                       proves every query's shortlist, re-scores with the reference's fp64 arithmetic only the
+ *                       query groups rank `rank` of `n_ranks` owns (every rank holds the whole packed store), and
+ *                       runs the exact fallback of unproven queries over its own shard.  pk_fullscan_keys then
+ *                       yields this rank's [nq][k] keys (empty lists for queries it does not own) for the final
+ *                       all-gather + pk_merge_keys.
+ * pk_fullscan_execute == execute_shortlists + execute_finish(NULL, 1, 0, 1).  All asynchronous on the store's stream. */
+int pk_fullscan_execute_shortlists(pk_store* s);
+int pk_fullscan_shortlist_keys(pk_store* s, uint64_t* d_short);
+int pk_fullscan_execute_finish(pk_store* s, const uint64_t* d_all_short, int n_lists, int rank, int n_ranks);
 
 int pk_sync(pk_store* s);
 /* The CUDA stream (cudaStream_t) every kernel of this store is launched on. */

@@ -120,7 +120,8 @@ struct FullscanJob {
     uint32_t max_smem_lean = 0;
     int64_t rr_pairs = 0;
     DevBuf<WorkItem> pre_items, rr_items;
-    DevBuf<uint64_t> keys_pre, keys_short, keys_rr;
+    DevBuf<uint64_t> keys_pre, keys_short, keys_short_all, keys_rr;
+    size_t n_rr = 0;
     // dynamic schedule of the pre-filter (PreParams): schedulable groups, {cursor, instances} per group
     DevBuf<int32_t> dyn_groups, dyn_state;
     int n_dyn = 0, n_slices = 1, sm_count = 148;
@@ -661,6 +662,7 @@ ScanParams base_scan_params(pk_store* s, int K) {
     P.norm = s->d_norm.p; P.tab_comp = s->d_tab_comp.p; P.tab_age = s->d_tab_age.p;
     P.T = s->T; P.K = K; P.Kp = (K + 31) / 32 * 32; P.exclude_mode = PK_EXCLUDE_NONE;
     P.nf = 3 + s->T + 2;
+    P.group_lo = 0; P.group_hi = 0x7fffffff;
     return P;
 }
 
@@ -868,7 +870,8 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
         TRY(upload(s, J.dyn_groups, dyn_groups));
         TRY(J.dyn_state.reserve(std::max<size_t>(2 * dyn_groups.size(), 1)));
         // exact re-score items: the 32 x Ks shortlist rows of each group, in list mode
-        const int rr_splits = 4;
+        int rr_splits = 4;      // measured: 8 splits (6.92 waves) cost 4.7 ms against 3.9 ms (table staging per CTA)
+        if (const char* e = getenv("POKEC_B200_RR_SPLITS")) rr_splits = std::max(1, atoi(e));
         std::vector<WorkItem> rr;
         std::vector<int32_t> rr_slot0(nq, 0), rr_nl(nq, 0), gr0(ng, 0);
         for (int gi = 0; gi < ng; ++gi) {
@@ -903,6 +906,7 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
         TRY(J.keys_pre.reserve(std::max<size_t>(pre.size(), 1) * 32 * (size_t)Ks));
         TRY(J.keys_short.reserve((size_t)nq * Ks));
         TRY(J.keys_rr.reserve(std::max<size_t>(rr.size(), 1) * 32 * (size_t)Kp));
+        J.n_rr = rr.size();
         TRY(J.short_rows.reserve((size_t)ng * 32 * Ks));
     }
     CK(cudaStreamSynchronize(s->stream));
@@ -935,7 +939,7 @@ PreParams base_pre_params(pk_store* s) {
     return P;
 }
 
-int fullscan_execute(pk_store* s) {
+int fullscan_shortlists(pk_store* s) {
     FullscanJob& J = s->job;
     if (!J.valid) return fail(PK_ERR_STATE, "pk_fullscan_prepare has not been called");
     s->stat_scan_ns = 0; s->stat_scan_launches = 0; s->stat_prefilter_ns = 0;
@@ -992,15 +996,46 @@ int fullscan_execute(pk_store* s) {
     TRY(launch_prefilter(s, Q, pre_grid, J.max_smem_lean, Ks, false));
     CK(cudaEventRecord(s->ev1, s->stream));
     if (J.n_pre) { s->scan_time_pending = true; ++s->stat_scan_launches; }
-    // 2. merge the slices' shortlists, prove them complete (or flag the query), emit the rows to re-score
+    // 2. merge the instances' shortlists per query: the shard's approximate top-Ks
     MergeParams MS;
     memset(&MS, 0, sizeof(MS));
     MS.keys = J.keys_pre.p; MS.slot0 = J.pre_slot0.p; MS.n_lists_q = J.pre_nl.p; MS.lane = J.q_lane.p;
     MS.nq = J.nq; MS.K = Ks; MS.stride_k = Ks; MS.out_keys = J.keys_short.p;
     merge_topk_kernel<<<J.nq, 128, 0, s->stream>>>(MS);
     ++s->stat_launches;
+    CK(cudaGetLastError());
+    return PK_OK;
+}
+
+// Second half of the two-stage scan: proof, exact re-score, fallback, final merge.  With shortlists gathered from
+// n_ranks candidate shards (d_all_short = [n_lists][nq][Ks]) the merged list is the approximate top-Ks over ALL
+// candidates; every rank proves it for every query (the flags are the same everywhere), re-scores only the groups
+// it owns (any rank can: the packed store holds the whole world) and runs the exact fallback of flagged groups
+// over its own shard.  The per-rank [nq][k] keys are then merged by the caller exactly as before.
+int fullscan_finish(pk_store* s, const uint64_t* d_all_short, int n_lists, int rank, int n_ranks) {
+    FullscanJob& J = s->job;
+    if (!J.valid) return fail(PK_ERR_STATE, "pk_fullscan_prepare has not been called");
+    if (n_ranks < 1 || rank < 0 || rank >= n_ranks || n_lists < 1) return fail(PK_ERR_ARG, "bad rank / n_ranks / n_lists");
+    if (J.n_groups == 0 || !J.lean) return PK_OK;       // the exact scan of the first half already produced the keys
+    const int Ks = J.Ks;
+    const uint64_t* short_keys = J.keys_short.p;
+    if (d_all_short) {
+        TRY(J.keys_short_all.reserve((size_t)J.nq * Ks));
+        MergeParams MG;
+        memset(&MG, 0, sizeof(MG));
+        MG.keys = d_all_short; MG.n_lists = n_lists; MG.nq = J.nq; MG.K = Ks; MG.stride_k = Ks; MG.out_keys = J.keys_short_all.p;
+        merge_topk_kernel<<<J.nq, 128, 0, s->stream>>>(MG);
+        ++s->stat_launches;
+        short_keys = J.keys_short_all.p;
+    }
+    ScanParams P = base_scan_params(s, J.K);
+    P.groups = J.groups.p; P.arena = J.arena.p;
+    P.exclude_mode = J.exclude;
+    MergeParams M;
+    memset(&M, 0, sizeof(M));
+    M.lane = J.q_lane.p; M.nq = J.nq; M.K = J.K; M.out_keys = J.keys_b.p;
     CheckParams C;
-    C.short_keys = J.keys_short.p; C.q_group = J.q_group.p; C.q_lane = J.q_lane.p; C.cand_rows = J.short_rows.p;
+    C.short_keys = short_keys; C.q_group = J.q_group.p; C.q_lane = J.q_lane.p; C.cand_rows = J.short_rows.p;
     C.q_flag = J.q_flag.p; C.group_flag = J.group_flag.p; C.lean_fail = J.lean_fail.p; C.nq = J.nq; C.K = J.K; C.Ks = Ks; C.margin = s->margin;
     shortlist_check_kernel<<<J.nq, 64, 0, s->stream>>>(C);
     ++s->stat_launches;
@@ -1009,6 +1044,11 @@ int fullscan_execute(pk_store* s) {
     CK(cudaEventRecord(s->ev2, s->stream));
     ScanParams R = P;
     R.cand_rows = J.short_rows.p; R.out_keys = J.keys_rr.p;
+    if (n_ranks > 1) {   // groups of other ranks are not re-scored here: their lists must read as empty
+        R.group_lo = (int)((int64_t)J.n_groups * rank / n_ranks);
+        R.group_hi = (int)((int64_t)J.n_groups * (rank + 1) / n_ranks);
+        CK(cudaMemsetAsync(J.keys_rr.p, 0, J.n_rr * 32 * (size_t)J.Kp * 8, s->stream));
+    }
     TRY((launch_scan_plain<EPI_TOPK, false>(s, R, J.rr_items.p, J.n_rr_sm, J.n_rr_gl, J.max_smem_arena)));
     ScanParams F = P;
     F.out_keys = J.keys_a.p; F.group_flag = J.group_flag.p;
@@ -1022,6 +1062,11 @@ int fullscan_execute(pk_store* s) {
     ++s->stat_launches;
     CK(cudaGetLastError());
     return PK_OK;
+}
+
+int fullscan_execute(pk_store* s) {
+    TRY(fullscan_shortlists(s));
+    return fullscan_finish(s, nullptr, 1, 0, 1);
 }
 
 int fullscan_fetch(pk_store* s, int32_t* out_id, float* out_score, int32_t* out_cnt) {
@@ -1874,6 +1919,28 @@ int pk_fullscan_execute(pk_store* s) {
     return fullscan_execute(s);
 }
 
+int pk_fullscan_execute_shortlists(pk_store* s) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    CK(cudaSetDevice(s->device));
+    return fullscan_shortlists(s);
+}
+
+int pk_fullscan_shortlist_keys(pk_store* s, uint64_t* d_short) {
+    if (!s || !d_short) return fail(PK_ERR_ARG, "null argument");
+    FullscanJob& J = s->job;
+    if (!J.valid) return fail(PK_ERR_STATE, "pk_fullscan_prepare has not been called");
+    if (!J.lean || J.nq == 0) return PK_OK;
+    CK(cudaSetDevice(s->device));
+    CK(cudaMemcpyAsync(d_short, J.keys_short.p, (size_t)J.nq * J.Ks * 8, cudaMemcpyDeviceToDevice, s->stream));
+    return PK_OK;
+}
+
+int pk_fullscan_execute_finish(pk_store* s, const uint64_t* d_all_short, int n_lists, int rank, int n_ranks) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    CK(cudaSetDevice(s->device));
+    return fullscan_finish(s, d_all_short, n_lists, rank, n_ranks);
+}
+
 int pk_fullscan_fetch(pk_store* s, int32_t* out_id, float* out_score, int32_t* out_cnt) {
     if (!s) return fail(PK_ERR_ARG, "null store");
     if (s->job.valid && s->job.nq > 0 && (!out_cnt || (s->job.k > 0 && (!out_id || !out_score)))) return fail(PK_ERR_ARG, "null output");
@@ -1909,8 +1976,9 @@ int pk_merge_keys(pk_store* s, const uint64_t* d_keys, int n_lists, int nq, int 
     if (!s) return fail(PK_ERR_ARG, "null store");
     if (n_lists < 1 || nq < 0 || k < 0 || k > kMaxK) return fail(PK_ERR_ARG, "bad n_lists/nq/k");
     if (nq == 0) return PK_OK;
-    if (k == 0) { for (int q = 0; q < nq; ++q) out_cnt[q] = 0; return PK_OK; }
-    if (!d_keys || !out_id || !out_score || !out_cnt) return fail(PK_ERR_ARG, "null argument");
+    const bool device_only = !out_id && !out_score && !out_cnt;     // merge on the device, fetch nothing (asynchronous)
+    if (k == 0) { for (int q = 0; q < nq && out_cnt; ++q) out_cnt[q] = 0; return PK_OK; }
+    if (!d_keys || (!device_only && (!out_id || !out_score || !out_cnt))) return fail(PK_ERR_ARG, "null argument");
     if (n_lists > 128 * 8) return fail(PK_ERR_UNSUPPORTED, "at most 1024 lists");
     CK(cudaSetDevice(s->device));
     TRY(s->d_keys_c.reserve((size_t)nq * k));
@@ -1920,6 +1988,7 @@ int pk_merge_keys(pk_store* s, const uint64_t* d_keys, int n_lists, int nq, int 
     merge_topk_kernel<<<nq, 128, 0, s->stream>>>(M);
     ++s->stat_launches;
     CK(cudaGetLastError());
+    if (device_only) return PK_OK;
     std::vector<uint64_t> keys((size_t)nq * k);
     CK(cudaMemcpyAsync(keys.data(), s->d_keys_c.p, keys.size() * 8, cudaMemcpyDeviceToHost, s->stream));
     s->stat_d2h += (int64_t)keys.size() * 8;

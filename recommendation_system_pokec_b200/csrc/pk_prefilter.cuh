@@ -321,7 +321,8 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                         m = ((e1.x == key) ? e1.y : 0u) | ((e1.z == key) ? e1.w : 0u) | ((e2.x == key) ? e2.y : 0u) |
                             ((e2.z == key) ? e2.w : 0u);
                     }
-                    if (__ballot_sync(kFull, m != 0u) == 0u) continue;
+                    const uint32_t hit_lanes = __ballot_sync(kFull, m != 0u);
+                    if (hit_lanes == 0u) continue;
                     const uint32_t mine = transpose32(m, lane);
                     const uint32_t ncl_here = (pcl > e0) ? min(pcl - e0, 32u) : 0u;           // warp-uniform
                     const uint32_t cmask = (ncl_here >= 32u) ? 0xffffffffu : ((1u << ncl_here) - 1u);
@@ -357,7 +358,8 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                         id = ((e1.x == key) ? e1.y : 0u) | ((e1.z == key) ? e1.w : 0u) | ((e2.x == key) ? e2.y : 0u) |
                              ((e2.z == key) ? e2.w : 0u);
                     }
-                    if (__ballot_sync(kFull, id != 0u) == 0u) continue;
+                    const uint32_t hit_lanes = __ballot_sync(kFull, id != 0u);
+                    if (hit_lanes == 0u) continue;
                     if (id) {
                         const uint2 en = t_ent[id - 1u];
                         m = en.x;

@@ -220,6 +220,7 @@ struct ScanParams {
     const double* tab_age;
     const int32_t* cand_rows;    // explicit candidate rows (negative = skip), or null = the row index itself
     const int32_t* group_flag;   // when set: CTAs of groups whose flag is 0 exit at once (fallback pass of the full scan)
+    int group_lo, group_hi;      // CTAs of groups outside [group_lo, group_hi) exit at once (re-score split over ranks)
     int T;
     int K, Kp;                   // top-k and its padding to a multiple of 32
     int exclude_mode;
@@ -310,6 +311,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
     const WorkItem it = P.items[blockIdx.x];
     const GroupDesc* gd = P.groups + it.group;
     if (P.group_flag && P.group_flag[it.group] == 0) return;   // uniform for the CTA
+    if (it.group < P.group_lo || it.group >= P.group_hi) return;
 
     // ---- shared memory carve-up ------------------------------------------------------------
     const uint32_t arena_sm = SM ? P.smem_arena_bytes : 0u;

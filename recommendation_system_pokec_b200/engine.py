@@ -25,6 +25,7 @@ ABI_SYMBOLS = (
     "pk_store_load_world", "pk_store_set_shard", "pk_set_normalizers", "pk_compute_idf", "pk_set_idf",
     "pk_idf_size", "pk_get_idf", "pk_set_adj_row", "pk_pair_similarity", "pk_pair_fields", "pk_pair_overlap",
     "pk_fullscan_topk", "pk_fullscan_prepare", "pk_fullscan_execute", "pk_fullscan_fetch", "pk_fullscan_keys", "pk_recommend", "pk_candidates", "pk_fullscan_local_keys", "pk_merge_keys", "pk_sync",
+    "pk_fullscan_execute_shortlists", "pk_fullscan_shortlist_keys", "pk_fullscan_execute_finish",
     "pk_stream", "pk_stat", "pk_debug_prefilter",
 )
 STAT_KERNEL_LAUNCHES, STAT_PAIRS_SCORED, STAT_STORE_BYTES, STAT_SCAN_KERNEL_NS, STAT_SCAN_LAUNCHES, STAT_GROUPS, \
@@ -185,6 +186,16 @@ class DeviceRecommender:
     def fullscan_execute(self):
         _check(self.lib, self.lib.pk_fullscan_execute(self.h))
 
+    def fullscan_execute_shortlists(self):
+        _check(self.lib, self.lib.pk_fullscan_execute_shortlists(self.h))
+
+    def fullscan_shortlist_keys(self, d_short_ptr: int):
+        _check(self.lib, self.lib.pk_fullscan_shortlist_keys(self.h, C.c_void_p(d_short_ptr)))
+
+    def fullscan_execute_finish(self, d_all_short_ptr, n_lists, rank, n_ranks):
+        p = C.c_void_p(d_all_short_ptr) if d_all_short_ptr else None
+        _check(self.lib, self.lib.pk_fullscan_execute_finish(self.h, p, int(n_lists), int(rank), int(n_ranks)))
+
     def fullscan_fetch(self):
         ids, sc, cnt = self._alloc(*self._job_shape)
         _check(self.lib, self.lib.pk_fullscan_fetch(self.h, ptr(ids, i32p), ptr(sc, f32p), ptr(cnt, i32p)))
@@ -228,7 +239,11 @@ class DeviceRecommender:
         _check(self.lib, self.lib.pk_fullscan_local_keys(self.h, len(q), ptr(q, i32p), int(k), int(exclude_mode),
                                                          C.c_void_p(d_keys_ptr)))
 
-    def merge_keys(self, d_keys_ptr: int, n_lists, nq, k):
+    def merge_keys(self, d_keys_ptr: int, n_lists, nq, k, fetch=True):
+        if not fetch:      # device merge only, asynchronous
+            _check(self.lib, self.lib.pk_merge_keys(self.h, C.c_void_p(d_keys_ptr), int(n_lists), int(nq), int(k),
+                                                    None, None, None))
+            return None
         ids, sc, cnt = self._alloc(nq, k)
         _check(self.lib, self.lib.pk_merge_keys(self.h, C.c_void_p(d_keys_ptr), int(n_lists), int(nq), int(k),
                                                 ptr(ids, i32p), ptr(sc, f32p), ptr(cnt, i32p)))

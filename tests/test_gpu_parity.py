@@ -250,6 +250,65 @@ def test_sharded_scan_and_key_merge(env):
         assert np.array_equal(x, y)
 
 
+def sharded_pipeline(dev, w, q, k, exclude, cuts):
+    """the N-rank full scan on one GPU (rank r = candidate rows [cuts[r], cuts[r+1])): pre-filter per shard, gather the
+    approximate shortlists, prove + re-score the owned groups per rank, merge the per-rank keys"""
+    import torch
+    from recommendation_system_pokec_b200.engine import STAT_SHORTLIST
+    n_ranks = len(cuts) - 1
+    shorts = None
+    for r in range(n_ranks):
+        dev.set_shard(cuts[r], cuts[r + 1])
+        dev.fullscan_prepare(q, k, exclude)
+        ks = dev.stat(STAT_SHORTLIST)
+        assert ks > 0, "the pre-filter was expected to run"
+        if shorts is None:
+            shorts = torch.zeros((n_ranks, len(q), ks), dtype=torch.int64, device="cuda")
+        dev.fullscan_execute_shortlists()
+        dev.fullscan_shortlist_keys(shorts[r].data_ptr())
+        dev.sync()
+    keys = torch.zeros((n_ranks, len(q), k), dtype=torch.int64, device="cuda")
+    for r in range(n_ranks):
+        dev.set_shard(cuts[r], cuts[r + 1])
+        dev.fullscan_prepare(q, k, exclude)
+        dev.fullscan_execute_shortlists()        # rebuilds the group tables of this `rank`
+        dev.fullscan_execute_finish(shorts.data_ptr(), n_ranks, r, n_ranks)
+        dev.fullscan_keys(keys[r].data_ptr())
+        dev.sync()
+    dev.set_shard(0, w.n)
+    return dev.merge_keys(keys.data_ptr(), n_ranks, len(q), k), keys
+
+
+def test_sharded_scan_with_shared_rescore(env):
+    """every rank proves the merged shortlist and re-scores only the query groups it owns; the merged result is
+    identical to the unsharded scan (pk_fullscan_execute_shortlists / _finish)"""
+    w, dev, orc = env
+    q = sample_queries(w, 150, seed=14)          # 5 groups over 3 ranks: 1 / 2 / 2
+    full = dev.fullscan(q, 50, EXCLUDE_SELF_AND_ADJ)
+    merged, keys = sharded_pipeline(dev, w, q, 50, EXCLUDE_SELF_AND_ADJ, [0, w.n // 3 + 5, 2 * w.n // 3 - 11, w.n])
+    owned = (keys != 0).any(dim=2).sum(dim=0).cpu().numpy()
+    assert (owned == 1).all(), "every query must be re-scored by exactly one rank"
+    for x, y in zip(merged, full):
+        assert np.array_equal(x, y)
+
+
+def test_sharded_scan_tie_heavy_fallback(oracle_libs):
+    """unproven queries in the N-rank pipeline: every rank runs their exact scan over its own shard, the key merge
+    puts the shards together -- identical to the unsharded result"""
+    from recommendation_system_pokec_b200.engine import DeviceRecommender, STAT_FALLBACK_QUERIES
+    w = make_test_world(n=4000, seed=5, T=2, pairs=800)
+    w.age[:] = 20 + (w.age % 3)
+    w.comp[:] = 50
+    dev = DeviceRecommender(w)
+    q = sample_queries(w, 40, seed=2)            # 2 groups, one per rank
+    full = dev.fullscan(q, 50, EXCLUDE_SELF)
+    assert dev.stat(STAT_FALLBACK_QUERIES) > 0, "the world was meant to defeat the shortlist proof"
+    merged, _ = sharded_pipeline(dev, w, q, 50, EXCLUDE_SELF, [0, 1700, w.n])
+    for x, y in zip(merged, full):
+        assert np.array_equal(x, y)
+    dev.close()
+
+
 def test_vs_compiled_reference(small_world, oracle_libs):
     """the same comparison against the UNMODIFIED reference built from /root/reference (when the prebuilt
     library travelled with the snapshot)"""

@@ -57,13 +57,30 @@ def main():
     local = torch.zeros((B, k), dtype=torch.int64, device=f"cuda:{lr}")
     gathered = torch.zeros((ws, B, k), dtype=torch.int64, device=f"cuda:{lr}")
 
+    bufs = {}
+
     def run_batch(b):
         q = w.uid[(b * B) % w.n:(b * B) % w.n + B].astype(np.int32)
         if len(q) < B:
             q = np.concatenate([q, w.uid[:B - len(q)].astype(np.int32)])
         if ws == 1:
             return dev.fullscan(q, k, EXCLUDE_SELF_AND_ADJ)
-        dev.fullscan_local_keys(q, k, EXCLUDE_SELF_AND_ADJ, local.data_ptr())
+        from recommendation_system_pokec_b200 import engine
+        dev.fullscan_prepare(q, k, EXCLUDE_SELF_AND_ADJ)
+        ks = dev.stat(engine.STAT_SHORTLIST)
+        if ks > 0:      # shared exact re-score
+            if "s" not in bufs:
+                bufs["s"] = (torch.zeros((B, ks), dtype=torch.int64, device=f"cuda:{lr}"),
+                             torch.zeros((ws, B, ks), dtype=torch.int64, device=f"cuda:{lr}"))
+            ls, gs = bufs["s"]
+            dev.fullscan_execute_shortlists()
+            dev.fullscan_shortlist_keys(ls.data_ptr())
+            with torch.cuda.stream(stream):
+                dist.all_gather_into_tensor(gs.view(-1), ls.view(-1))
+            dev.fullscan_execute_finish(gs.data_ptr(), ws, rank, ws)
+        else:
+            dev.fullscan_execute()
+        dev.fullscan_keys(local.data_ptr())
         with torch.cuda.stream(stream):
             dist.all_gather_into_tensor(gathered.view(-1), local.view(-1))
         return dev.merge_keys(gathered.data_ptr(), ws, B, k)
