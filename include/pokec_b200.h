@@ -101,6 +101,16 @@ int pk_pair_similarity(pk_store* s, int64_t n, const int32_t* a_uid, const int32
  * src/recommender.cpp:116,127,138.) */
 int pk_pair_fields(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid, float* out);
 
+/* Replaces compute_column_normalizers (src/utils.cpp:155-240) for a caller-supplied sample of n user pairs (the
+ * reference draws them with mt19937(12345) from its unordered_map's iteration order, which only the caller's C++
+ * side can reproduce): per field -- the 7 fixed keys then the text columns, as in pk_set_normalizers -- the mean and
+ * the sample standard deviation (1.0 when 0 or n < 2) of the RAW similarities, 0 where a field is absent on a side,
+ * raw-count cosine (src/utils.cpp:99-121) for every text column whatever idf tables are set.  The per-pair
+ * similarities come from the device; the sums run in pair order in double, so the floats are bit-identical to the
+ * reference's.  Fails with PK_ERR_ARG when a pair names a user without a profile (the reference's at() throws). */
+int pk_normalizers_from_pairs(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid, float* out_mean,
+                              float* out_sd);
+
 /* Set-overlap counts of n pairs (which: 0 clubs, 1 friends), the integer numerator of
  * vec_set_similarity (src/recommender.cpp:119-128); -1 when either uid has no profile. */
 int pk_pair_overlap(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid, int which, int32_t* out);

@@ -142,6 +142,7 @@ struct pk_store {
     std::vector<int32_t> uid;
     std::vector<std::pair<int32_t, int32_t>> uid_sorted;   // (uid, row)
     std::vector<uint32_t> h_ncl, h_nfr, h_ntok;
+    std::vector<int32_t> h_pub, h_gender, h_comp, h_age;   // scalar fields (pk_normalizers_from_pairs)
     std::vector<int32_t> adj_uid;
     std::vector<int64_t> adj_ptr;
     std::vector<int32_t> adj;
@@ -1693,6 +1694,8 @@ int pk_store_load_world(pk_store* s, const pk_world* w) {
     for (int i = 1; i < n; ++i)
         if (s->uid_sorted[i].first == s->uid_sorted[i - 1].first) return fail(PK_ERR_ARG, "duplicate profile uid %d", s->uid_sorted[i].first);
     s->h_ncl.resize(n); s->h_nfr.resize(n); s->h_ntok.assign(n, 0);
+    s->h_pub.assign(w->pub, w->pub + n); s->h_gender.assign(w->gender, w->gender + n);
+    s->h_comp.assign(w->comp, w->comp + n); s->h_age.assign(w->age, w->age + n);
     s->max_comp = 0; s->max_age = 0;
     for (int i = 0; i < n; ++i) {
         s->h_ncl[i] = (uint32_t)(w->clubs_ptr[i + 1] - w->clubs_ptr[i]);
@@ -1885,6 +1888,72 @@ int pk_pair_fields(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* 
     const int nfo = 3 + s->T, nf = nfo + 2;
     for (int64_t i = 0; i < n; ++i)
         for (int j = 0; j < nfo; ++j) out[i * nfo + j] = where[i] < 0 ? -1.0f : fields[(size_t)where[i] * nf + j];
+    return PK_OK;
+}
+
+// compute_column_normalizers (src/utils.cpp:155-240) for a caller-supplied pair sample: per field the mean and
+// the sample standard deviation of the RAW similarities (0 where a field is absent, raw-count cosine for every
+// text column whatever idf tables are set), accumulated in pair order in double exactly as the reference does.
+int pk_normalizers_from_pairs(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid, float* out_mean, float* out_sd) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
+    if (n < 0 || (n > 0 && (!a_uid || !b_uid)) || !out_mean || !out_sd) return fail(PK_ERR_ARG, "bad argument");
+    CK(cudaSetDevice(s->device));
+    const int T = s->T, nfo = 3 + T, nf = nfo + 2, NF = kNumFixed + T;
+    for (int64_t i = 0; i < n; ++i)
+        if (s->row_of(a_uid[i]) < 0 || s->row_of(b_uid[i]) < 0)
+            return fail(PK_ERR_ARG, "pair %lld names a user without a profile", (long long)i);   // the reference's profiles.at() throws
+    // raw-count weights: every column temporarily loses its idf table (src/recommender_similarity.cpp:103 path),
+    // the packed store is rebuilt for the sample and again, lazily, for the next scoring call
+    const std::vector<uint8_t> saved = s->col_state;
+    std::fill(s->col_state.begin(), s->col_state.end(), (uint8_t)0);
+    s->idf_dirty = true; s->store_dirty = true;
+    std::vector<float> vals((size_t)n * nfo);        // region, clubs, friends, text columns of every pair
+    int rc = ensure_ready(s);
+    for (int64_t p0 = 0; rc == PK_OK && p0 < n; p0 += 32768) {       // the kernel's [32 x 32] blocks stay bounded
+        const int64_t m = std::min<int64_t>(32768, n - p0);
+        std::vector<float> f, fields;
+        std::vector<int64_t> where;
+        rc = pairs_run<true>(s, m, a_uid + p0, b_uid + p0, f, fields, where);
+        if (rc != PK_OK) break;
+        for (int64_t i = 0; i < m; ++i)
+            memcpy(&vals[(size_t)(p0 + i) * nfo], &fields[(size_t)where[i] * nf], (size_t)nfo * 4);
+    }
+    s->col_state = saved;
+    s->idf_dirty = true; s->store_dirty = true;
+    if (rc != PK_OK) return rc;
+    // per-field value of pair i, in the reference's field order (public, gender, completion, age, region, clubs,
+    // friends, text columns); -1 from the kernel = field absent on a side = the reference's 0.0
+    auto value = [&](int64_t i, int fld) -> double {
+        const int ra = s->row_of(a_uid[i]), rb = s->row_of(b_uid[i]);
+        switch (fld) {
+            case 0: return (s->h_pub[ra] >= 0 && s->h_pub[rb] >= 0 && s->h_pub[ra] == s->h_pub[rb]) ? 1.0 : 0.0;
+            case 1: return (s->h_gender[ra] >= 0 && s->h_gender[rb] >= 0 && s->h_gender[ra] == s->h_gender[rb]) ? 1.0 : 0.0;
+            case 2: case 3: {
+                const int x = fld == 2 ? s->h_comp[ra] : s->h_age[ra], y = fld == 2 ? s->h_comp[rb] : s->h_age[rb];
+                if (x <= 0 || y <= 0) return 0.0;
+                return (double)std::min(x, y) / (double)std::max(x, y);
+            }
+            default: {
+                const float v = vals[(size_t)i * nfo + (fld - 4)];             // 4 region, 5 clubs, 6 friends, 7+t text
+                return v < 0.0f ? 0.0 : (double)v;
+            }
+        }
+    };
+    parallel_for(NF, [&](int fld) {
+        if (n == 0) { out_mean[fld] = 0.0f; out_sd[fld] = 1.0f; return; }
+        double mu = 0.0;
+        for (int64_t i = 0; i < n; ++i) mu += value(i, fld);
+        mu /= (double)n;
+        double sd = 1.0;
+        if (n > 1) {
+            double acc = 0.0;
+            for (int64_t i = 0; i < n; ++i) { const double d = value(i, fld) - mu; acc += d * d; }
+            sd = std::sqrt(acc / (double)(n - 1));
+            if (sd == 0.0) sd = 1.0;
+        }
+        out_mean[fld] = (float)mu; out_sd[fld] = (float)sd;
+    });
     return PK_OK;
 }
 

@@ -25,7 +25,7 @@ ABI_SYMBOLS = (
     "pk_store_load_world", "pk_store_set_shard", "pk_set_normalizers", "pk_compute_idf", "pk_set_idf",
     "pk_idf_size", "pk_get_idf", "pk_set_adj_row", "pk_pair_similarity", "pk_pair_fields", "pk_pair_overlap",
     "pk_fullscan_topk", "pk_fullscan_prepare", "pk_fullscan_execute", "pk_fullscan_fetch", "pk_fullscan_keys", "pk_recommend", "pk_candidates", "pk_fullscan_local_keys", "pk_merge_keys", "pk_sync",
-    "pk_fullscan_execute_shortlists", "pk_fullscan_shortlist_keys", "pk_fullscan_execute_finish",
+    "pk_normalizers_from_pairs", "pk_fullscan_execute_shortlists", "pk_fullscan_shortlist_keys", "pk_fullscan_execute_finish",
     "pk_stream", "pk_stat", "pk_debug_prefilter",
 )
 STAT_KERNEL_LAUNCHES, STAT_PAIRS_SCORED, STAT_STORE_BYTES, STAT_SCAN_KERNEL_NS, STAT_SCAN_LAUNCHES, STAT_GROUPS, \
@@ -158,6 +158,16 @@ class DeviceRecommender:
         out = np.zeros((len(a), 3 + self.world.T), np.float32)
         _check(self.lib, self.lib.pk_pair_fields(self.h, C.c_int64(len(a)), ptr(a, i32p), ptr(b, i32p), ptr(out, f32p)))
         return out
+
+    def normalizers_from_pairs(self, a, b):
+        """compute_column_normalizers (src/utils.cpp:155-240) on a given pair sample -> (mean, sd), 7 + T floats each"""
+        a = np.ascontiguousarray(a, np.int32)
+        b = np.ascontiguousarray(b, np.int32)
+        nf = self.world.n_fields
+        mean, sd = np.zeros(nf, np.float32), np.zeros(nf, np.float32)
+        _check(self.lib, self.lib.pk_normalizers_from_pairs(self.h, C.c_int64(len(a)), ptr(a, i32p), ptr(b, i32p),
+                                                            ptr(mean, f32p), ptr(sd, f32p)))
+        return mean, sd
 
     def pair_overlap(self, a, b, which):
         a = np.ascontiguousarray(a, np.int32)
