@@ -141,6 +141,18 @@ int pk_fullscan_keys(pk_store* s, uint64_t* d_keys);
 int pk_recommend(pk_store* s, int mode, int nq, const int32_t* q_uid, int k, int limit,
                  int32_t* out_id, float* out_score, int32_t* out_cnt);
 
+/* Per-edge FAS cache.  Both weights of recommend_clubs_collab are FAS values on adjacency
+ * entries -- w_f = FAS(u, f), f in adj[u] (src/recommender_clubs.cpp:23-28), and s = FAS(f, fof), fof in adj[f]
+ * (:56) -- and do not depend on the query.  pk_edge_cache_build scores every loaded adjacency entry once with the
+ * exact kernel (-1 where a side has no profile) and keeps the floats on the device; pk_recommend(PK_MODE_CLUBS)
+ * then only enumerates edges and scatters (same visiting order, same floats, bit-identical results).  The cache is
+ * dropped by pk_store_load_world, pk_set_normalizers, pk_compute_idf and pk_set_idf, and bypassed while rows
+ * replaced with pk_set_adj_row exist.  pk_edge_cache_row reads the cached values of uid's adjacency row (in row
+ * order; *n = row length). */
+int pk_edge_cache_build(pk_store* s);
+int pk_edge_cache_drop(pk_store* s);
+int pk_edge_cache_row(pk_store* s, int32_t uid, float* out, int64_t cap, int64_t* n);
+
 /* Candidate id lists of one user (integer contract): PK_MODE_GRAPH = gather_candidates_local
  * (src/recommender_graph.cpp:10-31), PK_MODE_COLLAB = the FoF expansion of :114-125.
  * Returns the list length in *n (may exceed cap; only cap entries are written). */
@@ -198,7 +210,8 @@ enum {
     PK_STAT_RESCORE_NS = 11,       /* device time of the exact re-score + fallback kernels of the last full scan */
     PK_STAT_SHARD_LEAN_BYTES = 12, /* bytes of the lean fp32 records inside the candidate shard */
     PK_STAT_SHORTLIST = 13,        /* shortlist length Ks of the prepared full scan (0 = no pre-filter) */
-    PK_STAT_MARGIN_E9 = 14         /* the pre-filter's error bound on a FAS value, times 1e9 */
+    PK_STAT_MARGIN_E9 = 14,        /* the pre-filter's error bound on a FAS value, times 1e9 */
+    PK_STAT_EDGE_CACHE = 15        /* adjacency entries held by a valid per-edge FAS cache (0 = none) */
 };
 int64_t pk_stat(pk_store* s, int which);
 

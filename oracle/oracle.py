@@ -179,6 +179,17 @@ class CpuOracle:
         self.lib.ref_column_normalizers(self.h, int(sample_size), int(comps_per_user), ptr(mean, f32p), ptr(sd, f32p))
         return mean, sd
 
+    def normalizer_pairs(self, sample_size=100000, comps_per_user=5):
+        """the (a, b) uid pairs compute_column_normalizers samples (src/utils.cpp:163-181), in its order"""
+        assert self.kind == "reference"
+        cap = int(sample_size) * int(comps_per_user)
+        a = np.zeros(max(cap, 1), np.int32)
+        b = np.zeros(max(cap, 1), np.int32)
+        self.lib.ref_normalizer_pairs.restype = C.c_longlong
+        n = int(self.lib.ref_normalizer_pairs(self.h, int(sample_size), int(comps_per_user), ptr(a, i32p), ptr(b, i32p),
+                                              C.c_longlong(cap)))
+        return a[:n].copy(), b[:n].copy()
+
     def set_adj_row(self, uid, nb):
         assert self.kind == "reference"
         nb = np.ascontiguousarray(nb, np.int32)

@@ -18,6 +18,8 @@
 #include <algorithm>
 #include <atomic>
 #include <cstring>
+#include <random>
+#include <unordered_set>
 #include <string>
 #include <thread>
 #include <vector>
@@ -312,6 +314,36 @@ int ref_column_normalizers(void* hv, int sample_size, int comps_per_user, float*
     return 0;
 }
 #endif
+
+// The pair sample compute_column_normalizers draws (src/utils.cpp:163-181): ids in the iteration order of the
+// reference's unordered_map, mt19937(12345), uniform_int_distribution over the ids, a == b and repeated pairs
+// skipped, at most 10 x the wanted count of attempts.  Restated here (the reference does not expose it) with the
+// same libstdc++ so that the device path can be fed the very pairs the reference scores.  Returns the count.
+long long ref_normalizer_pairs(void* hv, int sample_size, int comps_per_user, int32_t* a_out, int32_t* b_out, long long cap) {
+    auto* h = (RefHandle*)hv;
+    if (h->profiles.empty()) return 0;
+    vector<int> ids;
+    ids.reserve(h->profiles.size());
+    for (auto& kv : h->profiles) ids.push_back(kv.first);
+    mt19937 rng(12345);
+    uniform_int_distribution<size_t> dist(0, ids.size() - 1);
+    const size_t total_needed = (size_t)sample_size * (size_t)comps_per_user;
+    unordered_set<uint64_t> seen;
+    size_t attempts = 0;
+    long long n = 0;
+    while (seen.size() < total_needed && attempts < total_needed * 10) {
+        ++attempts;
+        const int a = ids[dist(rng)];
+        const int b = ids[dist(rng)];
+        if (a == b) continue;
+        uint32_t A = (uint32_t)a, B = (uint32_t)b;
+        if (A > B) swap(A, B);
+        if (!seen.insert(((uint64_t)A << 32) | (uint64_t)B).second) continue;
+        if (n < cap) { a_out[n] = a; b_out[n] = b; }
+        ++n;
+    }
+    return n;
+}
 
 // mutate one adjacency row behind the live Recommender (what src/test.cpp:59-73 does)
 int ref_set_adj_row(void* hv, int uid, int n, const int32_t* nb) {

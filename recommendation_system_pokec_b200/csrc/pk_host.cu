@@ -206,6 +206,11 @@ struct pk_store {
     DevBuf<uint32_t> d_u32a;
     DevBuf<int> d_flag;
     DevBuf<ClubEdge> d_edges;
+    // per-edge FAS cache: FAS(u, v) of every loaded adjacency entry u -> v, aligned with `adj`
+    // (-1 where either side has no profile); valid until the normalizers, the idf tables or the world change
+    DevBuf<float> d_edge_fas;
+    std::vector<float> h_edge_fas;
+    bool edge_cache_valid = false;
     FullscanJob job;
     bool scan_time_pending = false;
     int64_t stat_h2d = 0, stat_d2h = 0;
@@ -1396,7 +1401,144 @@ int recommend_collab(pk_store* s, int nq, const int32_t* q_uid, int k, int limit
     return PK_OK;
 }
 
+// ---- per-edge FAS cache ----------------------------------------------------------------------------------
+// Both weights of recommend_clubs_collab are FAS values on adjacency edges -- w_f = FAS(u, f) for f in adj[u]
+// (src/recommender_clubs.cpp:23-28) and s = FAS(f, fof) for fof in adj[f] (:56) -- and do not depend on the query.
+// Scored once (the exact kernel, pairs mode), they turn the clubs call into edge enumeration + weighted scatter.
+template <bool FIELDS>
+int pairs_run(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid, std::vector<float>& out_f,
+              std::vector<float>& out_fields, std::vector<int64_t>& where);
+
+int edge_cache_build(pk_store* s) {
+    TRY(ensure_ready(s));
+    const int64_t E = (int64_t)s->adj.size();
+    std::vector<int32_t> src((size_t)E);
+    for (size_t r = 0; r < s->adj_uid.size(); ++r)
+        for (int64_t j = s->adj_ptr[r]; j < s->adj_ptr[r + 1]; ++j) src[(size_t)j] = s->adj_uid[r];
+    s->h_edge_fas.assign((size_t)E, -1.0f);
+    int64_t pairs = 0, scan_ns = 0;
+    for (int64_t p0 = 0; p0 < E; p0 += (1 << 20)) {                   // bounded [rows][32] score blocks
+        const int64_t m = std::min<int64_t>(1 << 20, E - p0);
+        std::vector<float> f, fields;
+        std::vector<int64_t> where;
+        TRY(pairs_run<false>(s, m, src.data() + p0, s->adj.data() + p0, f, fields, where));
+        TRY(collect_scan_time(s));
+        pairs += s->stat_pairs; scan_ns += s->stat_scan_ns;
+        for (int64_t i = 0; i < m; ++i)
+            if (where[(size_t)i] >= 0) s->h_edge_fas[(size_t)(p0 + i)] = f[(size_t)where[(size_t)i]];
+    }
+    s->stat_pairs = pairs; s->stat_scan_ns = scan_ns;
+    TRY(upload(s, s->d_edge_fas, s->h_edge_fas));
+    CK(cudaStreamSynchronize(s->stream));
+    s->edge_cache_valid = true;
+    return PK_OK;
+}
+
+int recommend_clubs_cached(pk_store* s, int nq, const int32_t* q_uid, int k, uint64_t* h_keys) {
+    const int K = std::max(k, 1);
+    std::vector<uint64_t> keys((size_t)std::max(nq, 1) * K, 0ull);
+    // users with a profile, in caller order
+    std::vector<int> uq; std::vector<int32_t> urow;
+    for (int q = 0; q < nq; ++q) {
+        const int r = s->row_of(q_uid[q]);
+        if (r < 0) continue;                                             // src/recommender_clubs.cpp:16
+        uq.push_back(q); urow.push_back(r);
+    }
+    const int nu = (int)uq.size();
+    s->stat_pairs = 0; s->stat_groups = 0; s->stat_scan_ns = 0; s->stat_scan_launches = 0;
+    if (nu > 0) {
+        // phase 1 (host threads): every user's edge stream in the reference's visiting order -- 1-hop entries, then
+        // 2-hop entries; the FAS values are indices into the edge cache (position of the adjacency entry)
+        std::vector<std::vector<ClubEdge>> u_edges((size_t)nu);
+        std::vector<std::vector<uint32_t>> u_con((size_t)nu);
+        std::vector<uint64_t> u_total((size_t)nu, 0);
+        parallel_for(nu, [&](int i) {
+            const int32_t uid = q_uid[uq[i]];
+            std::vector<ClubEdge>& ed = u_edges[i];
+            std::vector<uint32_t>& co = u_con[i];
+            uint64_t con = 0;
+            const int32_t *b, *e;
+            if (!s->adj_of(uid, &b, &e)) return;
+            const int64_t e0 = b - s->adj.data();
+            for (const int32_t* pf = b; pf != e; ++pf) {                 // :34-43
+                const int rf = s->row_of(*pf);
+                if (rf < 0) continue;
+                ClubEdge ce;
+                ce.w_idx = e0 + (pf - b); ce.s_idx = -1; ce.target_row = rf; ce.pad_ = 0;
+                co.push_back((uint32_t)std::min<uint64_t>(con, 0xffffffffull));
+                con += s->h_ncl[rf];
+                ed.push_back(ce);
+            }
+            for (const int32_t* pf = b; pf != e; ++pf) {                 // :45-64
+                const int32_t *b2, *e2;
+                if (!s->adj_of(*pf, &b2, &e2)) continue;
+                if (s->row_of(*pf) < 0) continue;
+                const int64_t f0 = b2 - s->adj.data();
+                for (const int32_t* p = b2; p != e2; ++p) {
+                    if (*p == uid) continue;
+                    const int rc = s->row_of(*p);
+                    if (rc < 0) continue;                                // no profile
+                    ClubEdge ce;
+                    ce.w_idx = e0 + (pf - b); ce.s_idx = f0 + (p - b2); ce.target_row = rc; ce.pad_ = 0;
+                    co.push_back((uint32_t)std::min<uint64_t>(con, 0xffffffffull));
+                    con += s->h_ncl[rc];
+                    ed.push_back(ce);
+                }
+            }
+            u_total[i] = con;
+        });
+        std::vector<ClubEdge> edges;
+        std::vector<int32_t> ueb(nu + 1, 0), ucon(nu + 1, 0);
+        std::vector<uint32_t> con_off;
+        for (int i = 0; i < nu; ++i) {
+            const uint64_t con = u_total[i];
+            if (con > 0x7fffffffull) return fail(PK_ERR_UNSUPPORTED, "club contribution stream too large");
+            edges.insert(edges.end(), u_edges[i].begin(), u_edges[i].end());
+            con_off.insert(con_off.end(), u_con[i].begin(), u_con[i].end());
+            std::vector<ClubEdge>().swap(u_edges[i]);
+            std::vector<uint32_t>().swap(u_con[i]);
+            if (edges.size() > 0x7fffffffull) return fail(PK_ERR_UNSUPPORTED, "club batch too large (split the batch)");
+            ueb[i + 1] = (int32_t)edges.size();
+            const int64_t capu = (int64_t)1 << log2_table(std::max<uint64_t>(con, 1));
+            if ((int64_t)ucon[i] + capu > 0x7fffffffll) return fail(PK_ERR_UNSUPPORTED, "club batch too large (split the batch)");
+            ucon[i + 1] = ucon[i] + (int32_t)capu;
+        }
+        const int64_t total_slots = ucon[nu];
+        if (!edges.empty()) {
+            TRY(s->d_edges.reserve(edges.size()));
+            CK(cudaMemcpyAsync(s->d_edges.p, edges.data(), edges.size() * sizeof(ClubEdge), cudaMemcpyHostToDevice, s->stream));
+            TRY(upload(s, s->d_u32a, con_off));
+            TRY(upload(s, s->d_i32a, ueb));
+            TRY(upload(s, s->d_i32b, ucon));
+            TRY(upload(s, s->d_i32c, urow));
+            TRY(s->d_i32d.reserve((size_t)total_slots));
+            TRY(s->d_keys_a.reserve((size_t)total_slots));
+            TRY(s->d_f64a.reserve((size_t)total_slots));
+            TRY(s->d_keys_b.reserve((size_t)nu * K));
+            CK(cudaMemsetAsync(s->d_keys_a.p, 0, (size_t)total_slots * 8, s->stream));
+            CK(cudaMemsetAsync(s->d_f64a.p, 0, (size_t)total_slots * 8, s->stream));
+            ClubParams C;
+            C.rec = s->d_rec.p; C.rec_off = s->d_rec_off.p; C.fas = s->d_edge_fas.p; C.edges = s->d_edges.p;
+            C.con_off = s->d_u32a.p; C.user_edge_begin = s->d_i32a.p; C.user_slot_begin = s->d_i32b.p;
+            C.user_row = s->d_i32c.p; C.con_slot = s->d_i32d.p; C.slot_key = s->d_keys_a.p; C.slot_acc = s->d_f64a.p;
+            clubs_scatter_kernel<<<nu, kClubThreads, 0, s->stream>>>(C);
+            ++s->stat_launches;
+            slice_topk_kernel<<<nu, 256, 0, s->stream>>>(s->d_keys_a.p, s->d_i32b.p, K, s->d_keys_b.p);
+            ++s->stat_launches;
+            CK(cudaGetLastError());
+            std::vector<uint64_t> uk((size_t)nu * K);
+            CK(cudaMemcpyAsync(uk.data(), s->d_keys_b.p, uk.size() * 8, cudaMemcpyDeviceToHost, s->stream));
+            CK(cudaStreamSynchronize(s->stream));
+            for (int i = 0; i < nu; ++i) memcpy(&keys[(size_t)uq[i] * K], &uk[(size_t)i * K], (size_t)K * 8);
+        }
+    }
+    memcpy(h_keys, keys.data(), (size_t)nq * K * 8);
+    return PK_OK;
+}
+
 int recommend_clubs(pk_store* s, int nq, const int32_t* q_uid, int k, uint64_t* h_keys) {
+    // the cache mirrors the LOADED adjacency: rows replaced behind the store (pk_set_adj_row) bypass it
+    if (s->edge_cache_valid && s->adj_override.empty()) return recommend_clubs_cached(s, nq, q_uid, k, h_keys);
     const int K = std::max(k, 1);
     std::vector<CollabUser> users;
     Plan plan;
@@ -1738,12 +1880,12 @@ int pk_store_load_world(pk_store* s, const pk_world* w) {
     s->col_state.assign(T, 0);
     s->custom_tok.assign(T, {});
     s->custom_idf.assign(T, {});
-    s->idf_dirty = true; s->store_dirty = true;
+    s->idf_dirty = true; s->store_dirty = true; s->edge_cache_valid = false;
     const int nf = kNumFixed + T;
     s->nmean.assign(nf, 0.f); s->nsd.assign(nf, 0.f); s->nhas.assign(nf, 0);
     if (w->norm_mean && w->norm_sd && w->norm_has)
         for (int f = 0; f < nf; ++f) { s->nmean[f] = w->norm_mean[f]; s->nsd[f] = w->norm_sd[f]; s->nhas[f] = w->norm_has[f]; }
-    s->norm_dirty = true;
+    s->norm_dirty = true; s->edge_cache_valid = false;
     s->shard_begin = 0; s->shard_end = n;
     s->loaded = true;
     return PK_OK;
@@ -1763,7 +1905,7 @@ int pk_set_normalizers(pk_store* s, const float* mean, const float* sd, const ui
     if (n_fields != kNumFixed + s->T) return fail(PK_ERR_ARG, "n_fields = %d, expected %d", n_fields, kNumFixed + s->T);
     if (!mean || !sd) return fail(PK_ERR_ARG, "null normalizer array");
     for (int f = 0; f < n_fields; ++f) { s->nmean[f] = mean[f]; s->nsd[f] = sd[f]; s->nhas[f] = has ? has[f] : 1; }
-    s->norm_dirty = true;
+    s->norm_dirty = true; s->edge_cache_valid = false;
     return PK_OK;
 }
 
@@ -1772,7 +1914,7 @@ int pk_compute_idf(pk_store* s, int double_log) {
     if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
     for (int t = 0; t < s->T; ++t) { s->col_state[t] = 1; s->custom_tok[t].clear(); s->custom_idf[t].clear(); }
     s->double_log = double_log ? 1 : 0;
-    s->idf_dirty = true;
+    s->idf_dirty = true; s->edge_cache_valid = false;
     CK(cudaSetDevice(s->device));
     return rebuild_idf(s);
 }
@@ -1791,7 +1933,7 @@ int pk_set_idf(pk_store* s, int col, const int32_t* token, const float* idf, int
         s->custom_tok[col].assign(token, token + n);
         s->custom_idf[col].assign(idf, idf + n);
     }
-    s->idf_dirty = true;
+    s->idf_dirty = true; s->edge_cache_valid = false;
     return PK_OK;
 }
 
@@ -1954,6 +2096,34 @@ int pk_normalizers_from_pairs(pk_store* s, int64_t n, const int32_t* a_uid, cons
         }
         out_mean[fld] = (float)mu; out_sd[fld] = (float)sd;
     });
+    return PK_OK;
+}
+
+int pk_edge_cache_build(pk_store* s) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
+    CK(cudaSetDevice(s->device));
+    return edge_cache_build(s);
+}
+
+int pk_edge_cache_drop(pk_store* s) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    s->edge_cache_valid = false;
+    return PK_OK;
+}
+
+int pk_edge_cache_row(pk_store* s, int32_t uid, float* out, int64_t cap, int64_t* n) {
+    if (!s || !n || (cap > 0 && !out)) return fail(PK_ERR_ARG, "null argument");
+    if (!s->edge_cache_valid) return fail(PK_ERR_STATE, "no valid edge cache (pk_edge_cache_build)");
+    *n = 0;
+    const int64_t i = (int64_t)uid - s->uid_lo;
+    int32_t r = -1;
+    if (!s->adj_direct.empty()) r = (i >= 0 && i < (int64_t)s->adj_direct.size()) ? s->adj_direct[(size_t)i] : -1;
+    else { auto it = s->adj_row.find(uid); if (it != s->adj_row.end()) r = it->second; }
+    if (r < 0) return PK_OK;
+    const int64_t b = s->adj_ptr[r], e = s->adj_ptr[r + 1];
+    *n = e - b;
+    for (int64_t j = b; j < e && j - b < cap; ++j) out[j - b] = s->h_edge_fas[(size_t)j];
     return PK_OK;
 }
 
@@ -2177,6 +2347,7 @@ int64_t pk_stat(pk_store* s, int which) {
         }
         case PK_STAT_SHORTLIST: return s->job.valid && s->job.lean ? s->job.Ks : 0;
         case PK_STAT_MARGIN_E9: return (int64_t)((double)s->margin * 1e9);
+        case PK_STAT_EDGE_CACHE: return s->edge_cache_valid ? (int64_t)s->h_edge_fas.size() : 0;
         default: return -1;
     }
 }

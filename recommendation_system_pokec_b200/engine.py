@@ -25,12 +25,12 @@ ABI_SYMBOLS = (
     "pk_store_load_world", "pk_store_set_shard", "pk_set_normalizers", "pk_compute_idf", "pk_set_idf",
     "pk_idf_size", "pk_get_idf", "pk_set_adj_row", "pk_pair_similarity", "pk_pair_fields", "pk_pair_overlap",
     "pk_fullscan_topk", "pk_fullscan_prepare", "pk_fullscan_execute", "pk_fullscan_fetch", "pk_fullscan_keys", "pk_recommend", "pk_candidates", "pk_fullscan_local_keys", "pk_merge_keys", "pk_sync",
-    "pk_normalizers_from_pairs", "pk_fullscan_execute_shortlists", "pk_fullscan_shortlist_keys", "pk_fullscan_execute_finish",
+    "pk_normalizers_from_pairs", "pk_edge_cache_build", "pk_edge_cache_drop", "pk_edge_cache_row", "pk_fullscan_execute_shortlists", "pk_fullscan_shortlist_keys", "pk_fullscan_execute_finish",
     "pk_stream", "pk_stat", "pk_debug_prefilter",
 )
 STAT_KERNEL_LAUNCHES, STAT_PAIRS_SCORED, STAT_STORE_BYTES, STAT_SCAN_KERNEL_NS, STAT_SCAN_LAUNCHES, STAT_GROUPS, \
     STAT_SHARD_RECORD_BYTES, STAT_H2D_BYTES, STAT_D2H_BYTES, STAT_PREFILTER, STAT_FALLBACK_QUERIES, STAT_RESCORE_NS, \
-    STAT_SHARD_LEAN_BYTES, STAT_SHORTLIST, STAT_MARGIN_E9 = range(15)
+    STAT_SHARD_LEAN_BYTES, STAT_SHORTLIST, STAT_MARGIN_E9, STAT_EDGE_CACHE = range(16)
 
 _lib = None
 
@@ -168,6 +168,19 @@ class DeviceRecommender:
         _check(self.lib, self.lib.pk_normalizers_from_pairs(self.h, C.c_int64(len(a)), ptr(a, i32p), ptr(b, i32p),
                                                             ptr(mean, f32p), ptr(sd, f32p)))
         return mean, sd
+
+    # ---- per-edge FAS cache (clubs) ---------------------------------------------------------------
+    def edge_cache_build(self):
+        _check(self.lib, self.lib.pk_edge_cache_build(self.h))
+
+    def edge_cache_drop(self):
+        _check(self.lib, self.lib.pk_edge_cache_drop(self.h))
+
+    def edge_cache_row(self, uid, cap=1 << 16):
+        out = np.zeros(cap, np.float32)
+        n = C.c_int64()
+        _check(self.lib, self.lib.pk_edge_cache_row(self.h, int(uid), ptr(out, f32p), C.c_int64(cap), C.byref(n)))
+        return out[:min(int(n.value), cap)].copy()
 
     def pair_overlap(self, a, b, which):
         a = np.ascontiguousarray(a, np.int32)

@@ -309,6 +309,81 @@ def test_sharded_scan_tie_heavy_fallback(oracle_libs):
     dev.close()
 
 
+def test_edge_cache_clubs_identical(small_world, oracle_libs):
+    """the per-edge FAS cache holds exactly the floats pk_pair_similarity returns, the clubs call
+    served from it is bit-identical to the scan-based one and to the oracle, and every setter drops it"""
+    from oracle.oracle import CpuOracle
+    from recommendation_system_pokec_b200.engine import DeviceRecommender, STAT_EDGE_CACHE, STAT_PAIRS_SCORED
+    w = small_world
+    dev, orc = DeviceRecommender(w), CpuOracle(w, "port")
+    q = sample_queries(w, 120, seed=31)
+    q = np.concatenate([q, np.array([10 ** 8], np.int32)])            # an unknown user rides along
+    plain = dev.recommend(MODE_CLUBS, q, 30, 5000)
+    assert dev.stat(STAT_EDGE_CACHE) == 0 and dev.stat(STAT_PAIRS_SCORED) > 0
+    dev.edge_cache_build()
+    assert dev.stat(STAT_EDGE_CACHE) == len(w.adj)
+    # cached floats == the pair kernel's floats, in adjacency order (-1 for neighbours without a profile)
+    rng = np.random.default_rng(5)
+    for r in rng.integers(0, len(w.adj_uid), 25):
+        u = int(w.adj_uid[r])
+        nb = w.adj[w.adj_ptr[r]:w.adj_ptr[r + 1]].astype(np.int32)
+        got = dev.edge_cache_row(u)
+        want = dev.pair_similarity(np.full(len(nb), u, np.int32), nb)
+        assert got.tobytes() == want.tobytes()
+    cached = dev.recommend(MODE_CLUBS, q, 30, 5000)
+    assert dev.stat(STAT_PAIRS_SCORED) == 0, "the cached call must not score pairs"
+    for x, y in zip(cached, plain):
+        assert np.array_equal(x, y)
+    assert_topk_equal(cached, orc.recommend(MODE_CLUBS, q, 30, 5000, 4), "clubs from the edge cache")
+    # a row replaced behind the store bypasses the cache (and still matches the oracle) ...
+    u = int(w.adj_uid[3])
+    new_row = w.uid[:7].astype(np.int32)
+    dev.set_adj_row(u, new_row)
+    got = dev.recommend(MODE_CLUBS, np.array([u], np.int32), 30, 5000)
+    assert dev.stat(STAT_PAIRS_SCORED) > 0
+    dev.set_adj_row(u, w.adj[w.adj_ptr[3]:w.adj_ptr[4]].astype(np.int32))     # restored: served from the cache again
+    dev.recommend(MODE_CLUBS, np.array([u], np.int32), 30, 5000)
+    assert dev.stat(STAT_PAIRS_SCORED) == 0
+    # ... and the setters drop it
+    dev.set_normalizers(w.norm_mean, w.norm_sd)
+    assert dev.stat(STAT_EDGE_CACHE) == 0
+    dev.edge_cache_build()
+    dev.compute_idf()
+    assert dev.stat(STAT_EDGE_CACHE) == 0
+    dev.close()
+    orc.close()
+
+
+def test_column_normalizers_bit_exact(small_world, oracle_libs):
+    """compute_column_normalizers (src/utils.cpp:155-240) -- per-pair raw similarities from the
+    device (raw-count cosines whatever idf is set), sums in the reference's order: every mean / sd float identical;
+    the scoring path afterwards still sees the tf-idf weights"""
+    from oracle.oracle import CpuOracle, reference_available
+    from recommendation_system_pokec_b200.engine import DeviceRecommender
+    if not reference_available():
+        pytest.skip("oracle/_ref did not travel")
+    w = small_world
+    ref = CpuOracle(w, "reference")
+    dev = DeviceRecommender(w)
+    q = sample_queries(w, 40, seed=3)
+    before = dev.fullscan(q, 20, EXCLUDE_SELF_AND_ADJ)
+    for sample, comps in ((400, 5), (1, 1), (50, 3)):
+        mean, sd = ref.column_normalizers(sample, comps)
+        a, b = ref.normalizer_pairs(sample, comps)
+        gm, gs = dev.normalizers_from_pairs(a, b)
+        assert gm.tobytes() == mean.tobytes(), f"means differ ({sample} x {comps}): {np.flatnonzero(gm != mean)}"
+        assert gs.tobytes() == sd.tobytes(), f"sds differ ({sample} x {comps}): {np.flatnonzero(gs != sd)}"
+    after = dev.fullscan(q, 20, EXCLUDE_SELF_AND_ADJ)
+    for x, y in zip(before, after):
+        assert np.array_equal(x, y), "the idf state must be restored after the raw-count pass"
+    gm, gs = dev.normalizers_from_pairs(np.zeros(0, np.int32), np.zeros(0, np.int32))
+    assert (gm == 0).all() and (gs == 1).all()
+    with pytest.raises(Exception):
+        dev.normalizers_from_pairs(np.array([int(w.uid[0])], np.int32), np.array([-5], np.int32))
+    dev.close()
+    ref.close()
+
+
 def test_vs_compiled_reference(small_world, oracle_libs):
     """the same comparison against the UNMODIFIED reference built from /root/reference (when the prebuilt
     library travelled with the snapshot)"""

@@ -108,3 +108,40 @@ def test_port_vs_compiled_reference(oracle_libs):
     check_topk(port.fullscan(q[:12], 50, 2, nthreads=8), ref.fullscan(q[:12], 50, 2, nthreads=8), "fullscan vs reference")
     port.close()
     ref.close()
+
+
+def test_normalizer_pair_sample_matches_the_reference(oracle_libs):
+    """oracle/ref_driver.cpp restates the pair sampling of compute_column_normalizers (src/utils.cpp:163-181); the
+    scalar fields recomputed from those pairs in numpy (double sums in pair order) must reproduce the reference's
+    mean / sd floats bit for bit -- which pins the sample the GPU test feeds to pk_normalizers_from_pairs"""
+    from oracle.oracle import CpuOracle, reference_available
+    if not reference_available():
+        pytest.skip("oracle/_ref was not built (no /root/reference here)")
+    from tests.conftest import make_test_world
+    w = make_test_world(n=2000, seed=13, T=8, pairs=500)
+    orc = CpuOracle(w, "reference")
+    mean, sd = orc.column_normalizers(300, 5)
+    a, b = orc.normalizer_pairs(300, 5)
+    assert len(a) == 1500 and (a != b).all()
+    row = {int(u): i for i, u in enumerate(w.uid)}
+    ra = np.array([row[int(x)] for x in a])
+    rb = np.array([row[int(x)] for x in b])
+
+    def stats(v):
+        mu = 0.0
+        for x in v:
+            mu += float(x)
+        mu /= len(v)
+        acc = 0.0
+        for x in v:
+            acc += (float(x) - mu) ** 2
+        s = np.sqrt(acc / (len(v) - 1))
+        return np.float32(mu), np.float32(1.0 if s == 0 else s)
+
+    pub = ((w.pub[ra] >= 0) & (w.pub[rb] >= 0) & (w.pub[ra] == w.pub[rb])).astype(np.float64)
+    x, y = w.age[ra].astype(np.float64), w.age[rb].astype(np.float64)
+    age = np.where((x > 0) & (y > 0), np.minimum(x, y) / np.maximum(np.maximum(x, y), 1.0), 0.0)
+    for fld, v in ((0, pub), (3, age)):
+        m, s = stats(v)
+        assert m.tobytes() == mean[fld].tobytes() and s.tobytes() == sd[fld].tobytes(), f"field {fld}"
+    orc.close()

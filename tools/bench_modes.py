@@ -52,8 +52,34 @@ def main():
     from oracle.oracle import CpuOracle, reference_available
     kind = "reference" if reference_available() else "port"
     orc = CpuOracle(w, kind) if args.cpu_queries > 0 else None
-    names = {"graph": MODE_GRAPH, "collab": MODE_COLLAB, "clubs": MODE_CLUBS}
+    names = {"graph": MODE_GRAPH, "collab": MODE_COLLAB, "clubs": MODE_CLUBS, "clubs_cached": MODE_CLUBS}
     for name in args.modes.split(","):
+        if name == "normalizers":
+            # compute_column_normalizers(profiles, cols, 100000, 5) (src/utils.cpp:155-240, api_cli's
+            # start-up call): the reference on one host core (as shipped) against pk_normalizers_from_pairs on the
+            # reference's own pair sample; every mean / sd float must be identical
+            if orc is None or kind != "reference":
+                continue
+            t = time.perf_counter()
+            rm, rs = orc.column_normalizers(100000, 5)
+            ct = time.perf_counter() - t
+            a, b = orc.normalizer_pairs(100000, 5)
+            dev.normalizers_from_pairs(a[:1000], b[:1000])
+            t = time.perf_counter()
+            gm, gs = dev.normalizers_from_pairs(a, b)
+            gt = time.perf_counter() - t
+            print(json.dumps({"mode": name, "users": w.n, "pairs": int(len(a)), "fields": int(len(rm)),
+                              "reference_cpu_s": ct, "cpu_cores": 1, "gpu_e2e_s": gt, "speedup": ct / gt,
+                              "bit_identical": bool(gm.tobytes() == rm.tobytes() and gs.tobytes() == rs.tobytes())}),
+                  flush=True)
+            continue
+        cache_s = None
+        if name == "clubs_cached":
+            # the clubs call served from the per-edge FAS cache (built once per world / normalizer set)
+            t = time.perf_counter()
+            dev.edge_cache_build()
+            cache_s = time.perf_counter() - t
+            cache_pairs, cache_scan_ms = dev.stat(engine.STAT_PAIRS_SCORED), dev.stat(engine.STAT_SCAN_KERNEL_NS) / 1e6
         mode = names[name]
         dev.recommend(mode, q, args.topk, args.limit)          # warm-up (also sizes the arenas)
         dev.sync()
@@ -67,6 +93,9 @@ def main():
                "pairs_scored_per_batch": dev.stat(engine.STAT_PAIRS_SCORED),
                "scan_kernel_ms": dev.stat(engine.STAT_SCAN_KERNEL_NS) / 1e6,
                "gpu_launches_per_batch": (dev.stat(engine.STAT_KERNEL_LAUNCHES) - l0) // args.steps}
+        if cache_s is not None:
+            out["edge_cache"] = {"edges": dev.stat(engine.STAT_EDGE_CACHE), "build_s": cache_s,
+                                 "pairs_scored": cache_pairs, "scan_kernel_ms": cache_scan_ms}
         if orc is not None:
             qc = q[:args.cpu_queries]
             t = time.perf_counter()
