@@ -55,8 +55,7 @@ def main():
     names = {"graph": MODE_GRAPH, "collab": MODE_COLLAB, "clubs": MODE_CLUBS, "clubs_cached": MODE_CLUBS}
     for name in args.modes.split(","):
         if name == "normalizers":
-            # compute_column_normalizers(profiles, cols, 100000, 5) (src/utils.cpp:155-240, api_cli's
-            # start-up call): the reference on one host core (as shipped) against pk_normalizers_from_pairs on the
+            # compute_column_normalizers(profiles, cols, 100000, 5) (src/utils.cpp:155-240, src/main.cpp:124): the reference on one host core (as shipped) against pk_normalizers_from_pairs on the
             # reference's own pair sample; every mean / sd float must be identical
             if orc is None or kind != "reference":
                 continue
