@@ -201,7 +201,7 @@ struct pk_store {
     DevBuf<int32_t> d_excl, d_cand_rows, d_i32a, d_i32b, d_i32c, d_i32d, d_i32e;
     DevBuf<int64_t> d_i64a;
     DevBuf<uint64_t> d_keys_a, d_keys_b, d_keys_c;
-    DevBuf<float> d_f32a, d_fields;
+    DevBuf<float> d_f32a, d_f32b, d_fields;
     DevBuf<double> d_f64a;
     DevBuf<uint32_t> d_u32a;
     DevBuf<int> d_flag;
@@ -1660,6 +1660,17 @@ int recommend_clubs(pk_store* s, int nq, const int32_t* q_uid, int k, uint64_t* 
 // ---- pairs --------------------------------------------------------------------------------------------
 // groups of 32 distinct `a` rows x the union of their `b` rows; the wanted (a, b) entries are picked
 // from the [cand][32] block on the host.
+// The pair kernel scores a [candidate rows] x [32 lanes] block per group; a pair owns one entry of it.  Compact
+// the wanted entries on the device (one `width`-float record per pair) so that only they travel to the host.
+__global__ void gather_pairs_kernel(const float* __restrict__ src, const int64_t* __restrict__ idx, int64_t n, int width,
+                                    float* __restrict__ dst) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n * width) return;
+    const int64_t p = t / width;
+    const int j = (int)(t - p * width);
+    dst[t] = src[idx[p] * width + j];
+}
+
 template <bool FIELDS>
 int pairs_run(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid, std::vector<float>& out_f,
               std::vector<float>& out_fields, std::vector<int64_t>& where) {
@@ -1687,6 +1698,8 @@ int pairs_run(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid
         std::sort(order.begin(), order.end());
         size_t i = 0;
         const int64_t base_out = FIELDS ? (int64_t)out_fields.size() / nf : (int64_t)out_f.size();
+        std::vector<int64_t> widx;                 // per pair of this batch (in `order`): its entry of the score block
+        widx.reserve(order.size());
         while (i < order.size()) {
             GroupDesc g = empty_group();
             WorkItem it;
@@ -1701,7 +1714,8 @@ int pairs_run(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid
                     prev = order[i].first;
                 }
                 const int rb = s->row_of(b_uid[order[i].second]);
-                where[order[i].second] = base_out + ((int64_t)rows + (int64_t)(cand_rows.size() - it.cand_begin)) * 32 + (g.n_lanes - 1);
+                where[order[i].second] = base_out + (int64_t)widx.size();
+                widx.push_back(((int64_t)rows + (int64_t)(cand_rows.size() - it.cand_begin)) * 32 + (g.n_lanes - 1));
                 cand_rows.push_back(rb);
                 ++i;
             }
@@ -1723,15 +1737,18 @@ int pairs_run(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid
             P.out_fields = s->d_fields.p;
         }
         TRY((run_scan<EPI_STORE, FIELDS>(s, plan, P, items)));
-        if (FIELDS) {
-            const size_t o = out_fields.size();
-            out_fields.resize(o + (size_t)rows * 32 * nf);
-            CK(cudaMemcpyAsync(out_fields.data() + o, s->d_fields.p, (size_t)rows * 32 * nf * 4, cudaMemcpyDeviceToHost, s->stream));
-        } else {
-            const size_t o = out_f.size();
-            out_f.resize(o + (size_t)rows * 32);
-            CK(cudaMemcpyAsync(out_f.data() + o, s->d_f32a.p, (size_t)rows * 32 * 4, cudaMemcpyDeviceToHost, s->stream));
-        }
+        const int64_t np = (int64_t)widx.size();
+        const int width = FIELDS ? nf : 1;
+        TRY(upload(s, s->d_i64a, widx));
+        TRY(s->d_f32b.reserve((size_t)np * width));
+        gather_pairs_kernel<<<(unsigned)((np * width + 255) / 256), 256, 0, s->stream>>>(
+            FIELDS ? s->d_fields.p : s->d_f32a.p, s->d_i64a.p, np, width, s->d_f32b.p);
+        ++s->stat_launches;
+        CK(cudaGetLastError());
+        std::vector<float>& dst = FIELDS ? out_fields : out_f;
+        const size_t o = dst.size();
+        dst.resize(o + (size_t)np * width);
+        CK(cudaMemcpyAsync(dst.data() + o, s->d_f32b.p, (size_t)np * width * 4, cudaMemcpyDeviceToHost, s->stream));
         CK(cudaStreamSynchronize(s->stream));
     }
     return PK_OK;
