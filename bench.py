@@ -106,11 +106,38 @@ class ClockSampler:
 
 
 def build_world(n_users):
+    """the seeded synthetic world of the bench (synth.make_world + sample_normalizers).  Generating it takes ~27 s per
+    process; it is deterministic, so the first process leaves a copy under POKEC_B200_WORLD_CACHE (default
+    /tmp/pokec_b200_worlds) and later invocations / ranks load that (outside every timed region either way)."""
+    from recommendation_system_pokec_b200.synth import SEED
+    from recommendation_system_pokec_b200.world import World
     t = time.time()
+    cache_dir = os.environ.get("POKEC_B200_WORLD_CACHE", "/tmp/pokec_b200_worlds")
+    path = os.path.join(cache_dir, f"world_v1_{n_users}_{SEED:x}.npz")
+    if cache_dir != "off" and os.path.exists(path):
+        try:
+            w = World.load(path)
+            with open(path + ".meta.json") as f:
+                w.meta = json.load(f)
+            w.validate()
+            log(f"[bench] world (cached {path}): {w.meta} ({time.time() - t:.1f}s)")
+            return w
+        except Exception as e:      # a torn or stale file: fall back to the generator
+            log(f"[bench] world cache unusable ({e}); regenerating")
     w = make_world(n=n_users)
     mean, sd = sample_normalizers(w, pairs=4000)
     w.set_normalizers(mean, sd)
     log(f"[bench] world: {w.meta} ({time.time() - t:.1f}s)")
+    if cache_dir != "off" and int(os.environ.get("LOCAL_RANK", "0")) == 0:
+        try:
+            os.makedirs(cache_dir, exist_ok=True)
+            tmp = os.path.join(cache_dir, f".tmp_{os.getpid()}.npz")
+            w.save(tmp)
+            with open(path + ".meta.json", "w") as f:
+                json.dump(w.meta, f)
+            os.replace(tmp, path)
+        except Exception as e:
+            log(f"[bench] world cache not written ({e})")
     return w
 
 
