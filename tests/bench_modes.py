@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench_modes.py -- BASELINE configs[2] / configs[3] (and the list-mode configs[0] shape) on one GPU.
 
-    python tools/bench_modes.py [--users N] [--queries Q] [--steps K] [--cpu-queries C]
+    python tests/bench_modes.py [--users N] [--queries Q] [--steps K] [--cpu-queries C]
 
 For each of the reference's list modes (include/recommender.h:24-28)
     graph   recommend_graph_registration == recommend_by_interest(uid, 50, 5000)
@@ -23,7 +23,7 @@ import time
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))   # repo root (this file lives in tests/: it times the oracle)
 sys.path.insert(0, ROOT)
 
 from recommendation_system_pokec_b200.synth import make_world, sample_normalizers, sample_queries, POKEC_N  # noqa: E402
