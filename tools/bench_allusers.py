@@ -23,7 +23,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
-from recommendation_system_pokec_b200.synth import make_world, sample_normalizers, POKEC_N  # noqa: E402
+from recommendation_system_pokec_b200.synth import POKEC_N  # noqa: E402
 from recommendation_system_pokec_b200.cabi import EXCLUDE_SELF_AND_ADJ  # noqa: E402
 from recommendation_system_pokec_b200.sharding import shard_rows  # noqa: E402
 
@@ -46,9 +46,8 @@ def main():
     torch.cuda.set_device(lr)
     if ws > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
-    w = make_world(n=args.users)
-    m, s = sample_normalizers(w, pairs=4000)
-    w.set_normalizers(m, s)
+    from bench import build_world          # the bench world (cached on disk between invocations and ranks)
+    w = build_world(args.users)
     dev = DeviceRecommender(w, device=lr)
     lo, hi = shard_rows(w.n, rank, ws)
     dev.set_shard(lo, hi)

@@ -19,7 +19,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
-from recommendation_system_pokec_b200.synth import make_world, sample_normalizers, sample_queries, POKEC_N  # noqa: E402
+from recommendation_system_pokec_b200.synth import sample_queries, POKEC_N  # noqa: E402
 from recommendation_system_pokec_b200.cabi import EXCLUDE_SELF_AND_ADJ  # noqa: E402
 from recommendation_system_pokec_b200 import engine  # noqa: E402
 
@@ -32,9 +32,8 @@ def main():
     ap.add_argument("--shard", type=int, default=1, help="scan only the first 1/shard of the rows (multi-GPU shard size)")
     ap.add_argument("names", nargs="+")
     args = ap.parse_args()
-    w = make_world(n=args.users)
-    m, s = sample_normalizers(w, pairs=4000)
-    w.set_normalizers(m, s)
+    from bench import build_world          # the bench world (cached on disk between invocations)
+    w = build_world(args.users)
     q = sample_queries(w, args.queries, seed=2)
     ref_ids = None
     for spec in args.names:
