@@ -1,7 +1,9 @@
 """Multi-GPU plumbing of the full scan: one process per GPU, candidate rows partitioned by row
 (= uid) range, every rank scans its shard for the whole query batch, the per-rank top-k lists travel as packed
-64-bit sort keys through ONE all-gather, and every rank merges them with the reference comparator
-(score desc, uid asc; reference src/recommender_graph.cpp:97-100).
+64-bit sort keys through an all-gather, and every rank merges them with the reference comparator
+(score desc, uid asc; reference src/recommender_graph.cpp:97-100).  With the two-stage scan a second all-gather
+sits in the middle: the shards' approximate shortlists are gathered and merged, and every rank re-scores exactly
+only the query groups it owns (`owned_groups`, the host mirror of pk_fullscan_execute_finish's split).
 
 The key layout is csrc/pk_layout.h:make_key; the numpy forms below are the host mirror used for decoding and by
 the CPU (gloo) tests of this plumbing.
@@ -14,6 +16,12 @@ import numpy as np
 def shard_rows(n: int, rank: int, world_size: int):
     """rows [lo, hi) of rank `rank`: contiguous, balanced to within one row, covering [0, n)"""
     return n * rank // world_size, n * (rank + 1) // world_size
+
+
+def owned_groups(n_groups: int, rank: int, world_size: int):
+    """query groups [lo, hi) whose merged shortlist rank `rank` re-scores (csrc/pk_host.cu:fullscan_finish); groups
+    are consecutive blocks of 32 queries that have a profile, in caller order"""
+    return n_groups * rank // world_size, n_groups * (rank + 1) // world_size
 
 
 def pack_keys(ids, scores):

@@ -9,7 +9,7 @@ import socket
 import numpy as np
 import pytest
 
-from recommendation_system_pokec_b200.sharding import shard_rows, pack_keys, unpack_keys, merge_key_lists
+from recommendation_system_pokec_b200.sharding import shard_rows, owned_groups, pack_keys, unpack_keys, merge_key_lists
 
 
 def test_shard_rows_cover_and_balance():
@@ -80,4 +80,68 @@ def test_two_rank_sharded_fullscan_over_gloo(tmp_path, oracle_libs):
     port = s.getsockname()[1]
     s.close()
     mp.spawn(_worker, args=(2, port, 20, str(tmp_path)), nprocs=2, join=True)
+    assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
+
+
+def test_owned_groups_partition():
+    for ng in (0, 1, 5, 128):
+        for ws in (1, 2, 3, 8):
+            b = [owned_groups(ng, r, ws) for r in range(ws)]
+            assert b[0][0] == 0 and b[-1][1] == ng and all(b[i][1] == b[i + 1][0] for i in range(ws - 1))
+
+
+def _worker_shared_rescore(rank, world_size, port, k, ks, out_dir):
+    """the split pipeline of the two-stage scan (bench.py N > 1): shortlists of length ks per shard -> all-gather ->
+    merged global shortlist -> the owner rank of each query group turns it into the top-k -> all-gather -> merge.
+    The shard scan and the exact re-score are played by the CPU oracle's exact scores."""
+    import torch
+    import torch.distributed as dist
+    from oracle.oracle import CpuOracle
+    from recommendation_system_pokec_b200.sharding import all_gather_keys
+    from recommendation_system_pokec_b200.synth import sample_queries
+    from tests.conftest import make_test_world
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world_size)
+    try:
+        w = make_test_world(n=900, seed=19, pairs=300)
+        orc = CpuOracle(w, "port")
+        q = sample_queries(w, 70, seed=4)                          # 3 groups of 32 / 32 / 6 queries
+        lo, hi = shard_rows(w.n, rank, world_size)
+        short = np.zeros((len(q), ks), np.uint64)                  # stage 1: the shard's shortlist, keyed by ROW
+        scores = []
+        for qi, u in enumerate(q):
+            sc = orc.scores_of_query(int(u))
+            scores.append(sc)
+            rows = np.array([r for r in range(lo, hi) if int(w.uid[r]) != int(u)], np.int64)
+            keys = np.sort(pack_keys(rows.astype(np.int32), sc[rows]))[::-1][:ks]
+            short[qi, :len(keys)] = keys
+        g_short = all_gather_keys(torch.from_numpy(short.view(np.int64)), world_size).numpy().view(np.uint64)
+        merged_short = merge_key_lists(g_short, ks)                # identical on every rank
+        g_lo, g_hi = owned_groups((len(q) + 31) // 32, rank, world_size)
+        local = np.zeros((len(q), k), np.uint64)                   # stage 2: exact top-k of the owned groups only
+        for qi in range(len(q)):
+            if not (g_lo <= qi // 32 < g_hi):
+                continue
+            rows, _, valid = unpack_keys(merged_short[qi])
+            rows = rows[valid]
+            keys = np.sort(pack_keys(w.uid[rows], scores[qi][rows]))[::-1][:k]
+            local[qi, :len(keys)] = keys
+        gathered = all_gather_keys(torch.from_numpy(local.view(np.int64)), world_size).numpy().view(np.uint64)
+        assert ((gathered != 0).any(axis=2).sum(axis=0) == 1).all(), "every query is owned by exactly one rank"
+        ids, sc2, valid = unpack_keys(merge_key_lists(gathered, k))
+        want = orc.fullscan(q, k, 1)
+        assert np.array_equal(ids, want[0]) and np.array_equal(sc2, want[1]) and np.array_equal(valid.sum(1), want[2])
+        open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_shared_rescore_over_gloo(tmp_path, oracle_libs):
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    mp.spawn(_worker_shared_rescore, args=(2, port, 20, 64, str(tmp_path)), nprocs=2, join=True)
     assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
