@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--batch", type=int, default=4096)
     ap.add_argument("--batches", type=int, default=16)
     ap.add_argument("--topk", type=int, default=50)
+    ap.add_argument("--depth", type=int, default=2, help="batches in flight (stores on the GPU); 1 = no overlap")
     args = ap.parse_args()
     fd = os.dup(1)
     os.dup2(2, 1)                      # NCCL prints its banner on stdout
@@ -48,41 +49,70 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
     from bench import build_world          # the bench world (cached on disk between invocations and ranks)
     w = build_world(args.users)
-    dev = DeviceRecommender(w, device=lr)
+    # `depth` stores on the same GPU take the batches in turn, each on its own stream: the host planning and H2D of
+    # batch i + 1 overlap the kernels of batch i, and its all-gather overlaps the next scan
     lo, hi = shard_rows(w.n, rank, ws)
-    dev.set_shard(lo, hi)
     k, B = args.topk, args.batch
-    stream = torch.cuda.ExternalStream(dev.stream(), device=lr)
-    local = torch.zeros((B, k), dtype=torch.int64, device=f"cuda:{lr}")
-    gathered = torch.zeros((ws, B, k), dtype=torch.int64, device=f"cuda:{lr}")
+    from recommendation_system_pokec_b200 import engine
 
-    bufs = {}
+    class Slot:
+        def __init__(self):
+            self.dev = DeviceRecommender(w, device=lr)
+            self.dev.set_shard(lo, hi)
+            self.stream = torch.cuda.ExternalStream(self.dev.stream(), device=lr)
+            self.local = torch.zeros((B, k), dtype=torch.int64, device=f"cuda:{lr}")
+            self.gathered = torch.zeros((ws, B, k), dtype=torch.int64, device=f"cuda:{lr}")
+            self.short = None
+            self.pending = False
 
-    def run_batch(b):
-        q = w.uid[(b * B) % w.n:(b * B) % w.n + B].astype(np.int32)
-        if len(q) < B:
-            q = np.concatenate([q, w.uid[:B - len(q)].astype(np.int32)])
-        if ws == 1:
-            return dev.fullscan(q, k, EXCLUDE_SELF_AND_ADJ)
-        from recommendation_system_pokec_b200 import engine
-        dev.fullscan_prepare(q, k, EXCLUDE_SELF_AND_ADJ)
-        ks = dev.stat(engine.STAT_SHORTLIST)
-        if ks > 0:      # shared exact re-score
-            if "s" not in bufs:
-                bufs["s"] = (torch.zeros((B, ks), dtype=torch.int64, device=f"cuda:{lr}"),
-                             torch.zeros((ws, B, ks), dtype=torch.int64, device=f"cuda:{lr}"))
-            ls, gs = bufs["s"]
-            dev.fullscan_execute_shortlists()
-            dev.fullscan_shortlist_keys(ls.data_ptr())
-            with torch.cuda.stream(stream):
-                dist.all_gather_into_tensor(gs.view(-1), ls.view(-1))
-            dev.fullscan_execute_finish(gs.data_ptr(), ws, rank, ws)
-        else:
-            dev.fullscan_execute()
-        dev.fullscan_keys(local.data_ptr())
-        with torch.cuda.stream(stream):
-            dist.all_gather_into_tensor(gathered.view(-1), local.view(-1))
-        return dev.merge_keys(gathered.data_ptr(), ws, B, k)
+        def launch(self, b):
+            """everything of batch b up to (not including) the fetch: asynchronous on this slot's stream"""
+            dev = self.dev
+            q = w.uid[(b * B) % w.n:(b * B) % w.n + B].astype(np.int32)
+            if len(q) < B:
+                q = np.concatenate([q, w.uid[:B - len(q)].astype(np.int32)])
+            dev.fullscan_prepare(q, k, EXCLUDE_SELF_AND_ADJ)
+            ks = dev.stat(engine.STAT_SHORTLIST)
+            if ws > 1 and ks > 0:      # shared exact re-score (DESIGN.md section 7)
+                if self.short is None:
+                    self.short = (torch.zeros((B, ks), dtype=torch.int64, device=f"cuda:{lr}"),
+                                  torch.zeros((ws, B, ks), dtype=torch.int64, device=f"cuda:{lr}"))
+                ls, gs = self.short
+                dev.fullscan_execute_shortlists()
+                dev.fullscan_shortlist_keys(ls.data_ptr())
+                with torch.cuda.stream(self.stream):
+                    dist.all_gather_into_tensor(gs.view(-1), ls.view(-1))
+                dev.fullscan_execute_finish(gs.data_ptr(), ws, rank, ws)
+            else:
+                dev.fullscan_execute()
+            if ws > 1:
+                dev.fullscan_keys(self.local.data_ptr())
+                with torch.cuda.stream(self.stream):
+                    dist.all_gather_into_tensor(self.gathered.view(-1), self.local.view(-1))
+            self.pending = True
+
+        def fetch(self):
+            """host top-k of the batch launched last on this slot (synchronises this slot's stream only)"""
+            self.pending = False
+            if ws == 1:
+                return self.dev.fullscan_fetch()
+            return self.dev.merge_keys(self.gathered.data_ptr(), ws, B, k)
+
+    slots = [Slot() for _ in range(max(1, args.depth))]
+    dev = slots[0].dev
+
+    def run_window(b0, nb):
+        res = None
+        for b in range(b0, b0 + nb):
+            sl = slots[b % len(slots)]
+            if sl.pending:
+                res = sl.fetch()
+            sl.launch(b)
+        for i in range(len(slots)):                # drain in launch order
+            sl = slots[(b0 + nb + i) % len(slots)]
+            if sl.pending:
+                res = sl.fetch()
+        return res
 
     def barrier():
         dev.sync()
@@ -91,12 +121,10 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    run_batch(0)
+    run_window(0, len(slots))
     barrier()
     t = time.perf_counter()
-    res = None
-    for b in range(1, args.batches + 1):
-        res = run_batch(b)
+    res = run_window(len(slots), args.batches)
     barrier()
     dt = time.perf_counter() - t
     if ws > 1:
@@ -106,14 +134,15 @@ def main():
     rate = args.batches * B / dt
     if rank == 0:
         out = {"workload": "all-users FAS top-50 (BASELINE configs[4])", "n_gpus": ws, "users": w.n, "batch": B,
-               "window_batches": args.batches, "query_users_per_s": rate, "ms_per_batch": dt / args.batches * 1e3,
+               "window_batches": args.batches, "batches_in_flight": len(slots), "query_users_per_s": rate, "ms_per_batch": dt / args.batches * 1e3,
                "full_sweep_batches": -(-w.n // B), "full_sweep_seconds_extrapolated": w.n / rate,
                "pairs_per_s": rate * w.n, "complete_lists": bool(int(res[2].min()) == k)}
         os.write(fd, (json.dumps(out) + "\n").encode())
     if ws > 1:
         dist.barrier()
         dist.destroy_process_group()
-    dev.close()
+    for sl in slots:
+        sl.dev.close()
     return 0
 
 
