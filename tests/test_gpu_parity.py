@@ -477,6 +477,36 @@ def test_fullscan_more_groups_than_sms(monkeypatch):
     dev.close()
 
 
+@pytest.mark.parametrize("case", range(10))
+def test_fullscan_fuzz_two_stage_equals_exact(case, monkeypatch):
+    """random small worlds / batch shapes / k / exclusion modes / shards: the two-stage scan (cuckoo tables, dynamic
+    schedule, shortlist proof, partial re-score) must return exactly what the exact kernel returns on every pair"""
+    from recommendation_system_pokec_b200.engine import DeviceRecommender
+    rng = np.random.default_rng(1000 + case)
+    n = int(rng.choice([40, 150, 700, 2500]))
+    T = int(rng.choice([1, 3, 10, 49]))
+    w = make_test_world(n=n, seed=200 + case, T=T, pairs=300, uid_gap=bool(rng.integers(0, 2)),
+                        mean_deg=float(rng.choice([2.0, 12.0])))
+    dev = DeviceRecommender(w)
+    nq = int(rng.choice([1, 31, 33, 200]))
+    q = w.uid[rng.integers(0, w.n, nq)].astype(np.int32)         # repeated users allowed
+    q[rng.integers(0, nq)] = -7 if case % 3 == 0 else q[0]        # sometimes an unknown user
+    k = int(rng.choice([1, 7, 50, 100]))
+    mode = int(rng.choice([EXCLUDE_NONE, EXCLUDE_SELF, EXCLUDE_SELF_AND_ADJ]))
+    lo = int(rng.integers(0, w.n // 2))
+    hi = int(rng.integers(lo + 1, w.n + 1))
+    for shard in ((0, w.n), (lo, hi)):
+        dev.set_shard(*shard)
+        monkeypatch.delenv("POKEC_B200_NO_PREFILTER", raising=False)
+        two_stage = dev.fullscan(q, k, mode)
+        monkeypatch.setenv("POKEC_B200_NO_PREFILTER", "1")
+        exact = dev.fullscan(q, k, mode)
+        for x, y in zip(two_stage, exact):
+            assert np.array_equal(x, y), f"case {case}: n={n} T={T} nq={nq} k={k} mode={mode} shard={shard}"
+    monkeypatch.delenv("POKEC_B200_NO_PREFILTER", raising=False)
+    dev.close()
+
+
 def test_fullscan_tie_heavy_world_falls_back_to_exact(oracle_libs):
     """few fields and tiny vocabularies: thousands of candidates tie at the k-th score, the shortlist cannot be
     proven complete, and the flagged queries must come out of the exact full scan -- identical to the oracle"""
