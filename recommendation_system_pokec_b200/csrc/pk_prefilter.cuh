@@ -123,20 +123,22 @@ __device__ __forceinline__ void shortlist_insert(uint64_t* list, int K, uint64_t
     if (lane == 0) atomicExch(lock, 0);
 }
 
-// 32 x 32 bit transpose across the warp: bit j of the result in lane l = bit l of x in lane j
+// 32 x 32 bit transpose across the warp: bit j of the result in lane l = bit l of x in lane j.
+// Butterfly over s = 16 .. 1 (swap the off-diagonal s x s sub-blocks of every 2s x 2s block) carried out in a
+// rotated frame: lane l holds its row rotated left by l.  In that frame the partner's row needs no shift at all
+// (upper rows would shift up by s, lower rows down by s; the relative rotation l - (l ^ s) cancels both), and the
+// columns a lane keeps are rotl(lo_s, l mod s) for upper and lower rows alike -- so a step is one SHFL and one LOP3.
 __device__ __forceinline__ uint32_t transpose32(uint32_t x, int lane) {
+    x = __funnelshift_l(x, x, lane);
     #pragma unroll
     for (int s = 16; s >= 1; s >>= 1) {
         const uint32_t lo = (s == 16) ? 0x0000ffffu : (s == 8) ? 0x00ff00ffu : (s == 4) ? 0x0f0f0f0fu : (s == 2) ? 0x33333333u : 0x55555555u;
+        // (the four lane-dependent masks are rebuilt per call: fetching them from shared memory measured slower)
+        const uint32_t keep = __funnelshift_l(lo, lo, lane & (s - 1));
         const uint32_t y = __shfl_xor_sync(kFull, x, s);
-        // upper half of a 2s x 2s block keeps its low columns and takes the partner's shifted up by s (lower half:
-        // the mirror image).  A rotate serves both shifts: the wrapped bits fall into the kept columns and are masked.
-        const bool up = (lane & s) != 0;
-        const uint32_t keep = up ? ~lo : lo;
-        const uint32_t rot = __funnelshift_l(y, y, up ? 32 - s : s);
-        x = (x & keep) | (rot & ~keep);
+        x = (x & keep) | (y & ~keep);
     }
-    return x;
+    return __funnelshift_r(x, x, lane);
 }
 
 template <bool STORE>
