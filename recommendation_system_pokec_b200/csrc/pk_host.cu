@@ -481,7 +481,7 @@ int rebuild_lean(pk_store* s) {
     std::vector<uint64_t> off((size_t)n + 1, 0);
     for (int r = 0; r < n; ++r) off[r + 1] = off[r] + lean_record_u4(s->h_ncl[r], s->h_nfr[r], s->h_ntok[r]);
     s->lean_u4 = off[n];
-    TRY(s->d_lrec.reserve(std::max<uint64_t>(s->lean_u4, 1)));
+    TRY(s->d_lrec.reserve(s->lean_u4 + 16));      // + 256 B: the pre-filter reads the first 32 set words of a record speculatively
     TRY(upload(s, s->d_lrec_off, off));
     if (n > 0) {
         const unsigned blocks = (unsigned)(((int64_t)n * 32 + 255) / 256);

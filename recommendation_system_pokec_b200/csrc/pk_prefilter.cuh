@@ -272,12 +272,23 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
 #endif
             const uint32_t* cw = reinterpret_cast<const uint32_t*>(cr);
             const uint4 h0 = __ldg(cr), h1 = __ldg(cr + 1), h2 = __ldg(cr + 2), h3 = __ldg(cr + 3);
+            // the first 32 club / friend ids sit at a fixed offset: their load does not wait for the header (words past
+            // the sets, or past the record -- the buffer is padded -- are read and ignored)
+            const uint32_t el0 = __ldg(cw + kLeanHdrWords + lane);
             const int c_uid = (int)h0.x, c_pub = (int)h0.y, c_gender = (int)h0.z, c_comp = (int)h0.w;
             const int c_age = (int)h1.x, c_r0 = (int)h1.y, c_r1 = (int)h1.z, c_r2 = (int)h1.w;
             const uint32_t c_ncl = h2.x, c_nfr = h2.y, c_ntok = h2.z;
             const int c_bcnt = (int)h2.w;
             const uint32_t o_clubs = kLeanHdrWords, o_friends = o_clubs + pad4(c_ncl), o_keys = o_friends + pad4(c_nfr),
                            o_w = o_keys + pad4(c_ntok);
+
+            // the token keys / weights of a round are requested one round ahead (the first round here, before the
+            // scalar fields and the sets), so that their latency is covered by other work
+            const uint32_t* keys = cw + o_keys;
+            const float* tokw = reinterpret_cast<const float*>(cw + o_w);
+            uint32_t key_n = 0;
+            float w_n = 0.f;
+            if ((uint32_t)lane < c_ntok) { key_n = __ldg(keys + lane); w_n = __ldg(tokw + lane); }
 
             // text columns present on both sides: every one contributes sigma(z(0)) unless a token matches
             const uint32_t b0 = q_m0 & h3.x, b1 = q_m1 & h3.y;
@@ -318,7 +329,7 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                     const bool is_fr = i >= pcl;
                     uint32_t m = 0;
                     if (is_fr ? (i < n_el) : (i < c_ncl)) {
-                        const uint32_t key = __ldg(cw + o_clubs + i) | (is_fr ? 0x80000000u : 0u);
+                        const uint32_t key = ((e0 == 0u) ? el0 : __ldg(cw + o_clubs + i)) | (is_fr ? 0x80000000u : 0u);
                         const uint4 e1 = t_sets[hash_u32(key, log_cs)], e2 = t_sets[hash2_u32(key, log_cs)];
                         m = ((e1.x == key) ? e1.y : 0u) | ((e1.z == key) ? e1.w : 0u) | ((e2.x == key) ? e2.y : 0u) |
                             ((e2.z == key) ? e2.w : 0u);
@@ -345,17 +356,17 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
 
             // text columns (:93-114): the lean weights are already divided by the cell norms
             if (c_ntok > 0) {
-                const uint32_t* keys = cw + o_keys;
-                const float* tokw = reinterpret_cast<const float*>(cw + o_w);
                 float acc = 0.f;
                 int cur = -1;                                         // per lane: column of the open cell of MY query
                 for (uint32_t cb = 0; cb < c_ntok; cb += 32) {
                     const uint32_t i = cb + lane;
-                    uint32_t m = 0, id = 0, key = 0;
+                    uint32_t m = 0, id = 0;
+                    const uint32_t key = key_n;
+                    const float w = w_n;
+                    if (i + 32u < c_ntok) { key_n = __ldg(keys + i + 32u); w_n = __ldg(tokw + i + 32u); }
                     if (i < c_ntok) {
                         // 2-choice cuckoo probe: both buckets are read unconditionally (two independent LDS.128), a key
                         // lives in at most one slot and empty slots carry entry 0, so the matches can simply be OR-ed
-                        key = __ldg(keys + i);
                         const uint4 e1 = t_ck[hash_u32(key, log_cb)], e2 = t_ck[hash2_u32(key, log_cb)];
                         id = ((e1.x == key) ? e1.y : 0u) | ((e1.z == key) ? e1.w : 0u) | ((e2.x == key) ? e2.y : 0u) |
                              ((e2.z == key) ? e2.w : 0u);
@@ -365,7 +376,7 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                     if (id) {
                         const uint2 en = t_ent[id - 1u];
                         m = en.x;
-                        stage[lane] = make_uint4(m, en.y, __float_as_uint(__ldg(tokw + i)), key >> kTokBits);
+                        stage[lane] = make_uint4(m, en.y, __float_as_uint(w), key >> kTokBits);
                     }
                     // bit j of `mine` = "token j of this chunk belongs to MY query": each lane walks only its own hits
                     uint32_t mine = transpose32(m, lane);
