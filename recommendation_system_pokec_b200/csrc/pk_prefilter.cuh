@@ -263,13 +263,6 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
         for (int ci = c0; ci < c1; ++ci) {
             const uint64_t off = __shfl_sync(kFull, offv, ci - c0);
             const uint4* cr = P.lrec + off;
-#ifdef PK_PREFETCH_L1
-            {   // pull the next record of the chunk (<= PK_PREFETCH_L1 lines of 128 B) into L1 while this one is scored
-                const uint64_t offn = __shfl_sync(kFull, offv, (ci + 1 - c0) & 31);
-                if (ci + 1 < c1 && lane < PK_PREFETCH_L1)
-                    asm volatile("prefetch.global.L1 [%0];" ::"l"(P.lrec + offn + lane * 8));
-            }
-#endif
             const uint32_t* cw = reinterpret_cast<const uint32_t*>(cr);
             const uint4 h0 = __ldg(cr), h1 = __ldg(cr + 1), h2 = __ldg(cr + 2), h3 = __ldg(cr + 3);
             // the first 32 club / friend ids sit at a fixed offset: their load does not wait for the header (words past
