@@ -27,12 +27,13 @@ def build(force=False):
     build_cuda()
     srcs = [os.path.join(HERE, "recommender_b200.cpp"), os.path.join(HERE, "tfidf_index_b200.cpp"),
             os.path.join(ROOT, "oracle", "ref_driver.cpp")]
-    deps = srcs + [os.path.join(ROOT, "include", "pokec_b200.h"), os.path.join(ROOT, "include", "pokec_world.h")]
+    deps = srcs + [os.path.join(ROOT, "include", "pokec_b200.h"), os.path.join(ROOT, "include", "pokec_world.h"),
+                   os.path.join(HERE, "recommender_b200_batch.h")]
     if not force and os.path.exists(OUT) and all(os.path.getmtime(d) <= os.path.getmtime(OUT) for d in deps):
         return OUT
     os.makedirs(OUT_DIR, exist_ok=True)
     cmd = ["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-pthread", "-DPK_DROPIN_BUILD",
-           "-I", os.path.join(REF, "include"), "-I", os.path.join(ROOT, "include")] + srcs + \
+           "-I", os.path.join(REF, "include"), "-I", os.path.join(ROOT, "include"), "-I", HERE] + srcs + \
           ["-L", PKG, "-lpokec_b200", "-Wl,-rpath,$ORIGIN/../../recommendation_system_pokec_b200", "-o", OUT]
     subprocess.check_call(cmd)
     return OUT

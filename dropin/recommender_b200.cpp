@@ -15,6 +15,7 @@
 #include "user_profile.h"
 
 #include "pokec_b200.h"
+#include "recommender_b200_batch.h"
 
 #include <algorithm>
 #include <cstdio>
@@ -391,6 +392,41 @@ vector<pair<int, float>> Recommender::recommend_friends_collab(int user, int top
 vector<pair<int, float>> Recommender::recommend_friends_by_interest(int user, int topk, int candidate_limit) const {
     return recommend_by_interest(user, topk, candidate_limit);
 }
+
+// ---- batched calls (recommender_b200_batch.h) -------------------------------------------------------
+// include/recommender.h:70 befriends this struct and no reference translation unit defines it: the drop-in uses it
+// to read the private column list from a free function.
+struct RecommenderInternalSim {
+    static const vector<string>& columns(const Recommender& r) { return r.text_columns_internal; }
+};
+
+namespace pokec_b200 {
+
+int batch_mode_from_name(const string& name) {
+    if (name == "graph" || name == "interest") return PK_MODE_GRAPH;      // recommender_graph.cpp:224-227: interest is an alias
+    if (name == "collaborative") return PK_MODE_COLLAB;
+    if (name == "clubs") return PK_MODE_CLUBS;
+    return -1;
+}
+
+vector<vector<pair<int, float>>> recommend_batch(const Recommender& r, int pk_mode, const vector<int>& users, int topk, int candidate_limit) {
+    vector<vector<pair<int, float>>> out(users.size());
+    if (!r.adj_list || !r.profiles || topk <= 0 || users.empty()) return out;
+    lock_guard<mutex> lk(g_mu);
+    Shim& s = sync_state(r, RecommenderInternalSim::columns(r));
+    for (int u : users) refresh_adjacency(s, r, u);
+    const size_t nq = users.size();
+    vector<int32_t> q(users.begin(), users.end()), id(nq * (size_t)topk), cnt(nq, 0);
+    vector<float> sc(nq * (size_t)topk);
+    PKCHECK(pk_recommend(s.store, pk_mode, (int)nq, q.data(), topk, candidate_limit, id.data(), sc.data(), cnt.data()));
+    for (size_t i = 0; i < nq; ++i) {
+        out[i].reserve((size_t)cnt[i]);
+        for (int j = 0; j < cnt[i]; ++j) out[i].emplace_back(id[i * topk + j], sc[i * topk + j]);
+    }
+    return out;
+}
+
+}  // namespace pokec_b200
 
 // src/recommender_clubs.cpp:75-149.  Only caller is the dead evaluator.cpp:86:
 // out of scope, no device path, returns no recommendations.

@@ -44,3 +44,44 @@ def test_api_cli_json_identical(tmp_path):
     assert not bad, f"{len(bad)} of {len(ref_lines)} lines differ; first: line {bad[0]}\nref: {ref_lines[bad[0]][:600]}\nour: {our_lines[bad[0]][:600]}"
     assert sum('"recommendations"' in ln for ln in our_lines) == len(users)
     assert "[pokec_b200] fatal" not in our_err
+
+
+BATCH_BIN = os.path.join(ROOT, "dropin", "_build", "api_cli_b200_batch")
+
+
+def test_api_cli_batch_lines_equal_user_lines(tmp_path):
+    """the BATCH line (dropin/api_cli_batch.inc, one device call for many users) returns, for every
+    user and each of the four modes, exactly the list the REFERENCE binary prints in its USER reply; the USER /
+    PING / error lines of the patched server stay byte-identical to the reference's."""
+    import json
+    if not (os.path.exists(REF_BIN) and os.path.exists(BATCH_BIN)):
+        pytest.skip("api_cli binaries not built (dropin/build_api_cli.py needs the reference sources)")
+    w = make_test_world(n=1500, seed=29, pairs=800)
+    d = str(tmp_path)
+    write_reference_data_dir(w, d)
+    users = [int(u) for u in sample_queries(w, 70, seed=9)]          # 70 users: three query groups in one call
+    user_lines = "".join(f"USER {u}\n" for u in users)
+    ref_lines, _ = run(REF_BIN, d, "PING\n" + user_lines + "BOGUS\nEXIT\n")
+    ulist = " ".join(str(u) for u in users)
+    modes = ["graph", "collaborative", "interest", "clubs"]
+    text = "PING\n" + user_lines + "BOGUS\n" + "".join(f"BATCH {m} 20 {ulist}\n" for m in modes) + \
+           f"BATCH graph 20 {users[0]} 987654321 {users[1]}\nBATCH graph 7 {users[2]}\n" \
+           "BATCH nosuchmode 20 1\nBATCH graph 0 1\nBATCH graph 20\nBATCH graph 20 12 x\nEXIT\n"
+    our_lines, our_err = run(BATCH_BIN, d, text)
+    assert "[pokec_b200] fatal" not in our_err
+    n0 = len(users) + 2
+    assert our_lines[:n0] == ref_lines[:n0], "USER / PING / unknown-command lines changed under the BATCH patch"
+    ref_recs = [json.loads(ln)["recommendations"] for ln in ref_lines[1:1 + len(users)]]
+    for mi, m in enumerate(modes):
+        rep = json.loads(our_lines[n0 + mi])
+        assert rep["mode"] == m and rep["k"] == 20 and len(rep["results"]) == len(users)
+        for u, res, rr in zip(users, rep["results"], ref_recs):
+            assert res["user_id"] == u
+            assert res["items"] == rr[m], f"BATCH {m} differs from the reference's USER reply for user {u}"
+    mixed = json.loads(our_lines[n0 + 4])["results"]
+    assert mixed[0]["items"] == ref_recs[0]["graph"] and mixed[2]["items"] == ref_recs[1]["graph"]
+    assert mixed[1] == {"user_id": 987654321, "error": "not found"}
+    k7 = json.loads(our_lines[n0 + 5])
+    assert k7["k"] == 7 and k7["results"][0]["items"] == ref_recs[2]["graph"][:7]
+    assert our_lines[n0 + 6:n0 + 10] == ['{"error":"bad batch"}'] * 4
+    assert json.loads(our_lines[n0 + 10]) == {"ok": True, "exiting": True}
