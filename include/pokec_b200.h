@@ -221,6 +221,22 @@ int64_t pk_stat(pk_store* s, int which);
 int pk_debug_prefilter(pk_store* s, int nq, const int32_t* q_uid, int64_t row_begin, int64_t row_end, float* out_approx,
                        float* out_exact);
 
+/* ---- binary profile store on disk ------------------------------------------------------
+ * Replaces, for callers of this ABI, the CSV parse of the reference's load_users_encoded
+ * (src/user_loader.cpp:10-96: single-threaded getline / stoi per cell, capped at 100 000 users, :34) and the
+ * adjacency.csv reload (src/graph_builder.cpp:39-75) with one mmap: the file holds the arrays of a pk_world
+ * (header + section table + 19 sections, 64-byte aligned, little-endian, checksummed header).
+ *   pk_world_save   writes w to path (through path.tmp + rename)
+ *   pk_world_open   maps path read-only; *view's pointers point into the mapping and stay valid until pk_world_close
+ *                   (pass view to pk_store_load_world, which copies what it keeps).  A file that is not a world
+ *                   file, is truncated, or whose section sizes contradict its counts fails with PK_ERR_ARG.
+ *   pk_world_close  unmaps; NULL is a no-op
+ * No CUDA device is needed for these three calls. */
+typedef struct pk_world_file pk_world_file;
+int pk_world_save(const pk_world* w, const char* path);
+int pk_world_open(const char* path, pk_world_file** out, pk_world* view);
+void pk_world_close(pk_world_file* f);
+
 #ifdef __cplusplus
 }
 #endif

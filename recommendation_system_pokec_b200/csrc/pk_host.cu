@@ -10,6 +10,11 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cstddef>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
 #include <atomic>
 #include <thread>
 #include <cmath>
@@ -2368,5 +2373,147 @@ int64_t pk_stat(pk_store* s, int which) {
         default: return -1;
     }
 }
+
+// ---- binary profile store on disk (include/pokec_b200.h) ------------------------------------------------
+// One file = header + section table + the 19 arrays of a pk_world, each 64-byte aligned, native little-endian.  The
+// reader maps the file read-only and hands out a pk_world whose pointers point into the mapping: no parse, no copy
+// before pk_store_load_world streams the arrays to the device.
+namespace {
+constexpr uint64_t kWorldMagic = 0x31444c52574b5000ull;   // "\0PKWRLD1"
+constexpr int kWorldSections = 19;
+struct WorldFileHeader {
+    uint64_t magic;
+    uint32_t version, endian_tag;          // 1, 0x01020304
+    int32_t n_users, n_text_cols, n_adj_rows, n_sections;
+    uint64_t file_bytes;
+    uint64_t off[kWorldSections], bytes[kWorldSections];
+    uint64_t header_sum;                   // FNV-1a of everything above
+};
+uint64_t fnv1a(const void* p, size_t n) {
+    const unsigned char* b = (const unsigned char*)p;
+    uint64_t h = 1469598103934665603ull;
+    for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 1099511628211ull; }
+    return h;
+}
+struct Section { const void* p; uint64_t bytes; };
+// element counts follow from the header ints and the last entries of the three offset arrays
+bool world_sections(const pk_world* w, Section* sec) {
+    const int64_t n = w->n_users, T = w->n_text_cols, m = w->n_adj_rows, nf = PK_NUM_FIXED + T;
+    if (n < 0 || T < 0 || m < 0) return false;
+    if (n > 0 && (!w->clubs_ptr || !w->friends_ptr || !w->tok_ptr)) return false;
+    if (m > 0 && !w->adj_ptr) return false;
+    const int64_t ncl = n ? w->clubs_ptr[n] : 0, nfr = n ? w->friends_ptr[n] : 0, ntk = n ? w->tok_ptr[n * T] : 0,
+                  nadj = m ? w->adj_ptr[m] : 0;
+    if (ncl < 0 || nfr < 0 || ntk < 0 || nadj < 0) return false;
+    const Section v[kWorldSections] = {
+        {w->uid, (uint64_t)n * 4}, {w->pub, (uint64_t)n * 4}, {w->comp, (uint64_t)n * 4}, {w->gender, (uint64_t)n * 4},
+        {w->age, (uint64_t)n * 4}, {w->region, (uint64_t)n * 12},
+        {w->clubs_ptr, n ? (uint64_t)(n + 1) * 8 : 0}, {w->clubs, (uint64_t)ncl * 4},
+        {w->friends_ptr, n ? (uint64_t)(n + 1) * 8 : 0}, {w->friends, (uint64_t)nfr * 4},
+        {w->tok_ptr, n ? (uint64_t)(n * T + 1) * 8 : 0}, {w->tok_id, (uint64_t)ntk * 4}, {w->tok_tf, (uint64_t)ntk * 4},
+        {w->adj_uid, (uint64_t)m * 4}, {w->adj_ptr, m ? (uint64_t)(m + 1) * 8 : 0}, {w->adj, (uint64_t)nadj * 4},
+        {w->norm_mean, (uint64_t)nf * 4}, {w->norm_sd, (uint64_t)nf * 4}, {w->norm_has, (uint64_t)nf}};
+    for (int i = 0; i < kWorldSections; ++i) {
+        if (v[i].bytes && !v[i].p) return false;
+        sec[i] = v[i];
+    }
+    return true;
+}
+}  // namespace
+
+struct pk_world_file {
+    void* map = nullptr;
+    size_t bytes = 0;
+};
+
+int pk_world_save(const pk_world* w, const char* path) {
+    if (!w || !path) return fail(PK_ERR_ARG, "pk_world_save: null argument");
+    Section sec[kWorldSections];
+    if (!world_sections(w, sec)) return fail(PK_ERR_ARG, "pk_world_save: inconsistent world (null array or negative size)");
+    WorldFileHeader H;
+    memset(&H, 0, sizeof(H));
+    H.magic = kWorldMagic; H.version = 1; H.endian_tag = 0x01020304u;
+    H.n_users = w->n_users; H.n_text_cols = w->n_text_cols; H.n_adj_rows = w->n_adj_rows; H.n_sections = kWorldSections;
+    uint64_t off = (sizeof(H) + 63) & ~63ull;
+    for (int i = 0; i < kWorldSections; ++i) { H.off[i] = off; H.bytes[i] = sec[i].bytes; off = (off + sec[i].bytes + 63) & ~63ull; }
+    H.file_bytes = off;
+    H.header_sum = fnv1a(&H, offsetof(WorldFileHeader, header_sum));
+    const std::string tmp = std::string(path) + ".tmp";
+    FILE* f = fopen(tmp.c_str(), "wb");
+    if (!f) return fail(PK_ERR_ARG, "pk_world_save: cannot create %s", tmp.c_str());
+    bool ok = fwrite(&H, sizeof(H), 1, f) == 1;
+    uint64_t pos = sizeof(H);
+    static const char zeros[64] = {0};
+    for (int i = 0; ok && i < kWorldSections; ++i) {
+        if (pos < H.off[i]) { ok = fwrite(zeros, 1, H.off[i] - pos, f) == H.off[i] - pos; pos = H.off[i]; }
+        if (ok && sec[i].bytes) { ok = fwrite(sec[i].p, 1, sec[i].bytes, f) == sec[i].bytes; pos += sec[i].bytes; }
+    }
+    if (ok && pos < H.file_bytes) ok = fwrite(zeros, 1, H.file_bytes - pos, f) == H.file_bytes - pos;
+    ok = (fclose(f) == 0) && ok;
+    if (!ok || rename(tmp.c_str(), path) != 0) { remove(tmp.c_str()); return fail(PK_ERR_ARG, "pk_world_save: write to %s failed", path); }
+    return PK_OK;
+}
+
+int pk_world_open(const char* path, pk_world_file** out, pk_world* view) {
+    if (!path || !out || !view) return fail(PK_ERR_ARG, "pk_world_open: null argument");
+    *out = nullptr;
+    const int fd = open(path, O_RDONLY);
+    if (fd < 0) return fail(PK_ERR_ARG, "pk_world_open: cannot open %s", path);
+    struct stat st;
+    if (fstat(fd, &st) != 0 || (size_t)st.st_size < sizeof(WorldFileHeader)) { close(fd); return fail(PK_ERR_ARG, "pk_world_open: %s is not a world file (too short)", path); }
+    void* map = mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+    close(fd);
+    if (map == MAP_FAILED) return fail(PK_ERR_ARG, "pk_world_open: mmap of %s failed", path);
+    const WorldFileHeader& H = *reinterpret_cast<const WorldFileHeader*>(map);
+    const char* why = nullptr;
+    if (H.magic != kWorldMagic) why = "bad magic";
+    else if (H.version != 1 || H.n_sections != kWorldSections) why = "unsupported version";
+    else if (H.endian_tag != 0x01020304u) why = "written on a machine of the other byte order";
+    else if (H.header_sum != fnv1a(&H, offsetof(WorldFileHeader, header_sum))) why = "header checksum mismatch";
+    else if (H.file_bytes != (uint64_t)st.st_size) why = "truncated (size differs from the header)";
+    else if (H.n_users < 0 || H.n_text_cols < 0 || H.n_adj_rows < 0) why = "negative count";
+    if (!why)
+        for (int i = 0; i < kWorldSections; ++i)
+            if ((H.off[i] & 63) || H.off[i] > H.file_bytes || H.bytes[i] > H.file_bytes - H.off[i]) { why = "section outside the file"; break; }
+    pk_world w;
+    memset(&w, 0, sizeof(w));
+    if (!why) {
+        const char* base = reinterpret_cast<const char*>(map);
+        auto at = [&](int i) -> const void* { return H.bytes[i] ? base + H.off[i] : nullptr; };
+        w.n_users = H.n_users; w.n_text_cols = H.n_text_cols; w.n_adj_rows = H.n_adj_rows;
+        w.uid = (const int32_t*)at(0); w.pub = (const int32_t*)at(1); w.comp = (const int32_t*)at(2);
+        w.gender = (const int32_t*)at(3); w.age = (const int32_t*)at(4); w.region = (const int32_t*)at(5);
+        w.clubs_ptr = (const int64_t*)at(6); w.clubs = (const uint32_t*)at(7);
+        w.friends_ptr = (const int64_t*)at(8); w.friends = (const uint32_t*)at(9);
+        w.tok_ptr = (const int64_t*)at(10); w.tok_id = (const int32_t*)at(11); w.tok_tf = (const int32_t*)at(12);
+        w.adj_uid = (const int32_t*)at(13); w.adj_ptr = (const int64_t*)at(14); w.adj = (const int32_t*)at(15);
+        w.norm_mean = (const float*)at(16); w.norm_sd = (const float*)at(17); w.norm_has = (const uint8_t*)at(18);
+        // the section sizes must be the ones the counts and offset arrays imply
+        const int64_t n = H.n_users, T = H.n_text_cols, m = H.n_adj_rows;
+        const uint64_t fixed[6] = {(uint64_t)n * 4, (uint64_t)n * 4, (uint64_t)n * 4, (uint64_t)n * 4, (uint64_t)n * 4, (uint64_t)n * 12};
+        for (int i = 0; i < 6 && !why; ++i) if (H.bytes[i] != fixed[i]) why = "scalar section size";
+        if (!why && (H.bytes[6] != (n ? (uint64_t)(n + 1) * 8 : 0) || H.bytes[8] != H.bytes[6] ||
+                     H.bytes[10] != (n ? (uint64_t)(n * T + 1) * 8 : 0) || H.bytes[14] != (m ? (uint64_t)(m + 1) * 8 : 0) ||
+                     H.bytes[13] != (uint64_t)m * 4)) why = "offset section size";
+        if (!why) {
+            Section sec[kWorldSections];
+            if (!world_sections(&w, sec)) why = "inconsistent arrays";
+            else for (int i = 0; i < kWorldSections; ++i) if (sec[i].bytes != H.bytes[i]) { why = "array size differs from its offsets"; break; }
+        }
+    }
+    if (why) { munmap(map, (size_t)st.st_size); return fail(PK_ERR_ARG, "pk_world_open: %s: %s", path, why); }
+    pk_world_file* f = new pk_world_file;
+    f->map = map; f->bytes = (size_t)st.st_size;
+    *out = f;
+    *view = w;
+    return PK_OK;
+}
+
+void pk_world_close(pk_world_file* f) {
+    if (!f) return;
+    if (f->map) munmap(f->map, f->bytes);
+    delete f;
+}
+
 
 }  // extern "C"

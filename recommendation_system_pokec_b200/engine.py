@@ -26,7 +26,7 @@ ABI_SYMBOLS = (
     "pk_idf_size", "pk_get_idf", "pk_set_adj_row", "pk_pair_similarity", "pk_pair_fields", "pk_pair_overlap",
     "pk_fullscan_topk", "pk_fullscan_prepare", "pk_fullscan_execute", "pk_fullscan_fetch", "pk_fullscan_keys", "pk_recommend", "pk_candidates", "pk_fullscan_local_keys", "pk_merge_keys", "pk_sync",
     "pk_normalizers_from_pairs", "pk_edge_cache_build", "pk_edge_cache_drop", "pk_edge_cache_row", "pk_fullscan_execute_shortlists", "pk_fullscan_shortlist_keys", "pk_fullscan_execute_finish",
-    "pk_stream", "pk_stat", "pk_debug_prefilter",
+    "pk_stream", "pk_stat", "pk_debug_prefilter", "pk_world_save", "pk_world_open", "pk_world_close",
 )
 STAT_KERNEL_LAUNCHES, STAT_PAIRS_SCORED, STAT_STORE_BYTES, STAT_SCAN_KERNEL_NS, STAT_SCAN_LAUNCHES, STAT_GROUPS, \
     STAT_SHARD_RECORD_BYTES, STAT_H2D_BYTES, STAT_D2H_BYTES, STAT_PREFILTER, STAT_FALLBACK_QUERIES, STAT_RESCORE_NS, \
@@ -56,6 +56,8 @@ def load_library():
         lib.pk_stream.argtypes = [C.c_void_p]
         lib.pk_store_destroy.argtypes = [C.c_void_p]
         lib.pk_store_destroy.restype = None
+        lib.pk_world_close.argtypes = [C.c_void_p]
+        lib.pk_world_close.restype = None
         _lib = lib
     return _lib
 
@@ -65,16 +67,85 @@ def _check(lib, rc):
         raise PokecError(f"libpokec_b200 error {rc}: {lib.pk_last_error().decode()}")
 
 
+def world_save(world: World, path: str):
+    """the world as one mmap-able binary file (pk_world_save; no GPU needed)"""
+    lib = load_library()
+    pw = make_pk_world(world)
+    _check(lib, lib.pk_world_save(C.byref(pw), os.fsencode(path)))
+
+
+class WorldFile:
+    """A world file mapped read-only (pk_world_open).  `view` is the pk_world whose pointers point into the mapping;
+    `to_world()` copies it into a `World` (column names are not part of the file: pass them or get c0, c1, ...)."""
+
+    def __init__(self, path: str):
+        self.lib = load_library()
+        self.h = C.c_void_p()
+        self.view = PkWorld()
+        _check(self.lib, self.lib.pk_world_open(os.fsencode(path), C.byref(self.h), C.byref(self.view)))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.pk_world_close(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def to_world(self, text_columns=None) -> World:
+        v = self.view
+        n, T, m = int(v.n_users), int(v.n_text_cols), int(v.n_adj_rows)
+
+        def arr(p, count, dtype):
+            if count == 0 or not p:
+                return np.zeros(count, dtype)
+            return np.ctypeslib.as_array(p, shape=(count,)).astype(dtype, copy=True)
+
+        cp, fp, tp = arr(v.clubs_ptr, n + 1, np.int64), arr(v.friends_ptr, n + 1, np.int64), arr(v.tok_ptr, n * T + 1, np.int64)
+        ap = arr(v.adj_ptr, m + 1, np.int64)
+        ntk = int(tp[-1])
+        return World(text_columns=list(text_columns) if text_columns is not None else [f"c{i}" for i in range(T)],
+                     uid=arr(v.uid, n, np.int32), pub=arr(v.pub, n, np.int32), comp=arr(v.comp, n, np.int32),
+                     gender=arr(v.gender, n, np.int32), age=arr(v.age, n, np.int32),
+                     region=arr(v.region, 3 * n, np.int32).reshape(n, 3),
+                     clubs_ptr=cp, clubs=arr(v.clubs, int(cp[-1]), np.uint32),
+                     friends_ptr=fp, friends=arr(v.friends, int(fp[-1]), np.uint32),
+                     tok_ptr=tp, tok_id=arr(v.tok_id, ntk, np.int32), tok_tf=arr(v.tok_tf, ntk, np.int32),
+                     adj_uid=arr(v.adj_uid, m, np.int32), adj_ptr=ap, adj=arr(v.adj, int(ap[-1]), np.int32),
+                     norm_mean=arr(v.norm_mean, 7 + T, np.float32), norm_sd=arr(v.norm_sd, 7 + T, np.float32),
+                     norm_has=arr(v.norm_has, 7 + T, np.uint8))
+
+
 class DeviceRecommender:
-    def __init__(self, world: World, device: int = 0, compute_idf: bool = True):
+    def __init__(self, world: World, device: int = 0, compute_idf: bool = True, _view=None):
         self.lib = load_library()
         self.world = world
         self.h = C.c_void_p()
         _check(self.lib, self.lib.pk_store_create(int(device), C.byref(self.h)))
-        self._pw = make_pk_world(world)
+        self._pw = _view if _view is not None else make_pk_world(world)
         _check(self.lib, self.lib.pk_store_load_world(self.h, C.byref(self._pw)))
         if compute_idf:
             self.compute_idf()
+
+    @classmethod
+    def from_world_file(cls, path: str, device: int = 0, compute_idf: bool = True, text_columns=None):
+        """builds the device store straight from the mapped file (pk_world_open -> pk_store_load_world: no parse and
+        no host copy of the big arrays); `world` holds only what the host-side helpers need (sizes, names)"""
+        import types
+        with WorldFile(path) as f:
+            T, n = int(f.view.n_text_cols), int(f.view.n_users)
+            names = list(text_columns) if text_columns is not None else [f"c{i}" for i in range(T)]
+            shape = types.SimpleNamespace(T=T, n=n, n_fields=7 + T, text_columns=names)   # what the methods read from self.world
+            return cls(shape, device=device, compute_idf=compute_idf, _view=f.view)
 
     def close(self):
         if getattr(self, "h", None):

@@ -551,3 +551,28 @@ def test_cuda_path_vs_golden_fixtures(oracle_libs):
         tok, idf, _ = dev.get_idf(col)
         assert np.array_equal(bits(idf), bits(g[f"idf_dbl_{col}"]))
     dev.close()
+
+
+def test_store_from_world_file_identical(tmp_path):
+    """a store built straight from the mapped world file (pk_world_open -> pk_store_load_world) answers
+    every call exactly like the store built from the in-memory world"""
+    from recommendation_system_pokec_b200 import engine
+    w = make_test_world(n=3000, seed=61, pairs=500, uid_gap=True)
+    path = str(tmp_path / "world.pkw")
+    engine.world_save(w, path)
+    a = engine.DeviceRecommender(w)
+    b = engine.DeviceRecommender.from_world_file(path, text_columns=w.text_columns)
+    q = sample_queries(w, 48, seed=4)
+    for x, y in zip(a.fullscan(q, 50, EXCLUDE_SELF_AND_ADJ), b.fullscan(q, 50, EXCLUDE_SELF_AND_ADJ)):
+        assert np.array_equal(x, y)
+    for mode in (MODE_GRAPH, MODE_COLLAB, MODE_CLUBS):
+        for x, y in zip(a.recommend(mode, q, 20, 5000), b.recommend(mode, q, 20, 5000)):
+            assert np.array_equal(x, y), f"mode {mode}"
+    for t in range(0, w.T, 7):
+        ia, ib = a.get_idf(t), b.get_idf(t)
+        assert (ia is None) == (ib is None)
+        if ia is not None:
+            for x, y in zip(ia, ib):
+                assert np.array_equal(x, y)
+    a.close()
+    b.close()

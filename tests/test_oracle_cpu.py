@@ -145,3 +145,40 @@ def test_normalizer_pair_sample_matches_the_reference(oracle_libs):
         m, s = stats(v)
         assert m.tobytes() == mean[fld].tobytes() and s.tobytes() == sd[fld].tobytes(), f"field {fld}"
     orc.close()
+
+
+def test_world_file_round_trip_and_rejects_damage(tmp_path):
+    """SURVEY 8 f2 (pk_world_save / pk_world_open, host only): every array of the world survives the file bit for
+    bit; truncated, corrupted and foreign files are refused."""
+    from recommendation_system_pokec_b200 import engine
+    from tests.conftest import make_test_world
+    w = make_test_world(n=300, seed=41, T=5, pairs=100, uid_gap=True)
+    path = str(tmp_path / "world.pkw")
+    engine.world_save(w, path)
+    assert os.path.getsize(path) % 64 == 0 and not os.path.exists(path + ".tmp")
+    with engine.WorldFile(path) as f:
+        assert (f.view.n_users, f.view.n_text_cols, f.view.n_adj_rows) == (w.n, w.T, w.n_adj_rows)
+        back = f.to_world(w.text_columns)
+    for name in w._DTYPES:
+        a, b = getattr(w, name), getattr(back, name)
+        assert a.dtype == b.dtype and a.shape == b.shape and np.array_equal(a, b), name
+    blob = open(path, "rb").read()
+    cases = {"short": blob[:100], "truncated": blob[:-64], "magic": b"X" + blob[1:],
+             "header": blob[:40] + bytes([blob[40] ^ 1]) + blob[41:], "empty": b""}
+    for tag, data in cases.items():
+        bad = str(tmp_path / f"{tag}.pkw")
+        open(bad, "wb").write(data)
+        with pytest.raises(engine.PokecError):
+            engine.WorldFile(bad)
+    with pytest.raises(engine.PokecError):
+        engine.WorldFile(str(tmp_path / "missing.pkw"))
+    # an empty world is a valid file
+    e = make_test_world(n=300, seed=41, T=5, pairs=100)
+    e2 = type(e)(text_columns=e.text_columns, uid=e.uid[:0], pub=e.pub[:0], comp=e.comp[:0], gender=e.gender[:0], age=e.age[:0],
+                 region=e.region[:0], clubs_ptr=np.zeros(1, np.int64), clubs=e.clubs[:0], friends_ptr=np.zeros(1, np.int64),
+                 friends=e.friends[:0], tok_ptr=np.zeros(1, np.int64), tok_id=e.tok_id[:0], tok_tf=e.tok_tf[:0],
+                 adj_uid=e.adj_uid[:0], adj_ptr=np.zeros(1, np.int64), adj=e.adj[:0])
+    p0 = str(tmp_path / "empty_world.pkw")
+    engine.world_save(e2, p0)
+    with engine.WorldFile(p0) as f:
+        assert f.view.n_users == 0 and f.to_world(e.text_columns).n == 0
