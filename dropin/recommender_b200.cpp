@@ -16,6 +16,7 @@
 
 #include "pokec_b200.h"
 #include "recommender_b200_batch.h"
+#include "recommender_internal_sim.h"
 
 #include <algorithm>
 #include <cstdio>
@@ -126,9 +127,7 @@ namespace {
 
 // ---- world upload ----------------------------------------------------------------------------------
 // rows are sorted by uid so that a row range of the store is a user-id range (the multi-GPU shard key)
-void upload_world(Shim& s, const Recommender& r, int T) {
-    if (!s.store) PKCHECK(pk_store_create(device_from_env(), &s.store));
-    Flat f;
+void flatten(const Recommender& r, int T, Flat& f) {
     f.begin();
     const auto& P = *r.profiles;
     vector<const UserProfile*> order;
@@ -150,6 +149,13 @@ void upload_world(Shim& s, const Recommender& r, int T) {
             f.adj_ptr.push_back((int64_t)f.adj.size());
         }
     }
+}
+
+void upload_world(Shim& s, const Recommender& r, int T) {
+    if (!s.store) PKCHECK(pk_store_create(device_from_env(), &s.store));
+    Flat f;
+    flatten(r, T, f);
+    const auto& P = *r.profiles;
     PKCHECK(pk_store_load_world(s.store, f.finish(T)));
     s.profiles_ptr = r.profiles; s.adj_ptr = r.adj_list;
     s.n_profiles = P.size(); s.n_adj = r.adj_list ? r.adj_list->size() : 0;
@@ -172,10 +178,9 @@ uint64_t norm_fingerprint(const Recommender& r, const vector<string>& cols) {
     return h;
 }
 
-void push_normalizers(pk_store* st, const Recommender& r, const vector<string>& cols) {
+void normalizer_arrays(const Recommender& r, const vector<string>& cols, vector<float>& mean, vector<float>& sd, vector<uint8_t>& has) {
     const int nf = PK_NUM_FIXED + (int)cols.size();
-    vector<float> mean(nf, 0.f), sd(nf, 0.f);
-    vector<uint8_t> has(nf, 0);
+    mean.assign(nf, 0.f); sd.assign(nf, 0.f); has.assign(nf, 0);
     for (int f = 0; f < PK_NUM_FIXED; ++f) {
         auto it = r.field_normalizers.find(kFixedKeys[f]);                 // recommender_similarity.cpp:28-36
         if (it != r.field_normalizers.end()) { mean[f] = it->second.first; sd[f] = it->second.second; has[f] = 1; }
@@ -184,7 +189,13 @@ void push_normalizers(pk_store* st, const Recommender& r, const vector<string>& 
         auto it = r.column_normalizers.find(cols[t]);                      // :105-111
         if (it != r.column_normalizers.end()) { mean[PK_NUM_FIXED + t] = it->second.first; sd[PK_NUM_FIXED + t] = it->second.second; has[PK_NUM_FIXED + t] = 1; }
     }
-    PKCHECK(pk_set_normalizers(st, mean.data(), sd.data(), has.data(), nf));
+}
+
+void push_normalizers(pk_store* st, const Recommender& r, const vector<string>& cols) {
+    vector<float> mean, sd;
+    vector<uint8_t> has;
+    normalizer_arrays(r, cols, mean, sd, has);
+    PKCHECK(pk_set_normalizers(st, mean.data(), sd.data(), has.data(), (int)mean.size()));
 }
 
 // Brings the device store in line with the Recommender's current public state.  `cols` is the column
@@ -394,12 +405,7 @@ vector<pair<int, float>> Recommender::recommend_friends_by_interest(int user, in
 }
 
 // ---- batched calls (recommender_b200_batch.h) -------------------------------------------------------
-// include/recommender.h:70 befriends this struct and no reference translation unit defines it: the drop-in uses it
-// to read the private column list from a free function.
-struct RecommenderInternalSim {
-    static const vector<string>& columns(const Recommender& r) { return r.text_columns_internal; }
-};
-
+// (the private column list is read through the friend struct of recommender_internal_sim.h)
 namespace pokec_b200 {
 
 int batch_mode_from_name(const string& name) {
@@ -424,6 +430,60 @@ vector<vector<pair<int, float>>> recommend_batch(const Recommender& r, int pk_mo
         for (int j = 0; j < cnt[i]; ++j) out[i].emplace_back(id[i * topk + j], sc[i * topk + j]);
     }
     return out;
+}
+
+// ---- the reference's containers <-> one world file (pk_world_save / pk_world_open) ----------------------
+bool save_world_file(const Recommender& r, const string& path) {
+    if (!r.profiles) return false;
+    const vector<string>& cols = RecommenderInternalSim::columns(r);
+    const int T = (int)cols.size();
+    Flat f;
+    flatten(r, T, f);
+    normalizer_arrays(r, cols, f.nmean, f.nsd, f.nhas);
+    pk_world w = *f.finish(T);
+    w.norm_mean = f.nmean.data(); w.norm_sd = f.nsd.data(); w.norm_has = f.nhas.data();
+    if (pk_world_save(&w, path.c_str()) != PK_OK) {
+        fprintf(stderr, "[pokec_b200] save_world_file: %s\n", pk_last_error());
+        return false;
+    }
+    return true;
+}
+
+int load_world_file(const string& path, unordered_map<int, UserProfile>& profiles, unordered_map<int, vector<int>>& adj_list,
+                    vector<float>* norm_mean, vector<float>* norm_sd, vector<uint8_t>* norm_has) {
+    pk_world_file* f = nullptr;
+    pk_world w;
+    if (pk_world_open(path.c_str(), &f, &w) != PK_OK) {
+        fprintf(stderr, "[pokec_b200] load_world_file: %s\n", pk_last_error());
+        return -1;
+    }
+    const int n = w.n_users, T = w.n_text_cols, m = w.n_adj_rows;
+    profiles.clear();
+    profiles.reserve((size_t)n);
+    for (int i = 0; i < n; ++i) {
+        UserProfile p;
+        p.user_id = w.uid[i];
+        p.public_flag = w.pub[i]; p.completion_percentage = w.comp[i]; p.gender = w.gender[i]; p.age = w.age[i];
+        p.region_parts = {w.region[3 * i], w.region[3 * i + 1], w.region[3 * i + 2]};
+        p.clubs.assign(w.clubs + w.clubs_ptr[i], w.clubs + w.clubs_ptr[i + 1]);
+        p.friends.assign(w.friends + w.friends_ptr[i], w.friends + w.friends_ptr[i + 1]);
+        p.token_cols.resize((size_t)T);
+        for (int t = 0; t < T; ++t) {
+            const int64_t b = w.tok_ptr[(int64_t)i * T + t], e = w.tok_ptr[(int64_t)i * T + t + 1];
+            p.token_cols[t].reserve((size_t)(e - b));
+            for (int64_t j = b; j < e; ++j) p.token_cols[t].emplace(w.tok_id[j], w.tok_tf[j]);
+        }
+        profiles.emplace(w.uid[i], std::move(p));
+    }
+    adj_list.clear();
+    adj_list.reserve((size_t)m);
+    for (int i = 0; i < m; ++i) adj_list.emplace(w.adj_uid[i], vector<int>(w.adj + w.adj_ptr[i], w.adj + w.adj_ptr[i + 1]));
+    const int nf = PK_NUM_FIXED + T;
+    if (norm_mean) norm_mean->assign(w.norm_mean, w.norm_mean + nf);
+    if (norm_sd) norm_sd->assign(w.norm_sd, w.norm_sd + nf);
+    if (norm_has) norm_has->assign(w.norm_has, w.norm_has + nf);
+    pk_world_close(f);
+    return T;
 }
 
 }  // namespace pokec_b200

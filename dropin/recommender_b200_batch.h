@@ -9,8 +9,11 @@
 #pragma once
 
 #include "recommender.h"
+#include "user_profile.h"
 
+#include <cstdint>
 #include <string>
+#include <unordered_map>
 #include <utility>
 #include <vector>
 
@@ -25,5 +28,19 @@ int batch_mode_from_name(const std::string& name);
 // same ids in the same order, same float scores.  Unknown users and users without neighbours get an empty list.
 std::vector<std::vector<std::pair<int, float>>> recommend_batch(const Recommender& rec, int pk_mode, const std::vector<int>& users,
                                                                 int topk, int candidate_limit);
+
+// ---- the reference's containers <-> one binary world file -------------------------------
+// (pk_world_save / pk_world_open, include/pokec_b200.h).  Replaces the CSV round trip of save_users_encoded /
+// load_users_encoded (src/user_loader.cpp:10-96, capped at 100 000 users) and adjacency.csv
+// (src/graph_builder.cpp:39-75) for a server that restarts on unchanged data.
+//   save_world_file  writes rec's profiles (rows in uid order), adjacency and normalizers; columns are the list given
+//                    to rec.set_text_columns.  false (message on stderr) when the file cannot be written.
+//   load_world_file  clears and fills the caller's maps; returns the number of text columns, -1 on a missing /
+//                    damaged file (message on stderr).  The optional vectors receive the [7 + T] normalizer arrays
+//                    (fixed fields in the order public, gender, completion, age, region, clubs, friends; then columns).
+bool save_world_file(const Recommender& rec, const std::string& path);
+int load_world_file(const std::string& path, std::unordered_map<int, UserProfile>& profiles,
+                    std::unordered_map<int, std::vector<int>>& adj_list, std::vector<float>* norm_mean = nullptr,
+                    std::vector<float>* norm_sd = nullptr, std::vector<uint8_t>* norm_has = nullptr);
 
 }  // namespace pokec_b200

@@ -27,8 +27,12 @@
 using namespace std;
 
 // The reference declares `friend struct ::RecommenderInternalSim` (include/recommender.h:15,70) and
-// never defines it.  Defining it here gives the tests access to the private per-field helpers so
-// that each float rounding point can be pinned separately.
+// never defines it.  Defining it gives the tests access to the private per-field helpers so that each
+// float rounding point can be pinned separately.  Inside the drop-in library the definition is the
+// drop-in's own header (one definition per library); the compiled-reference build defines it here.
+#ifdef PK_DROPIN_BUILD
+#include "recommender_internal_sim.h"
+#else
 struct RecommenderInternalSim {
     static float set_sim(const vector<uint32_t>& a, const vector<uint32_t>& b) {
         return Recommender::vec_set_similarity(a, b);
@@ -44,6 +48,7 @@ struct RecommenderInternalSim {
         return r.tfidf_cosine_for_column(a, b, idf);
     }
 };
+#endif
 
 namespace {
 
@@ -344,6 +349,56 @@ long long ref_normalizer_pairs(void* hv, int sample_size, int comps_per_user, in
     }
     return n;
 }
+
+#ifdef PK_DROPIN_BUILD
+}  // extern "C"
+#include "recommender_b200_batch.h"
+extern "C" {
+// SURVEY 8 f2 through the reference's own containers: the handle's Recommender is written with
+// pokec_b200::save_world_file, read back with load_world_file into fresh maps, and the two worlds are compared
+// member by member.  0 = identical; otherwise the number of the first check that failed.
+int ref_world_file_round_trip(void* hv, const char* path) {
+    auto* h = (RefHandle*)hv;
+    if (!pokec_b200::save_world_file(*h->rec, path)) return 1;
+    unordered_map<int, UserProfile> P;
+    unordered_map<int, vector<int>> A;
+    vector<float> mean, sd;
+    vector<uint8_t> has;
+    const int T = pokec_b200::load_world_file(path, P, A, &mean, &sd, &has);
+    if (T != (int)h->cols.size()) return 2;
+    if (P.size() != h->profiles.size() || A.size() != h->adj.size()) return 3;
+    for (auto& kv : h->profiles) {
+        auto it = P.find(kv.first);
+        if (it == P.end()) return 4;
+        const UserProfile &a = kv.second, &b = it->second;
+        if (b.user_id != kv.first || a.public_flag != b.public_flag || a.completion_percentage != b.completion_percentage ||
+            a.gender != b.gender || a.age != b.age || a.region_parts != b.region_parts) return 5;
+        if (a.clubs != b.clubs || a.friends != b.friends) return 6;
+        if ((int)b.token_cols.size() != T) return 7;
+        for (int t = 0; t < T; ++t) {
+            static const unordered_map<int, int> none;
+            const auto& ca = (size_t)t < a.token_cols.size() ? a.token_cols[t] : none;
+            if (ca != b.token_cols[t]) return 8;
+        }
+    }
+    for (auto& kv : h->adj) {
+        auto it = A.find(kv.first);
+        if (it == A.end() || it->second != kv.second) return 9;
+    }
+    if ((int)mean.size() != PK_NUM_FIXED + T || sd.size() != mean.size() || has.size() != mean.size()) return 10;
+    static const char* fixed[PK_NUM_FIXED] = {"public", "gender", "completion", "age", "region", "clubs", "friends"};
+    for (int f = 0; f < PK_NUM_FIXED + T; ++f) {
+        const auto& m = f < PK_NUM_FIXED ? h->rec->field_normalizers : h->rec->column_normalizers;
+        auto it = m.find(f < PK_NUM_FIXED ? string(fixed[f]) : h->cols[f - PK_NUM_FIXED]);
+        if ((it != m.end()) != (has[f] != 0)) return 11;
+        if (it != m.end() && (memcmp(&it->second.first, &mean[f], 4) != 0 || memcmp(&it->second.second, &sd[f], 4) != 0)) return 12;
+    }
+    unordered_map<int, UserProfile> P2;
+    unordered_map<int, vector<int>> A2;
+    if (pokec_b200::load_world_file(string(path) + ".missing", P2, A2) != -1) return 13;
+    return 0;
+}
+#endif
 
 // mutate one adjacency row behind the live Recommender (what src/test.cpp:59-73 does)
 int ref_set_adj_row(void* hv, int uid, int n, const int32_t* nb) {

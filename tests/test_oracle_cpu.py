@@ -182,3 +182,26 @@ def test_world_file_round_trip_and_rejects_damage(tmp_path):
     engine.world_save(e2, p0)
     with engine.WorldFile(p0) as f:
         assert f.view.n_users == 0 and f.to_world(e.text_columns).n == 0
+
+
+def test_world_file_round_trip_through_reference_containers(tmp_path):
+    """SURVEY 8 f2 on the reference side: pokec_b200::save_world_file writes the drop-in Recommender's profile map,
+    adjacency map and normalizer maps; load_world_file rebuilds fresh unordered_maps of UserProfile from the file;
+    the C++ check in oracle/ref_driver.cpp (drop-in build) compares every member.  Host only: no GPU call is made."""
+    import ctypes as C
+    from oracle.oracle import CpuOracle, dropin_available
+    if not dropin_available():
+        pytest.skip("dropin/_build/libpokec_dropin.so not built (needs the reference headers)")
+    w = make_test_world(n=400, seed=5, T=6, pairs=200, uid_gap=True)
+    o = CpuOracle(w, kind="dropin", compute_idf=False)
+    o.lib.ref_world_file_round_trip.argtypes = [C.c_void_p, C.c_char_p]
+    path = str(tmp_path / "w.pkw")
+    assert o.lib.ref_world_file_round_trip(o.h, path.encode()) == 0
+    # the file the drop-in wrote is the same format the Python side reads
+    from recommendation_system_pokec_b200 import engine
+    with engine.WorldFile(path) as f:
+        back = f.to_world(w.text_columns)
+    order = np.argsort(w.uid)
+    assert np.array_equal(back.uid, w.uid[order]) and np.array_equal(back.age, w.age[order])
+    assert np.array_equal(back.norm_mean, w.norm_mean) and np.array_equal(back.norm_has, w.norm_has)
+    o.close()
