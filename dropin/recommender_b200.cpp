@@ -412,6 +412,7 @@ int batch_mode_from_name(const string& name) {
     if (name == "graph" || name == "interest") return PK_MODE_GRAPH;      // recommender_graph.cpp:224-227: interest is an alias
     if (name == "collaborative") return PK_MODE_COLLAB;
     if (name == "clubs") return PK_MODE_CLUBS;
+    if (name == "fullscan") return kBatchFullscan;
     return -1;
 }
 
@@ -424,7 +425,10 @@ vector<vector<pair<int, float>>> recommend_batch(const Recommender& r, int pk_mo
     const size_t nq = users.size();
     vector<int32_t> q(users.begin(), users.end()), id(nq * (size_t)topk), cnt(nq, 0);
     vector<float> sc(nq * (size_t)topk);
-    PKCHECK(pk_recommend(s.store, pk_mode, (int)nq, q.data(), topk, candidate_limit, id.data(), sc.data(), cnt.data()));
+    if (pk_mode == kBatchFullscan)   // every profile is a candidate; the user and the existing friends are excluded (recommender_graph.cpp:46-52)
+        PKCHECK(pk_fullscan_topk(s.store, (int)nq, q.data(), topk, PK_EXCLUDE_SELF_AND_ADJ, id.data(), sc.data(), cnt.data()));
+    else
+        PKCHECK(pk_recommend(s.store, pk_mode, (int)nq, q.data(), topk, candidate_limit, id.data(), sc.data(), cnt.data()));
     for (size_t i = 0; i < nq; ++i) {
         out[i].reserve((size_t)cnt[i]);
         for (int j = 0; j < cnt[i]; ++j) out[i].emplace_back(id[i * topk + j], sc[i * topk + j]);

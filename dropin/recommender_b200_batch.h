@@ -20,7 +20,11 @@
 namespace pokec_b200 {
 
 // "graph" | "collaborative" | "interest" | "clubs" (the keys of api_cli's "recommendations" object,
-// src/api_cli.cpp:213-236) -> PK_MODE_*; -1 for anything else.
+// src/api_cli.cpp:213-236) -> PK_MODE_*; "fullscan" -> kBatchFullscan; -1 for anything else.
+// kBatchFullscan is the path BASELINE.json's north_star names: FAS top-k of the user against EVERY profile instead of
+// the friends-of-friends candidate set, minus the user and the existing friends (pk_fullscan_topk; topk <= kBatchMaxK).
+constexpr int kBatchFullscan = 100;
+constexpr int kBatchMaxK = 256;
 int batch_mode_from_name(const std::string& name);
 
 // out[i] is exactly what the single-user member returns for users[i] with the same topk / candidate_limit

@@ -85,3 +85,39 @@ def test_api_cli_batch_lines_equal_user_lines(tmp_path):
     assert k7["k"] == 7 and k7["results"][0]["items"] == ref_recs[2]["graph"][:7]
     assert our_lines[n0 + 6:n0 + 10] == ['{"error":"bad batch"}'] * 4
     assert json.loads(our_lines[n0 + 10]) == {"ok": True, "exiting": True}
+
+
+def test_api_cli_save_and_batch_fullscan(tmp_path):
+    """SURVEY 8 f1 + f2 through the server: SAVE writes the world the server actually holds (CSV loaders,
+    fill_missing_ages and the parsed normalizers applied) as a world file; `BATCH fullscan` -- the north-star path,
+    FAS top-k against every profile -- must then equal the CPU oracle run on exactly that file."""
+    import json
+    from oracle.oracle import CpuOracle
+    from recommendation_system_pokec_b200 import engine
+    from recommendation_system_pokec_b200.cabi import EXCLUDE_SELF_AND_ADJ
+    if not os.path.exists(BATCH_BIN):
+        pytest.skip("api_cli_b200_batch not built (dropin/build_api_cli.py needs the reference sources)")
+    w = make_test_world(n=1500, seed=31, pairs=800)
+    w.age[::9] = 0
+    d = str(tmp_path)
+    write_reference_data_dir(w, d)
+    users = [int(u) for u in sample_queries(w, 40, seed=12)]
+    path = os.path.join(d, "world.pkw")
+    text = f"SAVE {path}\nBATCH fullscan 50 {' '.join(map(str, users))}\nSAVE\nBATCH fullscan 257 {users[0]}\nEXIT\n"
+    lines, err = run(BATCH_BIN, d, text)
+    assert "[pokec_b200] fatal" not in err
+    assert json.loads(lines[0]) == {"ok": True, "saved": path}
+    assert lines[2] == '{"error":"save failed"}' and lines[3] == '{"error":"bad batch"}'
+    with engine.WorldFile(path) as f:
+        served = f.to_world(w.text_columns)
+    assert served.n == w.n and not (served.age <= 0).any()          # the server filled the missing ages
+    orc = CpuOracle(served, kind="port")
+    want_id, want_sc, want_cnt = orc.fullscan(np.array(users, np.int32), 50, EXCLUDE_SELF_AND_ADJ, nthreads=8)
+    rep = json.loads(lines[1])
+    assert rep["mode"] == "fullscan" and rep["k"] == 50 and len(rep["results"]) == len(users)
+    for i, (u, res) in enumerate(zip(users, rep["results"])):
+        assert res["user_id"] == u and len(res["items"]) == int(want_cnt[i])
+        assert [it["id"] for it in res["items"]] == [int(x) for x in want_id[i, :want_cnt[i]]], f"user {u}"
+        got = np.array([it["score"] for it in res["items"]])
+        assert np.abs(got - want_sc[i, :want_cnt[i]].astype(np.float64)).max() <= 2e-6
+    orc.close()
