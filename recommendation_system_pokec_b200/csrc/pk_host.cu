@@ -106,6 +106,7 @@ double h_sigmoid(double x) {
 
 struct FullscanJob {
     bool valid = false;
+    int64_t gen = -1;                         // pk_store::gen the plan was built for
     int nq = 0, k = 0, K = 0, Kp = 0, exclude = 0, n_groups = 0;
     bool with_excl = false;
     size_t n_sm = 0, n_gl = 0;
@@ -217,6 +218,10 @@ struct pk_store {
     std::vector<float> h_edge_fas;
     bool edge_cache_valid = false;
     FullscanJob job;
+    // bumped by every call that changes what a prepared full-scan plan depends on (world, shard, normalizers, idf,
+    // adjacency overrides): a plan stamped with an older value is refused by execute / finish / fetch / keys
+    int64_t gen = 0;
+    int64_t max_cell = 0;     // longest token cell of the loaded world (scales the pre-filter's error bound)
     bool scan_time_pending = false;
     int64_t stat_h2d = 0, stat_d2h = 0;
     int64_t last_idf_n = 0;
@@ -430,9 +435,16 @@ int rebuild_norm(pk_store* s) {
                 L.lut[j][bits] = (float)acc;
             }
         L.inv_total = (float)(1.0 / (double)nf);
-        // per-field error: relative error of an fp32 cosine (<= 64 products) times the sensitivity above, plus the
-        // ex2/rcp approximations; the mean over fields cannot exceed the worst field; dFAS/dS <= 2; safety factor 2
-        const double rel_s = 4.2e-6;
+        // Error bound of the fp32 score.  A text cosine is a sum of m <= min(nnz_q, nnz_c) <= max_cell positive
+        // products of two normalised weights: each weight is one rounding of an fp64 quotient (2^-24 relative), each
+        // fmaf adds at most 2^-24 of the partial sum, so the cosine is off by at most (m + 2) 2^-24 relative --
+        // 4.2e-6 for the 64 products the bound was first written for, scaled here by the LONGEST cell of the loaded
+        // world (a 300-token cell gives 1.8e-5).  The set similarities (three roundings) are far inside that.
+        // sigma(z(s)) moves by at most `worst` per unit of relative error of s; ex2.approx / rcp.approx, the fp32 sum
+        // of <= 56 sigmas and the two approximate divisions add < 4e-6 absolute (5e-6 taken); the mean over fields
+        // cannot exceed the worst field; dFAS/dS <= 2; safety factor 2.  lean_usable() gives the pre-filter up
+        // (exact scan on every pair) when the bound exceeds 1e-3.
+        const double rel_s = std::max(4.2e-6, ((double)s->max_cell + 6.0) * 5.9604645e-8);
         L.margin = (float)(2.0 * 2.0 * (worst * rel_s + 5e-6));
         L.dim_comp = N.dim_comp; L.dim_age = N.dim_age;
         s->margin = L.margin;
@@ -696,6 +708,29 @@ void finish_group(pk_store* s, Plan& plan, GroupDesc& g, const uint32_t* excl_n,
     plan.groups.push_back(g);
 }
 
+// merge_topk_kernel launch: sort buffer sized for K (power of two >= 2K, at least 2048 keys)
+int launch_merge(pk_store* s, MergeParams M, int n_queries) {
+    if (n_queries <= 0) return PK_OK;
+    int cap = 2048;
+    while (cap < 2 * M.K) cap <<= 1;
+    M.cap = cap;
+    const size_t smem = ((size_t)cap + (size_t)M.K) * 8;
+    if (smem > (size_t)s->max_smem) return fail(PK_ERR_UNSUPPORTED, "top-k of %d exceeds the selection kernel's shared memory", M.K);
+    if (smem > 48 * 1024) CK(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    merge_topk_kernel<<<(unsigned)n_queries, kMergeThreads, smem, s->stream>>>(M);
+    ++s->stat_launches;
+    CK(cudaGetLastError());
+    return PK_OK;
+}
+
+// top-k of a flat key slice per user (collaborative / clubs / wide graph epilogue): keys[begin[u] .. begin[u+1])
+int launch_slice_topk(pk_store* s, const uint64_t* keys, const int32_t* begin, int nu, int K, uint64_t* out_keys) {
+    MergeParams M;
+    memset(&M, 0, sizeof(M));
+    M.keys = keys; M.seg_begin = begin; M.nq = nu; M.K = K; M.out_keys = out_keys;
+    return launch_merge(s, M, nu);
+}
+
 void decode_keys(const uint64_t* keys, int nq, int k, int32_t* out_id, float* out_score, int32_t* out_cnt) {
     for (int q = 0; q < nq; ++q) {
         int c = 0;
@@ -713,9 +748,9 @@ void decode_keys(const uint64_t* keys, int nq, int k, int32_t* out_id, float* ou
     }
 }
 
-int check_topk_args(pk_store* s, int nq, const int32_t* q_uid, int k) {
+int check_topk_args(pk_store* s, int nq, const int32_t* q_uid, int k, int max_k = kMaxK) {
     if (nq < 0 || k < 0 || (nq > 0 && !q_uid)) return fail(PK_ERR_ARG, "bad nq/k/q_uid");
-    if (k > kMaxK) return fail(PK_ERR_UNSUPPORTED, "k = %d exceeds the supported maximum %d", k, kMaxK);
+    if (k > max_k) return fail(PK_ERR_UNSUPPORTED, "k = %d exceeds the supported maximum %d", k, max_k);
     (void)s;
     return PK_OK;
 }
@@ -723,10 +758,19 @@ int check_topk_args(pk_store* s, int nq, const int32_t* q_uid, int k) {
 // ---- full scan ---------------------------------------------------------------------------------------
 // prepare: host planning + upload (queries -> groups -> work items); execute: arena clear, group_prep,
 // scan, merge -- all asynchronous on the store's stream, device-resident inputs only; fetch: D2H + decode.
+int job_ok(pk_store* s) {
+    if (!s->job.valid) return fail(PK_ERR_STATE, "pk_fullscan_prepare has not been called");
+    if (s->job.gen != s->gen)
+        return fail(PK_ERR_STATE, "the prepared full scan is stale: the world, shard, normalizers, idf or adjacency changed after "
+                                  "pk_fullscan_prepare (prepare again)");
+    return PK_OK;
+}
+
 bool lean_usable(pk_store* s, int K, int* Ks_out) {
     const char* e = getenv("POKEC_B200_NO_PREFILTER");
     if (e && e[0] == '1') return false;
     if (s->tf_negative || s->wide_ids) return false;
+    if (!(s->margin < 1e-3f)) return false;     // cells so long that the fp32 bound is useless: exact scan on every pair
     for (int t = 0; t < s->T; ++t)
         if (s->col_state[t] == 2)
             for (float v : s->custom_idf[t]) if (!(v >= 0.0f)) return false;   // negative weights break the error bound
@@ -747,7 +791,7 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
     J.lean = false; J.Ks = 0; J.n_pre = 0; J.n_rr_sm = J.n_rr_gl = 0; J.rr_pairs = 0;
     TRY(J.keys_b.reserve((size_t)std::max(nq, 1) * K));
     const int64_t n_cand = s->shard_end - s->shard_begin;
-    if (nq == 0 || k == 0 || n_cand <= 0) { J.valid = true; return PK_OK; }
+    if (nq == 0 || k == 0 || n_cand <= 0) { J.valid = true; J.gen = s->gen; return PK_OK; }
     int Ks = 0;
     const bool lean = lean_usable(s, K, &Ks);
     if (lean) TRY(rebuild_lean(s));
@@ -800,7 +844,7 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
     close_group();
     const int ng = (int)plan.groups.size();
     J.n_groups = ng;
-    if (ng == 0) { J.valid = true; return PK_OK; }
+    if (ng == 0) { J.valid = true; J.gen = s->gen; return PK_OK; }
     uint64_t off = 0;
     for (auto& gg : plan.groups) {
         gg.arena_off = (uint32_t)off;
@@ -922,6 +966,7 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
     }
     CK(cudaStreamSynchronize(s->stream));
     J.valid = true;
+    J.gen = s->gen;
     return PK_OK;
 }
 
@@ -952,7 +997,7 @@ PreParams base_pre_params(pk_store* s) {
 
 int fullscan_shortlists(pk_store* s) {
     FullscanJob& J = s->job;
-    if (!J.valid) return fail(PK_ERR_STATE, "pk_fullscan_prepare has not been called");
+    TRY(job_ok(s));
     s->stat_scan_ns = 0; s->stat_scan_launches = 0; s->stat_prefilter_ns = 0;
     s->stat_pairs = J.pairs; s->stat_groups = J.n_groups;
     CK(cudaMemsetAsync(J.keys_b.p, 0, (size_t)std::max(J.nq, 1) * J.K * 8, s->stream));
@@ -981,10 +1026,7 @@ int fullscan_shortlists(pk_store* s) {
         P.out_keys = J.keys_a.p;
         TRY((launch_scan<EPI_TOPK, false>(s, P, J.items.p, J.n_sm, J.n_gl, J.max_smem_arena)));
         M.keys = J.keys_a.p; M.slot0 = J.q_slot0.p; M.n_lists_q = J.q_nl.p; M.stride_k = J.Kp;
-        merge_topk_kernel<<<J.nq, 128, 0, s->stream>>>(M);
-        ++s->stat_launches;
-        CK(cudaGetLastError());
-        return PK_OK;
+        return launch_merge(s, M, J.nq);
     }
 
     // 1. pre-filter: fp32 scores of every pair, Ks best per query and slice
@@ -1012,10 +1054,8 @@ int fullscan_shortlists(pk_store* s) {
     memset(&MS, 0, sizeof(MS));
     MS.keys = J.keys_pre.p; MS.slot0 = J.pre_slot0.p; MS.n_lists_q = J.pre_nl.p; MS.lane = J.q_lane.p;
     MS.nq = J.nq; MS.K = Ks; MS.stride_k = Ks; MS.out_keys = J.keys_short.p;
-    merge_topk_kernel<<<J.nq, 128, 0, s->stream>>>(MS);
-    ++s->stat_launches;
-    CK(cudaGetLastError());
-    return PK_OK;
+    MS.poison_group_fail = J.lean_fail.p; MS.q_group = J.q_group.p;
+    return launch_merge(s, MS, J.nq);
 }
 
 // Second half of the two-stage scan: proof, exact re-score, fallback, final merge.  With shortlists gathered from
@@ -1025,7 +1065,7 @@ int fullscan_shortlists(pk_store* s) {
 // over its own shard.  The per-rank [nq][k] keys are then merged by the caller exactly as before.
 int fullscan_finish(pk_store* s, const uint64_t* d_all_short, int n_lists, int rank, int n_ranks) {
     FullscanJob& J = s->job;
-    if (!J.valid) return fail(PK_ERR_STATE, "pk_fullscan_prepare has not been called");
+    TRY(job_ok(s));
     if (n_ranks < 1 || rank < 0 || rank >= n_ranks || n_lists < 1) return fail(PK_ERR_ARG, "bad rank / n_ranks / n_lists");
     if (J.n_groups == 0 || !J.lean) return PK_OK;       // the exact scan of the first half already produced the keys
     const int Ks = J.Ks;
@@ -1035,8 +1075,7 @@ int fullscan_finish(pk_store* s, const uint64_t* d_all_short, int n_lists, int r
         MergeParams MG;
         memset(&MG, 0, sizeof(MG));
         MG.keys = d_all_short; MG.n_lists = n_lists; MG.nq = J.nq; MG.K = Ks; MG.stride_k = Ks; MG.out_keys = J.keys_short_all.p;
-        merge_topk_kernel<<<J.nq, 128, 0, s->stream>>>(MG);
-        ++s->stat_launches;
+        TRY(launch_merge(s, MG, J.nq));
         short_keys = J.keys_short_all.p;
     }
     ScanParams P = base_scan_params(s, J.K);
@@ -1069,10 +1108,7 @@ int fullscan_finish(pk_store* s, const uint64_t* d_all_short, int n_lists, int r
     // 5. final merge: the re-scored shortlist, or the full exact scan where the shortlist was not proven
     M.keys = J.keys_rr.p; M.slot0 = J.rr_slot0.p; M.n_lists_q = J.rr_nl.p; M.stride_k = J.Kp;
     M.q_flag = J.q_flag.p; M.alt_keys = J.keys_a.p; M.alt_slot0 = J.q_slot0.p; M.alt_n_lists_q = J.q_nl.p; M.alt_stride_k = J.Kp;
-    merge_topk_kernel<<<J.nq, 128, 0, s->stream>>>(M);
-    ++s->stat_launches;
-    CK(cudaGetLastError());
-    return PK_OK;
+    return launch_merge(s, M, J.nq);
 }
 
 int fullscan_execute(pk_store* s) {
@@ -1082,7 +1118,7 @@ int fullscan_execute(pk_store* s) {
 
 int fullscan_fetch(pk_store* s, int32_t* out_id, float* out_score, int32_t* out_cnt) {
     FullscanJob& J = s->job;
-    if (!J.valid) return fail(PK_ERR_STATE, "pk_fullscan_prepare has not been called");
+    TRY(job_ok(s));
     if (J.nq == 0) return PK_OK;
     if (J.k == 0) { for (int q = 0; q < J.nq; ++q) out_cnt[q] = 0; return PK_OK; }
     std::vector<uint64_t> keys((size_t)J.nq * J.k);
@@ -1175,12 +1211,24 @@ GroupDesc empty_group() {
 }
 
 // ---- recommend: graph / interest ---------------------------------------------------------------------
+// store-mode scores of 1-lane groups ([candidate][32], lane 0) -> sort keys with the candidates' uids
+__global__ void keys_from_scores_kernel(const float* __restrict__ f, const int32_t* __restrict__ cand_rows,
+                                        const int32_t* __restrict__ uid, int64_t n, uint64_t* __restrict__ keys) {
+    const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n) return;
+    keys[c] = make_key(__float_as_uint(f[c * 32]), uid[cand_rows[c]]);
+}
+
 int recommend_graph(pk_store* s, int nq, const int32_t* q_uid, int k, int limit, uint64_t* h_keys) {
     const int K = std::max(k, 1), Kp = (K + 31) / 32 * 32;
     Plan plan;
     std::vector<int32_t> cand_rows;
     std::vector<WorkItem> items;
     std::vector<int32_t> q_slot0(nq, 0), q_nl(nq, 0), q_lane(nq, 0);
+    // k beyond the fused shared-memory lists (the reference takes any topk, src/test.cpp:75 passes |friends| / 5):
+    // store-mode scan, then the sort-based selection over each query's slice
+    const bool wide = K > kMaxK;
+    std::vector<int32_t> q_begin((size_t)nq + 1, 0);
     // phase 1 (host threads): the candidate rows of every query, in the reference's order
     std::vector<std::vector<int32_t>> q_rows((size_t)nq);
     std::vector<int32_t> q_row((size_t)nq, -1);
@@ -1206,6 +1254,7 @@ int recommend_graph(pk_store* s, int nq, const int32_t* q_uid, int k, int limit,
     // phase 2: one single-lane group and one work item per query
     for (int q = 0; q < nq; ++q) {
         const int r = q_row[q];
+        q_begin[q] = q_begin[q + 1] = (int32_t)cand_rows.size();
         if (r < 0 || q_rows[q].empty()) continue;
         const int32_t c0 = (int32_t)cand_rows.size();
         cand_rows.insert(cand_rows.end(), q_rows[q].begin(), q_rows[q].end());
@@ -1214,15 +1263,35 @@ int recommend_graph(pk_store* s, int nq, const int32_t* q_uid, int k, int limit,
         g.n_lanes = 1; g.row[0] = r; g.qidx[0] = q;
         WorkItem it;
         it.group = (int32_t)plan.groups.size();
-        it.cand_begin = c0; it.cand_end = c1; it.out_slot = (int32_t)items.size();
-        finish_group(s, plan, g, nullptr, Kp);
+        it.cand_begin = c0; it.cand_end = c1; it.out_slot = wide ? c0 : (int32_t)items.size();
+        q_begin[q + 1] = c1;
+        finish_group(s, plan, g, nullptr, wide ? 0 : Kp);
         q_slot0[q] = it.out_slot; q_nl[q] = 1; q_lane[q] = 0;
         items.push_back(it);
         s->stat_pairs += c1 - c0;
     }
     s->stat_groups = (int64_t)plan.groups.size();
     std::vector<uint64_t> keys((size_t)std::max(nq, 1) * K, 0ull);
-    if (!items.empty()) {
+    if (!items.empty() && wide) {
+        const int64_t nc = (int64_t)cand_rows.size();
+        TRY(upload_plan(s, plan, false));
+        TRY(upload(s, s->d_cand_rows, cand_rows));
+        TRY(s->d_f32a.reserve((size_t)nc * 32));
+        TRY(s->d_keys_a.reserve((size_t)nc));
+        TRY(s->d_keys_b.reserve((size_t)nq * K));
+        ScanParams P = base_scan_params(s, K);
+        P.cand_rows = s->d_cand_rows.p;
+        P.out_f = s->d_f32a.p;
+        TRY((run_scan<EPI_STORE, false>(s, plan, P, items)));
+        keys_from_scores_kernel<<<(unsigned)((nc + 255) / 256), 256, 0, s->stream>>>(s->d_f32a.p, s->d_cand_rows.p, s->d_uid.p, nc,
+                                                                                    s->d_keys_a.p);
+        ++s->stat_launches;
+        CK(cudaGetLastError());
+        TRY(upload(s, s->d_i32a, q_begin));
+        TRY(launch_slice_topk(s, s->d_keys_a.p, s->d_i32a.p, nq, K, s->d_keys_b.p));
+        CK(cudaMemcpyAsync(keys.data(), s->d_keys_b.p, (size_t)nq * K * 8, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+    } else if (!items.empty()) {
         TRY(upload_plan(s, plan, false));
         TRY(upload(s, s->d_cand_rows, cand_rows));
         TRY(s->d_keys_a.reserve(items.size() * 32 * (size_t)Kp));
@@ -1238,9 +1307,7 @@ int recommend_graph(pk_store* s, int nq, const int32_t* q_uid, int k, int limit,
         memset(&M, 0, sizeof(M));
         M.keys = s->d_keys_a.p; M.slot0 = s->d_i32a.p; M.n_lists_q = s->d_i32b.p; M.lane = s->d_i32c.p;
         M.nq = nq; M.K = K; M.stride_k = Kp; M.out_keys = s->d_keys_b.p;
-        merge_topk_kernel<<<nq, 128, 0, s->stream>>>(M);
-        ++s->stat_launches;
-        CK(cudaGetLastError());
+        TRY(launch_merge(s, M, nq));
         CK(cudaMemcpyAsync(keys.data(), s->d_keys_b.p, (size_t)nq * K * 8, cudaMemcpyDeviceToHost, s->stream));
         CK(cudaStreamSynchronize(s->stream));
     }
@@ -1354,14 +1421,19 @@ int recommend_collab(pk_store* s, int nq, const int32_t* q_uid, int k, int limit
     s->stat_groups = (int64_t)plan.groups.size();
     std::vector<uint64_t> keys((size_t)std::max(nq, 1) * K, 0ull);
     const int nu = (int)users.size();
-    if (nu > 0 && rows > 0) {
-        TRY(upload_plan(s, plan, false));
-        TRY(upload(s, s->d_cand_rows, cand_rows));
-        TRY(s->d_f32a.reserve((size_t)rows * 32));
-        ScanParams P = base_scan_params(s, K);
-        P.cand_rows = s->d_cand_rows.p;
-        P.out_f = s->d_f32a.p;
-        TRY((run_scan<EPI_STORE, false>(s, plan, P, items)));
+    if (nu > 0) {
+        // a user none of whose friends has a profile still gets its candidates, each with score 0
+        // (src/recommender_graph.cpp:167-213: the sum over friends is empty, the candidate is emitted anyway),
+        // so the reduce and the top-k run whenever there are candidates; only the scan needs work items
+        TRY(s->d_f32a.reserve((size_t)std::max<int64_t>(rows, 1) * 32));
+        if (!items.empty()) {
+            TRY(upload_plan(s, plan, false));
+            TRY(upload(s, s->d_cand_rows, cand_rows));
+            ScanParams P = base_scan_params(s, K);
+            P.cand_rows = s->d_cand_rows.p;
+            P.out_f = s->d_f32a.p;
+            TRY((run_scan<EPI_STORE, false>(s, plan, P, items)));
+        }
 
         // reduce in friend order, then top-k per user
         std::vector<int32_t> ucb(nu + 1, 0), ufb(nu + 1, 0), fr_slot, cand_uid, u_ncand(nu);
@@ -1393,9 +1465,8 @@ int recommend_collab(pk_store* s, int nq, const int32_t* q_uid, int k, int limit
             R.out_keys = s->d_keys_a.p; R.nu = nu;
             collab_reduce_kernel<<<dim3(8, nu), 128, 0, s->stream>>>(R);
             ++s->stat_launches;
-            slice_topk_kernel<<<nu, 256, 0, s->stream>>>(s->d_keys_a.p, s->d_i32a.p, K, s->d_keys_b.p);
-            ++s->stat_launches;
             CK(cudaGetLastError());
+            TRY(launch_slice_topk(s, s->d_keys_a.p, s->d_i32a.p, nu, K, s->d_keys_b.p));
             std::vector<uint64_t> uk((size_t)nu * K);
             CK(cudaMemcpyAsync(uk.data(), s->d_keys_b.p, uk.size() * 8, cudaMemcpyDeviceToHost, s->stream));
             CK(cudaStreamSynchronize(s->stream));
@@ -1528,9 +1599,8 @@ int recommend_clubs_cached(pk_store* s, int nq, const int32_t* q_uid, int k, uin
             C.user_row = s->d_i32c.p; C.con_slot = s->d_i32d.p; C.slot_key = s->d_keys_a.p; C.slot_acc = s->d_f64a.p;
             clubs_scatter_kernel<<<nu, kClubThreads, 0, s->stream>>>(C);
             ++s->stat_launches;
-            slice_topk_kernel<<<nu, 256, 0, s->stream>>>(s->d_keys_a.p, s->d_i32b.p, K, s->d_keys_b.p);
-            ++s->stat_launches;
             CK(cudaGetLastError());
+            TRY(launch_slice_topk(s, s->d_keys_a.p, s->d_i32b.p, nu, K, s->d_keys_b.p));
             std::vector<uint64_t> uk((size_t)nu * K);
             CK(cudaMemcpyAsync(uk.data(), s->d_keys_b.p, uk.size() * 8, cudaMemcpyDeviceToHost, s->stream));
             CK(cudaStreamSynchronize(s->stream));
@@ -1649,9 +1719,8 @@ int recommend_clubs(pk_store* s, int nq, const int32_t* q_uid, int k, uint64_t* 
             C.user_row = s->d_i32c.p; C.con_slot = s->d_i32d.p; C.slot_key = s->d_keys_a.p; C.slot_acc = s->d_f64a.p;
             clubs_scatter_kernel<<<nu, kClubThreads, 0, s->stream>>>(C);
             ++s->stat_launches;
-            slice_topk_kernel<<<nu, 256, 0, s->stream>>>(s->d_keys_a.p, s->d_i32b.p, K, s->d_keys_b.p);
-            ++s->stat_launches;
             CK(cudaGetLastError());
+            TRY(launch_slice_topk(s, s->d_keys_a.p, s->d_i32b.p, nu, K, s->d_keys_b.p));
             std::vector<uint64_t> uk((size_t)nu * K);
             CK(cudaMemcpyAsync(uk.data(), s->d_keys_b.p, uk.size() * 8, cudaMemcpyDeviceToHost, s->stream));
             CK(cudaStreamSynchronize(s->stream));
@@ -1818,14 +1887,29 @@ int pk_store_load_world(pk_store* s, const pk_world* w) {
         return fail(PK_ERR_ARG, "null profile array");
     if (m > 0 && (!w->adj_uid || !w->adj_ptr)) return fail(PK_ERR_ARG, "null adjacency array");
     CK(cudaSetDevice(s->device));
+    // every offset array starts at 0 and never decreases (a damaged world file or a caller bug must not turn into
+    // out-of-bounds reads in the pack kernels or in the host's adjacency walk)
+    auto monotone = [](const int64_t* p, int64_t cnt) {
+        if (p[0] != 0) return false;
+        for (int64_t i = 0; i < cnt; ++i) if (p[i + 1] < p[i]) return false;
+        return true;
+    };
+    if (n > 0 && (!monotone(w->clubs_ptr, n) || !monotone(w->friends_ptr, n) || !monotone(w->tok_ptr, (int64_t)n * T)))
+        return fail(PK_ERR_ARG, "clubs_ptr / friends_ptr / tok_ptr must start at 0 and be non-decreasing");
+    if (m > 0 && !monotone(w->adj_ptr, m)) return fail(PK_ERR_ARG, "adj_ptr must start at 0 and be non-decreasing");
     const int64_t ncl = n ? w->clubs_ptr[n] : 0, nfr = n ? w->friends_ptr[n] : 0, nnz = n ? w->tok_ptr[(int64_t)n * T] : 0;
+    if ((ncl > 0 && !w->clubs) || (nfr > 0 && !w->friends) || (nnz > 0 && (!w->tok_id || !w->tok_tf)) ||
+        (m > 0 && w->adj_ptr[m] > 0 && !w->adj))
+        return fail(PK_ERR_ARG, "null element array");
     // cells sorted by token id (the reference's cells are hash maps: order-free); ids must fit 26 bits
     std::vector<int32_t> tid, ttf;
     const int32_t *tok_id = w->tok_id, *tok_tf = w->tok_tf;
     bool sorted = true, tf_negative = false;
+    int64_t max_cell = 0;
     for (int64_t c = 0; c < (int64_t)n * T; ++c) {
         const int64_t b = w->tok_ptr[c], e = w->tok_ptr[c + 1];
         if (e < b) return fail(PK_ERR_ARG, "tok_ptr not monotone");
+        max_cell = std::max(max_cell, e - b);
         for (int64_t j = b; j < e; ++j) {
             if ((uint32_t)tok_id[j] >= (1u << kTokBits)) return fail(PK_ERR_UNSUPPORTED, "token id %d outside [0, 2^26)", tok_id[j]);
             if (j > b && tok_id[j] <= tok_id[j - 1]) sorted = false;
@@ -1848,9 +1932,10 @@ int pk_store_load_world(pk_store* s, const pk_world* w) {
     }
     s->n = n; s->T = T; s->nnz = nnz;
     s->tf_negative = tf_negative;
+    s->max_cell = max_cell;
     s->wide_ids = false;
-    for (int64_t j = 0, e = w->clubs_ptr[n]; j < e && !s->wide_ids; ++j) s->wide_ids = (w->clubs[j] >> 31) != 0;
-    for (int64_t j = 0, e = w->friends_ptr[n]; j < e && !s->wide_ids; ++j) s->wide_ids = (w->friends[j] >> 31) != 0;
+    for (int64_t j = 0, e = ncl; j < e && !s->wide_ids; ++j) s->wide_ids = (w->clubs[j] >> 31) != 0;
+    for (int64_t j = 0, e = nfr; j < e && !s->wide_ids; ++j) s->wide_ids = (w->friends[j] >> 31) != 0;
     s->uid.assign(w->uid, w->uid + n);
     s->uid_sorted.resize(n);
     for (int i = 0; i < n; ++i) s->uid_sorted[i] = {w->uid[i], i};
@@ -1909,6 +1994,8 @@ int pk_store_load_world(pk_store* s, const pk_world* w) {
         for (int f = 0; f < nf; ++f) { s->nmean[f] = w->norm_mean[f]; s->nsd[f] = w->norm_sd[f]; s->nhas[f] = w->norm_has[f]; }
     s->norm_dirty = true; s->edge_cache_valid = false;
     s->shard_begin = 0; s->shard_end = n;
+    ++s->gen;
+    s->job.valid = false;
     s->loaded = true;
     return PK_OK;
 }
@@ -1918,6 +2005,7 @@ int pk_store_set_shard(pk_store* s, int64_t row_begin, int64_t row_end) {
     if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
     if (row_begin < 0 || row_end < row_begin || row_end > s->n) return fail(PK_ERR_ARG, "bad shard [%lld,%lld)", (long long)row_begin, (long long)row_end);
     s->shard_begin = row_begin; s->shard_end = row_end;
+    ++s->gen;
     return PK_OK;
 }
 
@@ -1928,6 +2016,7 @@ int pk_set_normalizers(pk_store* s, const float* mean, const float* sd, const ui
     if (!mean || !sd) return fail(PK_ERR_ARG, "null normalizer array");
     for (int f = 0; f < n_fields; ++f) { s->nmean[f] = mean[f]; s->nsd[f] = sd[f]; s->nhas[f] = has ? has[f] : 1; }
     s->norm_dirty = true; s->edge_cache_valid = false;
+    ++s->gen;
     return PK_OK;
 }
 
@@ -1937,6 +2026,7 @@ int pk_compute_idf(pk_store* s, int double_log) {
     for (int t = 0; t < s->T; ++t) { s->col_state[t] = 1; s->custom_tok[t].clear(); s->custom_idf[t].clear(); }
     s->double_log = double_log ? 1 : 0;
     s->idf_dirty = true; s->edge_cache_valid = false;
+    ++s->gen;
     CK(cudaSetDevice(s->device));
     return rebuild_idf(s);
 }
@@ -1956,6 +2046,7 @@ int pk_set_idf(pk_store* s, int col, const int32_t* token, const float* idf, int
         s->custom_idf[col].assign(idf, idf + n);
     }
     s->idf_dirty = true; s->edge_cache_valid = false;
+    ++s->gen;
     return PK_OK;
 }
 
@@ -2017,6 +2108,7 @@ int pk_get_idf(pk_store* s, int col, int32_t* token, float* idf, int32_t* df, in
 int pk_set_adj_row(pk_store* s, int32_t uid, const int32_t* nb, int64_t n) {
     if (!s || n < 0 || (n > 0 && !nb)) return fail(PK_ERR_ARG, "bad argument");
     if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
+    ++s->gen;          // a prepared full scan carries the exclusion ids of the old rows
     // a row equal to the loaded one needs no override (the drop-in re-sends the rows a query touches)
     auto it = s->adj_row.find(uid);
     if (it != s->adj_row.end()) {
@@ -2070,6 +2162,7 @@ int pk_normalizers_from_pairs(pk_store* s, int64_t n, const int32_t* a_uid, cons
     // raw-count weights: every column temporarily loses its idf table (src/recommender_similarity.cpp:103 path),
     // the packed store is rebuilt for the sample and again, lazily, for the next scoring call
     const std::vector<uint8_t> saved = s->col_state;
+    ++s->gen;
     std::fill(s->col_state.begin(), s->col_state.end(), (uint8_t)0);
     s->idf_dirty = true; s->store_dirty = true;
     std::vector<float> vals((size_t)n * nfo);        // region, clubs, friends, text columns of every pair
@@ -2189,7 +2282,7 @@ int pk_fullscan_execute_shortlists(pk_store* s) {
 int pk_fullscan_shortlist_keys(pk_store* s, uint64_t* d_short) {
     if (!s || !d_short) return fail(PK_ERR_ARG, "null argument");
     FullscanJob& J = s->job;
-    if (!J.valid) return fail(PK_ERR_STATE, "pk_fullscan_prepare has not been called");
+    TRY(job_ok(s));
     if (!J.lean || J.nq == 0) return PK_OK;
     CK(cudaSetDevice(s->device));
     CK(cudaMemcpyAsync(d_short, J.keys_short.p, (size_t)J.nq * J.Ks * 8, cudaMemcpyDeviceToDevice, s->stream));
@@ -2211,7 +2304,7 @@ int pk_fullscan_fetch(pk_store* s, int32_t* out_id, float* out_score, int32_t* o
 
 int pk_fullscan_keys(pk_store* s, uint64_t* d_keys) {
     if (!s) return fail(PK_ERR_ARG, "null store");
-    if (!s->job.valid) return fail(PK_ERR_STATE, "pk_fullscan_prepare has not been called");
+    TRY(job_ok(s));
     if (s->job.nq == 0 || s->job.k == 0) return PK_OK;
     if (!d_keys) return fail(PK_ERR_ARG, "null d_keys");
     CK(cudaMemcpyAsync(d_keys, s->job.keys_b.p, (size_t)s->job.nq * s->job.k * 8, cudaMemcpyDeviceToDevice, s->stream));
@@ -2246,9 +2339,7 @@ int pk_merge_keys(pk_store* s, const uint64_t* d_keys, int n_lists, int nq, int 
     MergeParams M;
     memset(&M, 0, sizeof(M));
     M.keys = d_keys; M.n_lists = n_lists; M.nq = nq; M.K = k; M.stride_k = k; M.out_keys = s->d_keys_c.p;
-    merge_topk_kernel<<<nq, 128, 0, s->stream>>>(M);
-    ++s->stat_launches;
-    CK(cudaGetLastError());
+    TRY(launch_merge(s, M, nq));
     if (device_only) return PK_OK;
     std::vector<uint64_t> keys((size_t)nq * k);
     CK(cudaMemcpyAsync(keys.data(), s->d_keys_c.p, keys.size() * 8, cudaMemcpyDeviceToHost, s->stream));
@@ -2261,7 +2352,7 @@ int pk_merge_keys(pk_store* s, const uint64_t* d_keys, int n_lists, int nq, int 
 int pk_recommend(pk_store* s, int mode, int nq, const int32_t* q_uid, int k, int limit, int32_t* out_id, float* out_score,
                  int32_t* out_cnt) {
     TRY(ensure_ready(s));
-    TRY(check_topk_args(s, nq, q_uid, k));
+    TRY(check_topk_args(s, nq, q_uid, k, kMaxListK));
     if (nq > 0 && (!out_cnt || (k > 0 && (!out_id || !out_score)))) return fail(PK_ERR_ARG, "null output");
     if (mode != PK_MODE_GRAPH && mode != PK_MODE_COLLAB && mode != PK_MODE_CLUBS) return fail(PK_ERR_ARG, "bad mode %d", mode);
     if (nq == 0) return PK_OK;
@@ -2387,6 +2478,7 @@ struct WorldFileHeader {
     int32_t n_users, n_text_cols, n_adj_rows, n_sections;
     uint64_t file_bytes;
     uint64_t off[kWorldSections], bytes[kWorldSections];
+    uint64_t payload_sum;                  // hash of the section contents (payload_hash), verified by pk_world_open
     uint64_t header_sum;                   // FNV-1a of everything above
 };
 uint64_t fnv1a(const void* p, size_t n) {
@@ -2396,6 +2488,30 @@ uint64_t fnv1a(const void* p, size_t n) {
     return h;
 }
 struct Section { const void* p; uint64_t bytes; };
+// content hash of a section: four interleaved multiply-xor lanes over 8-byte words (memory speed, ~1 s for the
+// 3 GB of a 1.63 M-user world), the tail bytes folded in last
+uint64_t hash_bytes(const void* p, uint64_t n) {
+    const unsigned char* b = (const unsigned char*)p;
+    uint64_t h[4] = {0x9E3779B97F4A7C15ull, 0xC2B2AE3D27D4EB4Full, 0x165667B19E3779F9ull, 0x27D4EB2F165667C5ull};
+    const uint64_t words = n / 8;
+    uint64_t i = 0;
+    for (; i + 4 <= words; i += 4)
+        for (int l = 0; l < 4; ++l) {
+            uint64_t w;
+            memcpy(&w, b + (i + l) * 8, 8);
+            h[l] = (h[l] ^ w) * 0x100000001B3ull;
+            h[l] ^= h[l] >> 29;
+        }
+    uint64_t r = h[0];
+    for (int l = 1; l < 4; ++l) r = (r ^ h[l]) * 0xFF51AFD7ED558CCDull;
+    for (uint64_t j = i * 8; j < n; ++j) { r ^= b[j]; r *= 0x100000001B3ull; }
+    return r ^ (r >> 32) ^ n;
+}
+uint64_t payload_hash(const Section* sec) {
+    uint64_t r = 0xCBF29CE484222325ull;
+    for (int i = 0; i < kWorldSections; ++i) r = (r ^ (sec[i].bytes ? hash_bytes(sec[i].p, sec[i].bytes) : (uint64_t)i)) * 0x100000001B3ull;
+    return r;
+}
 // element counts follow from the header ints and the last entries of the three offset arrays
 bool world_sections(const pk_world* w, Section* sec) {
     const int64_t n = w->n_users, T = w->n_text_cols, m = w->n_adj_rows, nf = PK_NUM_FIXED + T;
@@ -2432,11 +2548,12 @@ int pk_world_save(const pk_world* w, const char* path) {
     if (!world_sections(w, sec)) return fail(PK_ERR_ARG, "pk_world_save: inconsistent world (null array or negative size)");
     WorldFileHeader H;
     memset(&H, 0, sizeof(H));
-    H.magic = kWorldMagic; H.version = 1; H.endian_tag = 0x01020304u;
+    H.magic = kWorldMagic; H.version = 2; H.endian_tag = 0x01020304u;
     H.n_users = w->n_users; H.n_text_cols = w->n_text_cols; H.n_adj_rows = w->n_adj_rows; H.n_sections = kWorldSections;
     uint64_t off = (sizeof(H) + 63) & ~63ull;
     for (int i = 0; i < kWorldSections; ++i) { H.off[i] = off; H.bytes[i] = sec[i].bytes; off = (off + sec[i].bytes + 63) & ~63ull; }
     H.file_bytes = off;
+    H.payload_sum = payload_hash(sec);
     H.header_sum = fnv1a(&H, offsetof(WorldFileHeader, header_sum));
     const std::string tmp = std::string(path) + ".tmp";
     FILE* f = fopen(tmp.c_str(), "wb");
@@ -2467,7 +2584,7 @@ int pk_world_open(const char* path, pk_world_file** out, pk_world* view) {
     const WorldFileHeader& H = *reinterpret_cast<const WorldFileHeader*>(map);
     const char* why = nullptr;
     if (H.magic != kWorldMagic) why = "bad magic";
-    else if (H.version != 1 || H.n_sections != kWorldSections) why = "unsupported version";
+    else if (H.version != 2 || H.n_sections != kWorldSections) why = "unsupported version";
     else if (H.endian_tag != 0x01020304u) why = "written on a machine of the other byte order";
     else if (H.header_sum != fnv1a(&H, offsetof(WorldFileHeader, header_sum))) why = "header checksum mismatch";
     else if (H.file_bytes != (uint64_t)st.st_size) why = "truncated (size differs from the header)";
@@ -2499,6 +2616,9 @@ int pk_world_open(const char* path, pk_world_file** out, pk_world* view) {
             Section sec[kWorldSections];
             if (!world_sections(&w, sec)) why = "inconsistent arrays";
             else for (int i = 0; i < kWorldSections; ++i) if (sec[i].bytes != H.bytes[i]) { why = "array size differs from its offsets"; break; }
+            // the contents themselves (POKEC_B200_WORLD_VERIFY=0 skips the pass for callers that trust the file)
+            const char* ev = getenv("POKEC_B200_WORLD_VERIFY");
+            if (!why && !(ev && ev[0] == '0') && payload_hash(sec) != H.payload_sum) why = "payload checksum mismatch (damaged contents)";
         }
     }
     if (why) { munmap(map, (size_t)st.st_size); return fail(PK_ERR_ARG, "pk_world_open: %s: %s", path, why); }

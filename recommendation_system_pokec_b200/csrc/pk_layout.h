@@ -41,7 +41,8 @@ constexpr int kHdrU4 = 5;
 constexpr int kMaxT = 64;
 constexpr int kTokBits = 26;            // token ids < 2^26
 constexpr int kLanes = 32;              // queries per group = lanes of a warp
-constexpr int kMaxK = 256;              // top-k list capacity limit (shared memory)
+constexpr int kMaxK = 256;              // top-k list capacity of the full scan's fused shared-memory lists
+constexpr int kMaxListK = 8192;         // top-k limit of the list modes (sort-based selection, pk_scan.cuh merge_topk_kernel)
 constexpr int kNumFixed = 7;
 constexpr int kMaxFields = kNumFixed + kMaxT;
 

@@ -458,6 +458,11 @@ __global__ void shortlist_check_kernel(const CheckParams P) {
     if (g < 0) return;
     const uint64_t* keys = P.short_keys + (size_t)q * P.Ks;
     int32_t* rows = P.cand_rows + ((size_t)g * 32 + P.q_lane[q]) * P.Ks;
+    if (keys[0] == kPoisonKey) {          // some rank could not build this group's fp32 tables (MergeParams): nothing is proven
+        for (int i = threadIdx.x; i < P.Ks; i += blockDim.x) rows[i] = -1;
+        if (threadIdx.x == 0) { P.q_flag[q] = 1; atomicOr(P.group_flag + g, 1); }
+        return;
+    }
     // only candidates whose approximate score can still reach the exact top-k (approx >= a_k - 2 margin) are re-scored
     const float a_k0 = __uint_as_float(key_score_bits(keys[P.K - 1]));     // 0 when the list holds fewer than k entries
     const float keep_from = a_k0 - 2.0f * P.margin - 1e-7f;

@@ -561,18 +561,21 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
 }
 
 // ------------------------------------------------------------------------------------------------
-// merge: per query, the K best keys of n_lists sorted lists
+// merge / select: per query, the K best DISTINCT keys of a set of key segments (sorted or not)
 // ------------------------------------------------------------------------------------------------
 
 struct MergeParams {
-    const uint64_t* keys;       // list l of query q: keys + list_off[...] see below
-    // addressing mode A (scan output): list j of query q = keys + ((slot0[q] + j) * 32 + lane[q]) * stride_k
-    // addressing mode B (gathered):    list j of query q = keys + ((size_t)j * nq + q) * stride_k
-    const int32_t* slot0;       // mode A: first out_slot of the query's group (null = mode B)
+    const uint64_t* keys;
+    // addressing mode A (scan output): list j of query q = keys + ((slot0[q] + j) * 32 + lane[q]) * stride_k, K entries
+    // addressing mode B (gathered):    list j of query q = keys + ((size_t)j * nq + q) * stride_k, K entries
+    // addressing mode C (slice):       one unsorted segment keys[seg_begin[q] .. seg_begin[q + 1])
+    const int32_t* slot0;       // mode A: first out_slot of the query's group
     const int32_t* n_lists_q;   // mode A: number of lists of each query
     const int32_t* lane;        // mode A
+    const int32_t* seg_begin;   // mode C
     int n_lists;                // mode B
     int nq, K, stride_k;
+    int cap;                    // sort buffer capacity in keys (power of two, >= 2 K and >= kMergeThreads)
     uint64_t* out_keys;         // [nq][K], 0-padded
     // mode A, two-stage full scan: queries whose flag is set take their lists from the fallback pass instead
     const int32_t* q_flag;
@@ -580,68 +583,113 @@ struct MergeParams {
     const int32_t* alt_slot0;
     const int32_t* alt_n_lists_q;
     int alt_stride_k;
+    // pre-filter shortlists: a query whose group's fp32 tables could not be built on THIS rank gets the poison key
+    // ~0 in front of its list; it survives every later merge (it is the largest key), so every rank sees it and
+    // flags the query in shortlist_check_kernel -- the ranks' cuckoo builds need not fail alike
+    const int32_t* poison_group_fail;   // [group] (null = no poisoning)
+    const int32_t* q_group;
 };
 
-__global__ void __launch_bounds__(128) merge_topk_kernel(const MergeParams P) {
+constexpr int kMergeThreads = 256;
+constexpr uint64_t kPoisonKey = ~0ull;
+
+// One CTA per query.  The candidates are pulled through a shared-memory buffer in rounds: [running top-K | next
+// keys], bitonic sort (descending), duplicates dropped (the lists of a re-scored shortlist overlap: equal keys
+// are adjacent after the sort), first K kept.  ~log^2(cap)/2 compare-exchange steps per round instead of K
+// block-wide arg-max rounds with two barriers each.
+__global__ void __launch_bounds__(kMergeThreads) merge_topk_kernel(const MergeParams P) {
+    extern __shared__ uint64_t merge_sm[];
+    uint64_t* buf = merge_sm;               // [cap]
+    uint64_t* res = merge_sm + P.cap;       // [K]
+    __shared__ int wsum[kMergeThreads / 32];
     const int q = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const bool modeA = P.slot0 != nullptr;
+    const bool modeC = P.seg_begin != nullptr;
+    const bool modeA = !modeC && P.slot0 != nullptr;
     const bool alt = modeA && P.q_flag != nullptr && P.q_flag[q] != 0;
     const uint64_t* kbase = alt ? P.alt_keys : P.keys;
-    const int32_t* slot0 = alt ? P.alt_slot0 : P.slot0;
     const int stride = alt ? P.alt_stride_k : P.stride_k;
-    const int nl = modeA ? (alt ? P.alt_n_lists_q[q] : P.n_lists_q[q]) : P.n_lists;
-    __shared__ uint64_t wbest[4];
-    __shared__ int wown[4];
-    // thread t owns lists t, t+128, ...; head[] positions are kept in registers for up to 8 lists per thread
-    constexpr int kOwn = 8;
-    int head[kOwn];
-    #pragma unroll
-    for (int i = 0; i < kOwn; ++i) head[i] = 0;
-    auto list_ptr = [&](int j) -> const uint64_t* {
-        if (modeA) return kbase + ((size_t)(slot0[q] + j) * 32 + P.lane[q]) * stride;
-        return P.keys + ((size_t)j * P.nq + q) * P.stride_k;
+    const int K = P.K;
+    int64_t total;
+    const uint64_t* seg = nullptr;
+    size_t list0 = 0;
+    if (modeC) {
+        const int b = P.seg_begin[q];
+        seg = P.keys + b;
+        total = P.seg_begin[q + 1] - b;
+    } else if (modeA) {
+        const int nl = alt ? P.alt_n_lists_q[q] : P.n_lists_q[q];
+        list0 = ((size_t)(alt ? P.alt_slot0 : P.slot0)[q] * 32 + P.lane[q]) * stride;
+        total = (int64_t)nl * K;
+    } else {
+        total = (int64_t)P.n_lists * K;
+    }
+    auto fetch = [&](int64_t idx) -> uint64_t {
+        if (modeC) return seg[idx];
+        const int64_t j = idx / K;
+        const int i = (int)(idx - j * K);
+        if (modeA) return kbase[list0 + (size_t)j * 32 * stride + i];
+        return P.keys[((size_t)j * P.nq + q) * P.stride_k + i];
     };
-    // Keys are unique per (score, id) except across the slices of a re-scored shortlist, whose lanes' lists
-    // overlap: a key equal to the one just emitted is consumed without being emitted again.
-    uint64_t prev = 0ull;
-    for (int r = 0; r < P.K;) {
-        uint64_t best = 0ull;
-        int own = -1;
-        #pragma unroll
-        for (int i = 0; i < kOwn; ++i) {
-            const int j = tid + i * 128;
-            if (j < nl && head[i] < P.K) {
-                const uint64_t v = list_ptr(j)[head[i]];
-                if (v > best) { best = v; own = i; }
+
+    int have = 0;
+    for (int64_t base = 0; base < total;) {
+        const int64_t left_ = total - base, room_ = (int64_t)(P.cap - have);
+        const int take = (int)(left_ < room_ ? left_ : room_);
+        for (int i = tid; i < take; i += kMergeThreads) buf[have + i] = fetch(base + i);
+        const int n = have + take;
+        int n2 = kMergeThreads;
+        while (n2 < n) n2 <<= 1;
+        for (int i = n + tid; i < n2; i += kMergeThreads) buf[i] = 0ull;
+        __syncthreads();
+        // bitonic sort, descending.  Steps with j <= 16 exchange inside a warp's own 32 consecutive pair slots.
+        for (int k = 2; k <= n2; k <<= 1) {
+            for (int j = k >> 1; j > 0; j >>= 1) {
+                for (int t = tid; t < (n2 >> 1); t += kMergeThreads) {
+                    const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), l = i | j;
+                    const bool desc = (i & k) == 0;
+                    const uint64_t a = buf[i], b = buf[l];
+                    if ((a < b) == desc) { buf[i] = b; buf[l] = a; }
+                }
+                const int j_next = (j > 1) ? (j >> 1) : k;
+                if (j_next > 16) __syncthreads(); else __syncwarp();
             }
         }
-        // block arg-max
-        uint64_t b = best;
-        int src = tid;
-        for (int o = 16; o; o >>= 1) {
-            const uint64_t ob = __shfl_xor_sync(kFull, b, o);
-            const int os = __shfl_xor_sync(kFull, src, o);
-            if (ob > b || (ob == b && os < src)) { b = ob; src = os; }
-        }
-        if (lane == 0) { wbest[warp] = b; wown[warp] = src; }
         __syncthreads();
-        uint64_t gb = wbest[0];
-        int gs = wown[0];
-        for (int w2 = 1; w2 < 4; ++w2)
-            if (wbest[w2] > gb) { gb = wbest[w2]; gs = wown[w2]; }
-        if (tid == gs && gb != 0ull && own >= 0) {
-            #pragma unroll
-            for (int i = 0; i < kOwn; ++i)
-                if (i == own) ++head[i];
+        // drop zeros and duplicates, keep the first K (order-preserving compaction)
+        const int per = n2 / kMergeThreads, i0 = tid * per;
+        int cnt = 0;
+        for (int i = i0; i < i0 + per; ++i) {
+            const uint64_t v = buf[i];
+            cnt += (v != 0ull && (i == 0 || buf[i - 1] != v)) ? 1 : 0;
         }
-        const bool dup = gb != 0ull && gb == prev;
-        if (!dup) {
-            if (tid == 0) P.out_keys[(size_t)q * P.K + r] = gb;
-            prev = gb;
-            ++r;
+        int inc = cnt;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(kFull, inc, o);
+            if (lane >= o) inc += v;
         }
+        if (lane == 31) wsum[warp] = inc;
         __syncthreads();
+        int pos = inc - cnt, tot = 0;
+        for (int w2 = 0; w2 < kMergeThreads / 32; ++w2) { if (w2 < warp) pos += wsum[w2]; tot += wsum[w2]; }
+        for (int i = i0; i < i0 + per && pos < K; ++i) {
+            const uint64_t v = buf[i];
+            if (v != 0ull && (i == 0 || buf[i - 1] != v)) res[pos++] = v;
+        }
+        have = min(tot, K);
+        base += take;
+        __syncthreads();
+        if (base < total)
+            for (int i = tid; i < have; i += kMergeThreads) buf[i] = res[i];
+        __syncthreads();
+    }
+    const bool poison = P.poison_group_fail != nullptr && P.q_group[q] >= 0 && P.poison_group_fail[P.q_group[q]] != 0;
+    uint64_t* out = P.out_keys + (size_t)q * K;
+    for (int i = tid; i < K; i += kMergeThreads) {
+        uint64_t v = 0ull;
+        if (poison) v = (i == 0) ? kPoisonKey : ((i - 1 < have) ? res[i - 1] : 0ull);
+        else if (i < have) v = res[i];
+        out[i] = v;
     }
 }
 
@@ -679,40 +727,6 @@ __global__ void collab_reduce_kernel(const CollabReduceParams P) {
             score = __dadd_rn(score, __dmul_rn((double)w, (double)sfc));
         }
         P.out_keys[c] = make_key(__float_as_uint((float)score), P.cand_uid[c]);
-    }
-}
-
-// top-k of a flat key slice per user (collaborative / clubs epilogue): one CTA per user, repeated
-// block-wide max extraction.  Slices are short (<= candidate_limit).
-__global__ void __launch_bounds__(256) slice_topk_kernel(uint64_t* keys, const int32_t* begin, int K, uint64_t* out_keys) {
-    const int u = blockIdx.x;
-    const int b = begin[u], e = begin[u + 1];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    __shared__ uint64_t wb[8];
-    __shared__ int wi[8];
-    for (int r = 0; r < K; ++r) {
-        uint64_t best = 0ull;
-        int bi = -1;
-        for (int i = b + tid; i < e; i += 256) {
-            const uint64_t v = keys[i];
-            if (v > best) { best = v; bi = i; }
-        }
-        for (int o = 16; o; o >>= 1) {
-            const uint64_t ob = __shfl_xor_sync(kFull, best, o);
-            const int oi = __shfl_xor_sync(kFull, bi, o);
-            if (ob > best) { best = ob; bi = oi; }
-        }
-        if (lane == 0) { wb[warp] = best; wi[warp] = bi; }
-        __syncthreads();
-        if (tid == 0) {
-            uint64_t gb = 0ull;
-            int gi = -1;
-            for (int w2 = 0; w2 < 8; ++w2)
-                if (wb[w2] > gb) { gb = wb[w2]; gi = wi[w2]; }
-            out_keys[(size_t)u * K + r] = gb;
-            if (gi >= 0) keys[gi] = 0ull;
-        }
-        __syncthreads();
     }
 }
 

@@ -164,7 +164,10 @@ def test_world_file_round_trip_and_rejects_damage(tmp_path):
         assert a.dtype == b.dtype and a.shape == b.shape and np.array_equal(a, b), name
     blob = open(path, "rb").read()
     cases = {"short": blob[:100], "truncated": blob[:-64], "magic": b"X" + blob[1:],
-             "header": blob[:40] + bytes([blob[40] ^ 1]) + blob[41:], "empty": b""}
+             "header": blob[:40] + bytes([blob[40] ^ 1]) + blob[41:], "empty": b"",
+             # one flipped bit deep inside the payload (the last section with content), header untouched
+             "payload": blob[:len(blob) - 100] + bytes([blob[len(blob) - 100] ^ 4]) + blob[len(blob) - 99:],
+             "payload_mid": blob[:len(blob) // 2] + bytes([blob[len(blob) // 2] ^ 0x80]) + blob[len(blob) // 2 + 1:]}
     for tag, data in cases.items():
         bad = str(tmp_path / f"{tag}.pkw")
         open(bad, "wb").write(data)
@@ -205,3 +208,37 @@ def test_world_file_round_trip_through_reference_containers(tmp_path):
     assert np.array_equal(back.uid, w.uid[order]) and np.array_equal(back.age, w.age[order])
     assert np.array_equal(back.norm_mean, w.norm_mean) and np.array_equal(back.norm_has, w.norm_has)
     o.close()
+
+
+def test_restatement_vs_reference_on_edge_case_worlds(oracle_libs):
+    """the worlds of tests/test_edge_cases_gpu.py (friends without profiles, duplicated ids inside clubs / friends /
+    adjacency rows): the CPU restatement must agree with the compiled reference there too, because the GPU box may
+    only have the restatement to check the CUDA path against"""
+    from oracle.oracle import CpuOracle, reference_available
+    if not reference_available():
+        pytest.skip("oracle/_ref/libpokec_ref.so not present")
+    from tests.test_edge_cases_gpu import ghost_friend_world, duplicate_world
+    from recommendation_system_pokec_b200.cabi import MODE_GRAPH, MODE_COLLAB, MODE_CLUBS
+    from recommendation_system_pokec_b200.synth import sample_queries
+    w, a, b = ghost_friend_world()
+    port, ref = CpuOracle(w, "port"), CpuOracle(w, "reference")
+    q = np.concatenate([[a, b], sample_queries(w, 20, seed=2)]).astype(np.int32)
+    for mode in (MODE_GRAPH, MODE_COLLAB, MODE_CLUBS):
+        for x, y in zip(port.recommend(mode, q, 20, 5000, 4), ref.recommend(mode, q, 20, 5000, 4)):
+            assert np.array_equal(x, y), f"ghost world, mode {mode}"
+    one = ref.recommend(MODE_COLLAB, np.array([a], np.int32), 20, 5000)
+    assert one[2][0] == 20 and (one[1][0] == 0).all()
+    port.close(); ref.close()
+    w, rows = duplicate_world()
+    port, ref = CpuOracle(w, "port"), CpuOracle(w, "reference")
+    rng = np.random.default_rng(5)
+    a = np.concatenate([w.uid[rows], w.uid[rng.integers(0, w.n, len(rows))]]).astype(np.int32)
+    b = np.concatenate([w.uid[rng.integers(0, w.n, len(rows))], w.uid[rows]]).astype(np.int32)
+    assert np.array_equal(port.pair_fields(a, b, 4).view(np.int32), ref.pair_fields(a, b, 4).view(np.int32))
+    q = np.concatenate([w.uid[rows[:20]], sample_queries(w, 12, seed=6)]).astype(np.int32)
+    for mode in (MODE_GRAPH, MODE_COLLAB, MODE_CLUBS):
+        for x, y in zip(port.recommend(mode, q, 30, 5000, 4), ref.recommend(mode, q, 30, 5000, 4)):
+            assert np.array_equal(x, y), f"duplicate world, mode {mode}"
+    for x, y in zip(port.fullscan(q, 30, 2, 4), ref.fullscan(q, 30, 2, 4)):
+        assert np.array_equal(x, y)
+    port.close(); ref.close()
