@@ -31,7 +31,7 @@ enum {
     PK_OK = 0,
     PK_ERR_ARG = -1,         /* bad argument (null pointer, negative size, ...) */
     PK_ERR_CUDA = -2,        /* CUDA runtime failure or no device */
-    PK_ERR_UNSUPPORTED = -3, /* outside the supported envelope (T > 64, token id >= 2^26, k > 256) */
+    PK_ERR_UNSUPPORTED = -3, /* outside the supported envelope (T > 64, token id >= 2^26, full-scan k > 256, list-mode k > 8192) */
     PK_ERR_STATE = -4        /* call order (no world loaded, ...) */
 };
 
@@ -211,7 +211,9 @@ enum {
     PK_STAT_SHARD_LEAN_BYTES = 12, /* bytes of the lean fp32 records inside the candidate shard */
     PK_STAT_SHORTLIST = 13,        /* shortlist length Ks of the prepared full scan (0 = no pre-filter) */
     PK_STAT_MARGIN_E9 = 14,        /* the pre-filter's error bound on a FAS value, times 1e9 */
-    PK_STAT_EDGE_CACHE = 15        /* adjacency entries held by a valid per-edge FAS cache (0 = none) */
+    PK_STAT_EDGE_CACHE = 15,       /* adjacency entries held by a valid per-edge FAS cache (0 = none) */
+    PK_STAT_PREP_NS = 16,          /* device time of the query-table build of the last two-stage full scan */
+    PK_STAT_MERGE_NS = 17          /* device time of its merge / proof kernels (instances, gathered shortlists, final) */
 };
 int64_t pk_stat(pk_store* s, int which);
 

@@ -199,6 +199,11 @@ struct pk_store {
     int64_t stat_fallback = 0, stat_prefilter_ns = 0, stat_rescore_ns = 0;
     bool rescore_time_pending = false;
     cudaEvent_t ev2 = nullptr, ev3 = nullptr;
+    // phase marks of the two-stage scan (per-step breakdown of bench.py): start, after the table build, after the
+    // shortlist merge | start of the second half, after gather-merge + proof, after the final merge
+    cudaEvent_t pev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool phase_pending = false;
+    int64_t stat_prep_ns = 0, stat_merge_ns = 0;
 
     // ---- per-call scratch (grow-only) -------------------------------------------------------------
     DevBuf<GroupDesc> d_groups;
@@ -652,6 +657,16 @@ int collect_scan_time(pk_store* s) {
         CK(cudaEventElapsedTime(&ms, s->ev2, s->ev3));
         s->stat_rescore_ns = (int64_t)((double)ms * 1e6);
         s->rescore_time_pending = false;
+        if (s->phase_pending) {
+            float a = 0.f, b = 0.f, c = 0.f, d = 0.f;
+            CK(cudaEventElapsedTime(&a, s->pev[0], s->pev[1]));      // arena clear + group_prep_kernel
+            CK(cudaEventElapsedTime(&b, s->ev1, s->pev[2]));         // merge of the instances' shortlists
+            CK(cudaEventElapsedTime(&c, s->pev[3], s->ev2));         // merge of the gathered shortlists + proof
+            CK(cudaEventElapsedTime(&d, s->ev3, s->pev[5]));         // final merge
+            s->stat_prep_ns = (int64_t)((double)a * 1e6);
+            s->stat_merge_ns = (int64_t)(((double)b + c + d) * 1e6);
+            s->phase_pending = false;
+        }
     }
     return PK_OK;
 }
@@ -1002,6 +1017,7 @@ int fullscan_shortlists(pk_store* s) {
     s->stat_pairs = J.pairs; s->stat_groups = J.n_groups;
     CK(cudaMemsetAsync(J.keys_b.p, 0, (size_t)std::max(J.nq, 1) * J.K * 8, s->stream));
     if (J.n_groups == 0) return PK_OK;
+    if (J.lean) CK(cudaEventRecord(s->pev[0], s->stream));
     CK(cudaMemsetAsync(J.arena.p, 0, std::max<uint64_t>(J.arena_bytes, 16), s->stream));
     PrepParams PP;
     PP.rec = s->d_rec.p; PP.rec_off = s->d_rec_off.p; PP.groups = J.groups.p; PP.arena = J.arena.p;
@@ -1045,6 +1061,7 @@ int fullscan_shortlists(pk_store* s) {
     Q.n_dyn = J.n_dyn; Q.max_inst = J.n_slices;
     Q.cand_begin = (int)J.cand_begin; Q.cand_end = (int)J.cand_end;
     const size_t pre_grid = std::min<size_t>((size_t)J.sm_count, J.n_pre);     // one persistent CTA per SM
+    CK(cudaEventRecord(s->pev[1], s->stream));
     CK(cudaEventRecord(s->ev0, s->stream));
     TRY(launch_prefilter(s, Q, pre_grid, J.max_smem_lean, Ks, false));
     CK(cudaEventRecord(s->ev1, s->stream));
@@ -1055,7 +1072,9 @@ int fullscan_shortlists(pk_store* s) {
     MS.keys = J.keys_pre.p; MS.slot0 = J.pre_slot0.p; MS.n_lists_q = J.pre_nl.p; MS.lane = J.q_lane.p;
     MS.nq = J.nq; MS.K = Ks; MS.stride_k = Ks; MS.out_keys = J.keys_short.p;
     MS.poison_group_fail = J.lean_fail.p; MS.q_group = J.q_group.p;
-    return launch_merge(s, MS, J.nq);
+    TRY(launch_merge(s, MS, J.nq));
+    CK(cudaEventRecord(s->pev[2], s->stream));
+    return PK_OK;
 }
 
 // Second half of the two-stage scan: proof, exact re-score, fallback, final merge.  With shortlists gathered from
@@ -1070,6 +1089,7 @@ int fullscan_finish(pk_store* s, const uint64_t* d_all_short, int n_lists, int r
     if (J.n_groups == 0 || !J.lean) return PK_OK;       // the exact scan of the first half already produced the keys
     const int Ks = J.Ks;
     const uint64_t* short_keys = J.keys_short.p;
+    CK(cudaEventRecord(s->pev[3], s->stream));
     if (d_all_short) {
         TRY(J.keys_short_all.reserve((size_t)J.nq * Ks));
         MergeParams MG;
@@ -1108,7 +1128,10 @@ int fullscan_finish(pk_store* s, const uint64_t* d_all_short, int n_lists, int r
     // 5. final merge: the re-scored shortlist, or the full exact scan where the shortlist was not proven
     M.keys = J.keys_rr.p; M.slot0 = J.rr_slot0.p; M.n_lists_q = J.rr_nl.p; M.stride_k = J.Kp;
     M.q_flag = J.q_flag.p; M.alt_keys = J.keys_a.p; M.alt_slot0 = J.q_slot0.p; M.alt_n_lists_q = J.q_nl.p; M.alt_stride_k = J.Kp;
-    return launch_merge(s, M, J.nq);
+    TRY(launch_merge(s, M, J.nq));
+    CK(cudaEventRecord(s->pev[5], s->stream));
+    s->phase_pending = J.n_pre > 0;
+    return PK_OK;
 }
 
 int fullscan_execute(pk_store* s) {
@@ -1858,6 +1881,7 @@ int pk_store_create(int device, pk_store** out) {
     if (e == cudaSuccess) e = cudaEventCreate(&s->ev1);
     if (e == cudaSuccess) e = cudaEventCreate(&s->ev2);
     if (e == cudaSuccess) e = cudaEventCreate(&s->ev3);
+    for (int i = 0; i < 6 && e == cudaSuccess; ++i) e = cudaEventCreate(&s->pev[i]);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&s->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
     if (e != cudaSuccess) { delete s; return fail(PK_ERR_CUDA, "store init: %s", cudaGetErrorString(e)); }
     *out = s;
@@ -1872,6 +1896,7 @@ void pk_store_destroy(pk_store* s) {
     if (s->ev1) cudaEventDestroy(s->ev1);
     if (s->ev2) cudaEventDestroy(s->ev2);
     if (s->ev3) cudaEventDestroy(s->ev3);
+    for (int i = 0; i < 6; ++i) if (s->pev[i]) cudaEventDestroy(s->pev[i]);
     cudaStream_t st = s->stream;
     delete s;
     if (st) cudaStreamDestroy(st);
@@ -2461,6 +2486,8 @@ int64_t pk_stat(pk_store* s, int which) {
         case PK_STAT_SHORTLIST: return s->job.valid && s->job.lean ? s->job.Ks : 0;
         case PK_STAT_MARGIN_E9: return (int64_t)((double)s->margin * 1e9);
         case PK_STAT_EDGE_CACHE: return s->edge_cache_valid ? (int64_t)s->h_edge_fas.size() : 0;
+        case PK_STAT_PREP_NS: return s->stat_prep_ns;
+        case PK_STAT_MERGE_NS: return s->stat_merge_ns;
         default: return -1;
     }
 }

@@ -30,7 +30,7 @@ ABI_SYMBOLS = (
 )
 STAT_KERNEL_LAUNCHES, STAT_PAIRS_SCORED, STAT_STORE_BYTES, STAT_SCAN_KERNEL_NS, STAT_SCAN_LAUNCHES, STAT_GROUPS, \
     STAT_SHARD_RECORD_BYTES, STAT_H2D_BYTES, STAT_D2H_BYTES, STAT_PREFILTER, STAT_FALLBACK_QUERIES, STAT_RESCORE_NS, \
-    STAT_SHARD_LEAN_BYTES, STAT_SHORTLIST, STAT_MARGIN_E9, STAT_EDGE_CACHE = range(16)
+    STAT_SHARD_LEAN_BYTES, STAT_SHORTLIST, STAT_MARGIN_E9, STAT_EDGE_CACHE, STAT_PREP_NS, STAT_MERGE_NS = range(18)
 
 _lib = None
 

@@ -253,3 +253,40 @@ def sample_queries(world: World, q, seed):
     rng = np.random.default_rng(seed)
     idx = rng.choice(world.n, size=min(q, world.n), replace=False)
     return world.uid[np.sort(idx)].astype(np.int32)
+
+
+def normalizer_pair_sample(world: World, sample_size=100_000, comps_per_user=5, seed=12345):
+    """The pair sample of the reference's compute_column_normalizers(profiles, cols, sample_size, comps_per_user)
+    (src/utils.cpp:163-181): sample_size * comps_per_user DISTINCT unordered pairs (a != b) of users drawn uniformly
+    with an MT19937 stream seeded 12345, at most 10 attempts per wanted pair.  The reference indexes its
+    unordered_map's iteration order, which only its own C++ side can reproduce; here the users are indexed in
+    world order, so the sample has the same distribution, not the same pairs.  Returns (a_uid, b_uid) in draw order
+    -- the input of pk_normalizers_from_pairs."""
+    n = world.n
+    need = int(sample_size) * int(comps_per_user)
+    need = min(need, n * (n - 1) // 2)
+    rs = np.random.RandomState(seed)              # MT19937, like std::mt19937
+    a_out, b_out = [], []
+    seen = np.zeros(0, np.int64)
+    have, attempts = 0, 0
+    while have < need and attempts < need * 10:
+        m = int((need - have) * 1.05) + 16
+        a = rs.randint(0, n, m)
+        b = rs.randint(0, n, m)
+        attempts += m
+        ok = a != b
+        a, b = a[ok], b[ok]
+        key = np.minimum(a, b).astype(np.int64) * n + np.maximum(a, b)
+        _, first = np.unique(key, return_index=True)          # distinct inside the draw, first occurrence kept
+        first.sort()
+        a, b, key = a[first], b[first], key[first]
+        if seen.size:
+            new = ~np.isin(key, seen)
+            a, b, key = a[new], b[new], key[new]
+        take = min(len(a), need - have)
+        a_out.append(a[:take]); b_out.append(b[:take])
+        seen = np.concatenate([seen, key[:take]])
+        have += take
+    a = np.concatenate(a_out) if a_out else np.zeros(0, np.int64)
+    b = np.concatenate(b_out) if b_out else np.zeros(0, np.int64)
+    return world.uid[a].astype(np.int32), world.uid[b].astype(np.int32)

@@ -28,32 +28,24 @@ from recommendation_system_pokec_b200.cabi import EXCLUDE_SELF_AND_ADJ  # noqa: 
 from recommendation_system_pokec_b200.sharding import shard_rows  # noqa: E402
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--users", type=int, default=POKEC_N)
-    ap.add_argument("--batch", type=int, default=4096)
-    ap.add_argument("--batches", type=int, default=16)
-    ap.add_argument("--topk", type=int, default=50)
-    ap.add_argument("--depth", type=int, default=2, help="batches in flight (stores on the GPU); 1 = no overlap")
-    args = ap.parse_args()
-    fd = os.dup(1)
-    os.dup2(2, 1)                      # NCCL prints its banner on stdout
-    rank = int(os.environ.get("RANK", "0"))
-    ws = int(os.environ.get("WORLD_SIZE", "1"))
-    lr = int(os.environ.get("LOCAL_RANK", "0"))
+def sweep(w, ws, rank, lr, B, k, n_batches, depth=2, keep_batches=()):
+    """`n_batches` consecutive batches of B distinct query users (walked in uid order) through the end-to-end calls --
+    host uids in, host top-k out, host planning + H2D, both all-gathers and the merge every batch.  `depth` stores on the
+    same GPU take the batches in turn, each on its own stream: the host planning and H2D of batch i + 1 overlap the
+    kernels of batch i, and its all-gather overlaps the next scan.  Returns (query-users/s, seconds,
+    [(uids, lists) of the batches named in keep_batches]); timed with a barrier + synchronize on both sides, max over
+    ranks."""
     import torch
     import torch.distributed as dist
-    from recommendation_system_pokec_b200.engine import DeviceRecommender
-    torch.cuda.set_device(lr)
-    if ws > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
-    from bench import build_world          # the bench world (cached on disk between invocations and ranks)
-    w = build_world(args.users)
-    # `depth` stores on the same GPU take the batches in turn, each on its own stream: the host planning and H2D of
-    # batch i + 1 overlap the kernels of batch i, and its all-gather overlaps the next scan
-    lo, hi = shard_rows(w.n, rank, ws)
-    k, B = args.topk, args.batch
     from recommendation_system_pokec_b200 import engine
+    from recommendation_system_pokec_b200.engine import DeviceRecommender
+    lo, hi = shard_rows(w.n, rank, ws)
+
+    def batch_uids(b):
+        q = w.uid[(b * B) % w.n:(b * B) % w.n + B].astype(np.int32)
+        if len(q) < B:
+            q = np.concatenate([q, w.uid[:B - len(q)].astype(np.int32)])
+        return q
 
     class Slot:
         def __init__(self):
@@ -63,14 +55,12 @@ def main():
             self.local = torch.zeros((B, k), dtype=torch.int64, device=f"cuda:{lr}")
             self.gathered = torch.zeros((ws, B, k), dtype=torch.int64, device=f"cuda:{lr}")
             self.short = None
-            self.pending = False
+            self.pending = None
 
         def launch(self, b):
             """everything of batch b up to (not including) the fetch: asynchronous on this slot's stream"""
             dev = self.dev
-            q = w.uid[(b * B) % w.n:(b * B) % w.n + B].astype(np.int32)
-            if len(q) < B:
-                q = np.concatenate([q, w.uid[:B - len(q)].astype(np.int32)])
+            q = batch_uids(b)
             dev.fullscan_prepare(q, k, EXCLUDE_SELF_AND_ADJ)
             ks = dev.stat(engine.STAT_SHORTLIST)
             if ws > 1 and ks > 0:      # shared exact re-score (DESIGN.md section 7)
@@ -89,60 +79,94 @@ def main():
                 dev.fullscan_keys(self.local.data_ptr())
                 with torch.cuda.stream(self.stream):
                     dist.all_gather_into_tensor(self.gathered.view(-1), self.local.view(-1))
-            self.pending = True
+            self.pending = b
 
         def fetch(self):
             """host top-k of the batch launched last on this slot (synchronises this slot's stream only)"""
-            self.pending = False
+            b, self.pending = self.pending, None
             if ws == 1:
-                return self.dev.fullscan_fetch()
-            return self.dev.merge_keys(self.gathered.data_ptr(), ws, B, k)
+                return b, self.dev.fullscan_fetch()
+            return b, self.dev.merge_keys(self.gathered.data_ptr(), ws, B, k)
 
-    slots = [Slot() for _ in range(max(1, args.depth))]
+    slots = [Slot() for _ in range(max(1, depth))]
     dev = slots[0].dev
+    kept = []
+    state = {"complete": True}
 
-    def run_window(b0, nb):
-        res = None
+    def take(b, res):
+        state["complete"] = state["complete"] and int(res[2].min()) == k
+        if b in keep_batches:
+            kept.append((batch_uids(b), res))
+
+    def run_window(b0, nb, record):
         for b in range(b0, b0 + nb):
             sl = slots[b % len(slots)]
-            if sl.pending:
-                res = sl.fetch()
+            if sl.pending is not None:
+                bb, res = sl.fetch()
+                if record:
+                    take(bb, res)
             sl.launch(b)
         for i in range(len(slots)):                # drain in launch order
             sl = slots[(b0 + nb + i) % len(slots)]
-            if sl.pending:
-                res = sl.fetch()
-        return res
+            if sl.pending is not None:
+                bb, res = sl.fetch()
+                if record:
+                    take(bb, res)
 
     def barrier():
-        dev.sync()
+        for sl in slots:
+            sl.dev.sync()
         torch.cuda.synchronize()
         if ws > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    run_window(0, len(slots))
+    run_window(n_batches, len(slots), False)       # warm-up on batches past the window (wrapping around)
     barrier()
     t = time.perf_counter()
-    res = run_window(len(slots), args.batches)
+    run_window(0, n_batches, True)
     barrier()
     dt = time.perf_counter() - t
     if ws > 1:
         tt = torch.tensor([dt], dtype=torch.float64, device=f"cuda:{lr}")
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dt = float(tt.item())
-    rate = args.batches * B / dt
+    for sl in slots:
+        sl.dev.close()
+    assert state["complete"], "a batch of the sweep returned incomplete top-k lists"
+    return n_batches * B / dt, dt, kept
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--users", type=int, default=POKEC_N)
+    ap.add_argument("--batch", type=int, default=4096)
+    ap.add_argument("--batches", type=int, default=16)
+    ap.add_argument("--topk", type=int, default=50)
+    ap.add_argument("--depth", type=int, default=2, help="batches in flight (stores on the GPU); 1 = no overlap")
+    args = ap.parse_args()
+    fd = os.dup(1)
+    os.dup2(2, 1)                      # NCCL prints its banner on stdout
+    rank = int(os.environ.get("RANK", "0"))
+    ws = int(os.environ.get("WORLD_SIZE", "1"))
+    lr = int(os.environ.get("LOCAL_RANK", "0"))
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(lr)
+    if ws > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+    from bench import build_world          # the bench world (cached on disk between invocations and ranks)
+    w = build_world(args.users)
+    rate, dt, _ = sweep(w, ws, rank, lr, args.batch, args.topk, args.batches, args.depth)
     if rank == 0:
-        out = {"workload": "all-users FAS top-50 (BASELINE configs[4])", "n_gpus": ws, "users": w.n, "batch": B,
-               "window_batches": args.batches, "batches_in_flight": len(slots), "query_users_per_s": rate, "ms_per_batch": dt / args.batches * 1e3,
-               "full_sweep_batches": -(-w.n // B), "full_sweep_seconds_extrapolated": w.n / rate,
-               "pairs_per_s": rate * w.n, "complete_lists": bool(int(res[2].min()) == k)}
+        out = {"workload": "all-users FAS top-50 (BASELINE configs[4])", "n_gpus": ws, "users": w.n, "batch": args.batch,
+               "window_batches": args.batches, "batches_in_flight": max(1, args.depth), "query_users_per_s": rate,
+               "ms_per_batch": dt / args.batches * 1e3, "full_sweep_batches": -(-w.n // args.batch),
+               "full_sweep_seconds_extrapolated": w.n / rate, "pairs_per_s": rate * w.n, "complete_lists": True}
         os.write(fd, (json.dumps(out) + "\n").encode())
     if ws > 1:
         dist.barrier()
         dist.destroy_process_group()
-    for sl in slots:
-        sl.dev.close()
     return 0
 
 
