@@ -31,6 +31,7 @@
 #include "pk_scan.cuh"
 #include "pk_prefilter.cuh"
 #include "pk_clubs.cuh"
+#include "pk_pairs.cuh"
 
 using namespace pk;
 
@@ -452,6 +453,14 @@ int rebuild_norm(pk_store* s) {
         const double rel_s = std::max(4.2e-6, ((double)s->max_cell + 6.0) * 5.9604645e-8);
         L.margin = (float)(2.0 * 2.0 * (worst * rel_s + 5e-6));
         L.dim_comp = N.dim_comp; L.dim_age = N.dim_age;
+        {   // sigma is monotone in s on [0, 1], so a field's largest contribution is at s = 0 or s = 1
+            auto up = [](double v) { return (float)(v * (1.0 + 4e-7) + 1e-7); };
+            double mt = 0.0;
+            for (int t = 0; t < T; ++t) mt = std::max(mt, std::max(N.sig0[kNumFixed + t], N.sig1[kNumFixed + t]));
+            L.ub_text = up(mt);
+            L.ub_clubs = up(std::max(N.sig0[5], N.sig1[5]));
+            L.ub_friends = up(std::max(N.sig0[6], N.sig1[6]));
+        }
         s->margin = L.margin;
         TRY(s->d_lnorm.reserve(1));
         CK(cudaMemcpyAsync(s->d_lnorm.p, &L, sizeof(L), cudaMemcpyHostToDevice, s->stream));
@@ -706,7 +715,7 @@ ScanParams base_scan_params(pk_store* s, int K) {
 
 uint32_t lean_fixed_smem(int Ks) {
     const uint32_t norm = (uint32_t)((sizeof(LeanNorm) + 15) & ~15u);
-    return norm + 32u * Ks * 8u + 32u * 8u + 32u * 4u + 16u + (uint32_t)kPreWarps * 32u * 16u;
+    return norm + 32u * Ks * 8u + 32u * 8u + 32u * 4u + 32u * 4u + 16u + (uint32_t)kPreWarps * 32u * 16u;
 }
 
 void finish_group(pk_store* s, Plan& plan, GroupDesc& g, const uint32_t* excl_n, int Kp, bool with_lean = false, int Ks = 0) {
@@ -938,7 +947,7 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
         }
         J.n_dyn = (int)dyn_groups.size();
         TRY(upload(s, J.dyn_groups, dyn_groups));
-        TRY(J.dyn_state.reserve(std::max<size_t>(2 * dyn_groups.size(), 1)));
+        TRY(J.dyn_state.reserve(std::max<size_t>(34 * dyn_groups.size(), 1)));     // cursor, instances, theta[32] per group
         // exact re-score items: the 32 x Ks shortlist rows of each group, in list mode
         int rr_splits = 4;      // measured: 8 splits (6.92 waves) cost 4.7 ms against 3.9 ms (table staging per CTA)
         if (const char* e = getenv("POKEC_B200_RR_SPLITS")) rr_splits = std::max(1, atoi(e));
@@ -1056,9 +1065,12 @@ int fullscan_shortlists(pk_store* s) {
     Q.Ks = Ks; Q.exclude_mode = J.exclude; Q.smem_arena_bytes = J.max_smem_lean; Q.out_keys = J.keys_pre.p;
     // shortlist instances a CTA never takes stay empty; cursors and instance counters start at 0
     CK(cudaMemsetAsync(J.keys_pre.p, 0, std::max<size_t>(J.n_pre, 1) * 32 * (size_t)Ks * 8, s->stream));
-    CK(cudaMemsetAsync(J.dyn_state.p, 0, std::max<size_t>(2 * (size_t)J.n_dyn, 1) * 4, s->stream));
+    CK(cudaMemsetAsync(J.dyn_state.p, 0, std::max<size_t>(34 * (size_t)J.n_dyn, 1) * 4, s->stream));
     Q.dyn_cursor = J.dyn_state.p; Q.dyn_ninst = J.dyn_state.p + J.n_dyn; Q.dyn_groups = J.dyn_groups.p;
     Q.n_dyn = J.n_dyn; Q.max_inst = J.n_slices;
+    Q.dyn_theta = reinterpret_cast<unsigned int*>(J.dyn_state.p + 2 * J.n_dyn);
+    Q.K = J.K;
+    Q.theta_drop = (getenv("POKEC_B200_NO_PRUNE") && getenv("POKEC_B200_NO_PRUNE")[0] == '1') ? 1e9f : 2.0f * s->margin + 1e-5f;
     Q.cand_begin = (int)J.cand_begin; Q.cand_end = (int)J.cand_end;
     const size_t pre_grid = std::min<size_t>((size_t)J.sm_count, J.n_pre);     // one persistent CTA per SM
     CK(cudaEventRecord(s->pev[1], s->stream));
@@ -1234,24 +1246,15 @@ GroupDesc empty_group() {
 }
 
 // ---- recommend: graph / interest ---------------------------------------------------------------------
-// store-mode scores of 1-lane groups ([candidate][32], lane 0) -> sort keys with the candidates' uids
-__global__ void keys_from_scores_kernel(const float* __restrict__ f, const int32_t* __restrict__ cand_rows,
-                                        const int32_t* __restrict__ uid, int64_t n, uint64_t* __restrict__ keys) {
-    const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= n) return;
-    keys[c] = make_key(__float_as_uint(f[c * 32]), uid[cand_rows[c]]);
-}
+// recommend_graph_registration == recommend_by_interest (src/recommender_graph.cpp:33-103,224-227): every
+// (query, candidate) of the batch is one pair of the lane-per-pair kernel, which also emits the sort keys; the
+// sort-based selection then takes each query's top-k from its slice (any k: src/test.cpp:75 passes |friends| / 5).
+template <bool FIELDS>
+int pairs_launch(pk_store* s, int64_t n, const int32_t* d_a_row, const int32_t* d_b_row, float* d_out_f, float* d_out_fields,
+                 const int32_t* d_key_id, uint64_t* d_out_keys);
 
 int recommend_graph(pk_store* s, int nq, const int32_t* q_uid, int k, int limit, uint64_t* h_keys) {
-    const int K = std::max(k, 1), Kp = (K + 31) / 32 * 32;
-    Plan plan;
-    std::vector<int32_t> cand_rows;
-    std::vector<WorkItem> items;
-    std::vector<int32_t> q_slot0(nq, 0), q_nl(nq, 0), q_lane(nq, 0);
-    // k beyond the fused shared-memory lists (the reference takes any topk, src/test.cpp:75 passes |friends| / 5):
-    // store-mode scan, then the sort-based selection over each query's slice
-    const bool wide = K > kMaxK;
-    std::vector<int32_t> q_begin((size_t)nq + 1, 0);
+    const int K = std::max(k, 1);
     // phase 1 (host threads): the candidate rows of every query, in the reference's order
     std::vector<std::vector<int32_t>> q_rows((size_t)nq);
     std::vector<int32_t> q_row((size_t)nq, -1);
@@ -1274,65 +1277,32 @@ int recommend_graph(pk_store* s, int nq, const int32_t* q_uid, int k, int limit,
             out.push_back(rc);
         }
     });
-    // phase 2: one single-lane group and one work item per query
-    for (int q = 0; q < nq; ++q) {
-        const int r = q_row[q];
-        q_begin[q] = q_begin[q + 1] = (int32_t)cand_rows.size();
-        if (r < 0 || q_rows[q].empty()) continue;
-        const int32_t c0 = (int32_t)cand_rows.size();
-        cand_rows.insert(cand_rows.end(), q_rows[q].begin(), q_rows[q].end());
-        const int32_t c1 = (int32_t)cand_rows.size();
-        GroupDesc g = empty_group();
-        g.n_lanes = 1; g.row[0] = r; g.qidx[0] = q;
-        WorkItem it;
-        it.group = (int32_t)plan.groups.size();
-        it.cand_begin = c0; it.cand_end = c1; it.out_slot = wide ? c0 : (int32_t)items.size();
-        q_begin[q + 1] = c1;
-        finish_group(s, plan, g, nullptr, wide ? 0 : Kp);
-        q_slot0[q] = it.out_slot; q_nl[q] = 1; q_lane[q] = 0;
-        items.push_back(it);
-        s->stat_pairs += c1 - c0;
-    }
-    s->stat_groups = (int64_t)plan.groups.size();
+    // phase 2: flat pair arrays, one slice per query
+    std::vector<int32_t> q_begin((size_t)nq + 1, 0);
+    for (int q = 0; q < nq; ++q) q_begin[q + 1] = q_begin[q] + (int32_t)q_rows[q].size();
+    const int64_t np = q_begin[nq];
+    if (np > 0x7fffff00ll) return fail(PK_ERR_UNSUPPORTED, "graph batch too large (split the batch)");
+    std::vector<int32_t> a_row((size_t)np), b_row((size_t)np), b_uid((size_t)np);
+    parallel_for(nq, [&](int q) {
+        int32_t o = q_begin[q];
+        for (int32_t rc : q_rows[q]) { a_row[(size_t)o] = q_row[q]; b_row[(size_t)o] = rc; b_uid[(size_t)o] = s->uid[(size_t)rc]; ++o; }
+    });
+    s->stat_pairs += np;
+    s->stat_groups = 0;
     std::vector<uint64_t> keys((size_t)std::max(nq, 1) * K, 0ull);
-    if (!items.empty() && wide) {
-        const int64_t nc = (int64_t)cand_rows.size();
-        TRY(upload_plan(s, plan, false));
-        TRY(upload(s, s->d_cand_rows, cand_rows));
-        TRY(s->d_f32a.reserve((size_t)nc * 32));
-        TRY(s->d_keys_a.reserve((size_t)nc));
+    if (np > 0) {
+        TRY(upload(s, s->d_i32a, a_row));
+        TRY(upload(s, s->d_i32b, b_row));
+        TRY(upload(s, s->d_i32c, b_uid));
+        TRY(upload(s, s->d_i32d, q_begin));
+        TRY(s->d_f32a.reserve((size_t)np));
+        TRY(s->d_keys_a.reserve((size_t)np));
         TRY(s->d_keys_b.reserve((size_t)nq * K));
-        ScanParams P = base_scan_params(s, K);
-        P.cand_rows = s->d_cand_rows.p;
-        P.out_f = s->d_f32a.p;
-        TRY((run_scan<EPI_STORE, false>(s, plan, P, items)));
-        keys_from_scores_kernel<<<(unsigned)((nc + 255) / 256), 256, 0, s->stream>>>(s->d_f32a.p, s->d_cand_rows.p, s->d_uid.p, nc,
-                                                                                    s->d_keys_a.p);
-        ++s->stat_launches;
-        CK(cudaGetLastError());
-        TRY(upload(s, s->d_i32a, q_begin));
-        TRY(launch_slice_topk(s, s->d_keys_a.p, s->d_i32a.p, nq, K, s->d_keys_b.p));
+        TRY((pairs_launch<false>(s, np, s->d_i32a.p, s->d_i32b.p, s->d_f32a.p, nullptr, s->d_i32c.p, s->d_keys_a.p)));
+        TRY(launch_slice_topk(s, s->d_keys_a.p, s->d_i32d.p, nq, K, s->d_keys_b.p));
         CK(cudaMemcpyAsync(keys.data(), s->d_keys_b.p, (size_t)nq * K * 8, cudaMemcpyDeviceToHost, s->stream));
         CK(cudaStreamSynchronize(s->stream));
-    } else if (!items.empty()) {
-        TRY(upload_plan(s, plan, false));
-        TRY(upload(s, s->d_cand_rows, cand_rows));
-        TRY(s->d_keys_a.reserve(items.size() * 32 * (size_t)Kp));
-        TRY(s->d_keys_b.reserve((size_t)nq * K));
-        ScanParams P = base_scan_params(s, K);
-        P.cand_rows = s->d_cand_rows.p;
-        P.out_keys = s->d_keys_a.p;
-        TRY((run_scan<EPI_TOPK, false>(s, plan, P, items)));
-        TRY(upload(s, s->d_i32a, q_slot0));
-        TRY(upload(s, s->d_i32b, q_nl));
-        TRY(upload(s, s->d_i32c, q_lane));
-        MergeParams M;
-        memset(&M, 0, sizeof(M));
-        M.keys = s->d_keys_a.p; M.slot0 = s->d_i32a.p; M.n_lists_q = s->d_i32b.p; M.lane = s->d_i32c.p;
-        M.nq = nq; M.K = K; M.stride_k = Kp; M.out_keys = s->d_keys_b.p;
-        TRY(launch_merge(s, M, nq));
-        CK(cudaMemcpyAsync(keys.data(), s->d_keys_b.p, (size_t)nq * K * 8, cudaMemcpyDeviceToHost, s->stream));
-        CK(cudaStreamSynchronize(s->stream));
+        TRY(collect_scan_time(s));
     }
     memcpy(h_keys, keys.data(), (size_t)nq * K * 8);
     return PK_OK;
@@ -1504,30 +1474,39 @@ int recommend_collab(pk_store* s, int nq, const int32_t* q_uid, int k, int limit
 // Both weights of recommend_clubs_collab are FAS values on adjacency edges -- w_f = FAS(u, f) for f in adj[u]
 // (src/recommender_clubs.cpp:23-28) and s = FAS(f, fof) for fof in adj[f] (:56) -- and do not depend on the query.
 // Scored once (the exact kernel, pairs mode), they turn the clubs call into edge enumeration + weighted scatter.
-template <bool FIELDS>
-int pairs_run(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid, std::vector<float>& out_f,
-              std::vector<float>& out_fields, std::vector<int64_t>& where);
-
 int edge_cache_build(pk_store* s) {
     TRY(ensure_ready(s));
     const int64_t E = (int64_t)s->adj.size();
-    std::vector<int32_t> src((size_t)E);
-    for (size_t r = 0; r < s->adj_uid.size(); ++r)
-        for (int64_t j = s->adj_ptr[r]; j < s->adj_ptr[r + 1]; ++j) src[(size_t)j] = s->adj_uid[r];
-    s->h_edge_fas.assign((size_t)E, -1.0f);
-    int64_t pairs = 0, scan_ns = 0;
-    for (int64_t p0 = 0; p0 < E; p0 += (1 << 20)) {                   // bounded [rows][32] score blocks
-        const int64_t m = std::min<int64_t>(1 << 20, E - p0);
-        std::vector<float> f, fields;
-        std::vector<int64_t> where;
-        TRY(pairs_run<false>(s, m, src.data() + p0, s->adj.data() + p0, f, fields, where));
+    // per adjacency entry: (row of the source, row of the neighbour), -1 = no profile -> the kernel stores -1
+    std::vector<int32_t> ra((size_t)E), rb((size_t)E);
+    const int m = (int)s->adj_uid.size();
+    std::atomic<int64_t> valid{0};
+    parallel_for((m + 255) / 256, [&](int blk) {
+        int64_t v = 0;
+        for (int r = blk * 256, e = std::min(m, (blk + 1) * 256); r < e; ++r) {
+            const int32_t src = s->row_of(s->adj_uid[(size_t)r]);
+            for (int64_t j = s->adj_ptr[(size_t)r]; j < s->adj_ptr[(size_t)r + 1]; ++j) {
+                ra[(size_t)j] = src;
+                rb[(size_t)j] = s->row_of(s->adj[(size_t)j]);
+                v += (src >= 0 && rb[(size_t)j] >= 0) ? 1 : 0;
+            }
+        }
+        valid += v;
+    });
+    TRY(s->d_edge_fas.reserve((size_t)std::max<int64_t>(E, 1)));
+    s->stat_scan_ns = 0; s->stat_scan_launches = 0;
+    const int64_t kBatch = 1 << 23;
+    for (int64_t p0 = 0; p0 < E; p0 += kBatch) {
+        const int64_t n = std::min(kBatch, E - p0);
+        TRY(upload(s, s->d_i32a, ra.data() + p0, (size_t)n));
+        TRY(upload(s, s->d_i32b, rb.data() + p0, (size_t)n));
+        TRY((pairs_launch<false>(s, n, s->d_i32a.p, s->d_i32b.p, s->d_edge_fas.p + p0, nullptr, nullptr, nullptr)));
+        CK(cudaStreamSynchronize(s->stream));
         TRY(collect_scan_time(s));
-        pairs += s->stat_pairs; scan_ns += s->stat_scan_ns;
-        for (int64_t i = 0; i < m; ++i)
-            if (where[(size_t)i] >= 0) s->h_edge_fas[(size_t)(p0 + i)] = f[(size_t)where[(size_t)i]];
     }
-    s->stat_pairs = pairs; s->stat_scan_ns = scan_ns;
-    TRY(upload(s, s->d_edge_fas, s->h_edge_fas));
+    s->stat_pairs = valid.load();
+    s->h_edge_fas.resize((size_t)E);
+    if (E > 0) CK(cudaMemcpyAsync(s->h_edge_fas.data(), s->d_edge_fas.p, (size_t)E * 4, cudaMemcpyDeviceToHost, s->stream));
     CK(cudaStreamSynchronize(s->stream));
     s->edge_cache_valid = true;
     return PK_OK;
@@ -1755,98 +1734,58 @@ int recommend_clubs(pk_store* s, int nq, const int32_t* q_uid, int k, uint64_t* 
 }
 
 // ---- pairs --------------------------------------------------------------------------------------------
-// groups of 32 distinct `a` rows x the union of their `b` rows; the wanted (a, b) entries are picked
-// from the [cand][32] block on the host.
-// The pair kernel scores a [candidate rows] x [32 lanes] block per group; a pair owns one entry of it.  Compact
-// the wanted entries on the device (one `width`-float record per pair) so that only they travel to the host.
-__global__ void gather_pairs_kernel(const float* __restrict__ src, const int64_t* __restrict__ idx, int64_t n, int width,
-                                    float* __restrict__ dst) {
-    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n * width) return;
-    const int64_t p = t / width;
-    const int j = (int)(t - p * width);
-    dst[t] = src[idx[p] * width + j];
+// one lane per pair (pk_pairs.cuh): a_row / b_row on the device, scores (and per-field floats) written in pair order
+template <bool FIELDS>
+int pairs_launch(pk_store* s, int64_t n, const int32_t* d_a_row, const int32_t* d_b_row, float* d_out_f, float* d_out_fields,
+                 const int32_t* d_key_id, uint64_t* d_out_keys) {
+    if (n <= 0) return PK_OK;
+    PairParams P;
+    memset(&P, 0, sizeof(P));
+    P.rec = s->d_rec.p; P.rec_off = s->d_rec_off.p; P.norm = s->d_norm.p; P.tab_comp = s->d_tab_comp.p; P.tab_age = s->d_tab_age.p;
+    P.a_row = d_a_row; P.b_row = d_b_row; P.n = n; P.T = s->T; P.nf = 3 + s->T + 2;
+    P.out_f = d_out_f; P.out_fields = d_out_fields; P.key_id = d_key_id; P.out_keys = d_out_keys;
+    CK(cudaEventRecord(s->ev0, s->stream));
+    fas_pairs_kernel<FIELDS><<<(unsigned)((n + 255) / 256), 256, 0, s->stream>>>(P);
+    CK(cudaEventRecord(s->ev1, s->stream));
+    CK(cudaGetLastError());
+    ++s->stat_launches; ++s->stat_scan_launches;
+    s->scan_time_pending = true;
+    return PK_OK;
 }
 
+// host pairs in, host results out: out_f[i] = FAS or -1 (a side without a profile); FIELDS: out_fields[i * nf + j]
 template <bool FIELDS>
 int pairs_run(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* b_uid, std::vector<float>& out_f,
-              std::vector<float>& out_fields, std::vector<int64_t>& where) {
+              std::vector<float>& out_fields) {
     s->stat_scan_ns = 0; s->stat_scan_launches = 0; s->stat_pairs = 0;
-    where.assign((size_t)n, -1);
     const int nf = 3 + s->T + 2;
-    // process in batches of pairs so that the outputs stay bounded
-    const int64_t kBatch = FIELDS ? 32768 : 1 << 20;
-    out_f.clear();
-    out_fields.clear();
-    std::vector<float> hf;
+    out_f.assign((size_t)n, -1.0f);
+    if (FIELDS) out_fields.assign((size_t)n * nf, -1.0f);
+    const int64_t kBatch = FIELDS ? (1 << 18) : (1 << 22);      // bounded device buffers
+    std::vector<int32_t> ra, rb;
     for (int64_t p0 = 0; p0 < n; p0 += kBatch) {
-        const int64_t p1 = std::min(n, p0 + kBatch);
-        Plan plan;
-        std::vector<WorkItem> items;
-        std::vector<int32_t> cand_rows;
-        int64_t rows = 0;
-        // pairs with both profiles, ordered by a
-        std::vector<std::pair<int32_t, int64_t>> order;   // (row a, pair index)
-        for (int64_t i = p0; i < p1; ++i) {
-            const int ra = s->row_of(a_uid[i]);
-            if (ra < 0 || s->row_of(b_uid[i]) < 0) continue;
-            order.emplace_back(ra, i);
-        }
-        std::sort(order.begin(), order.end());
-        size_t i = 0;
-        const int64_t base_out = FIELDS ? (int64_t)out_fields.size() / nf : (int64_t)out_f.size();
-        std::vector<int64_t> widx;                 // per pair of this batch (in `order`): its entry of the score block
-        widx.reserve(order.size());
-        while (i < order.size()) {
-            GroupDesc g = empty_group();
-            WorkItem it;
-            it.group = (int32_t)plan.groups.size();
-            it.cand_begin = (int32_t)cand_rows.size();
-            it.out_slot = (int32_t)rows;
-            int prev = -1;
-            while (i < order.size()) {
-                if (order[i].first != prev) {
-                    if (g.n_lanes == 32) break;
-                    g.row[g.n_lanes++] = order[i].first;
-                    prev = order[i].first;
-                }
-                const int rb = s->row_of(b_uid[order[i].second]);
-                where[order[i].second] = base_out + (int64_t)widx.size();
-                widx.push_back(((int64_t)rows + (int64_t)(cand_rows.size() - it.cand_begin)) * 32 + (g.n_lanes - 1));
-                cand_rows.push_back(rb);
-                ++i;
+        const int64_t m = std::min(kBatch, n - p0);
+        ra.resize((size_t)m); rb.resize((size_t)m);
+        std::atomic<int64_t> valid{0};
+        parallel_for((int)((m + 4095) / 4096), [&](int blk) {
+            int64_t v = 0;
+            for (int64_t i = (int64_t)blk * 4096, e = std::min(m, (int64_t)(blk + 1) * 4096); i < e; ++i) {
+                ra[(size_t)i] = s->row_of(a_uid[p0 + i]);
+                rb[(size_t)i] = s->row_of(b_uid[p0 + i]);
+                v += (ra[(size_t)i] >= 0 && rb[(size_t)i] >= 0) ? 1 : 0;
             }
-            it.cand_end = (int32_t)cand_rows.size();
-            rows += it.cand_end - it.cand_begin;
-            s->stat_pairs += (int64_t)g.n_lanes * (it.cand_end - it.cand_begin);
-            finish_group(s, plan, g, nullptr, 0);
-            items.push_back(it);
-        }
-        if (items.empty()) continue;
-        TRY(upload_plan(s, plan, false));
-        TRY(upload(s, s->d_cand_rows, cand_rows));
-        TRY(s->d_f32a.reserve((size_t)rows * 32));
-        ScanParams P = base_scan_params(s, 1);
-        P.cand_rows = s->d_cand_rows.p;
-        P.out_f = s->d_f32a.p;
-        if (FIELDS) {
-            TRY(s->d_fields.reserve((size_t)rows * 32 * nf));
-            P.out_fields = s->d_fields.p;
-        }
-        TRY((run_scan<EPI_STORE, FIELDS>(s, plan, P, items)));
-        const int64_t np = (int64_t)widx.size();
-        const int width = FIELDS ? nf : 1;
-        TRY(upload(s, s->d_i64a, widx));
-        TRY(s->d_f32b.reserve((size_t)np * width));
-        gather_pairs_kernel<<<(unsigned)((np * width + 255) / 256), 256, 0, s->stream>>>(
-            FIELDS ? s->d_fields.p : s->d_f32a.p, s->d_i64a.p, np, width, s->d_f32b.p);
-        ++s->stat_launches;
-        CK(cudaGetLastError());
-        std::vector<float>& dst = FIELDS ? out_fields : out_f;
-        const size_t o = dst.size();
-        dst.resize(o + (size_t)np * width);
-        CK(cudaMemcpyAsync(dst.data() + o, s->d_f32b.p, (size_t)np * width * 4, cudaMemcpyDeviceToHost, s->stream));
+            valid += v;
+        });
+        s->stat_pairs += valid.load();
+        TRY(upload(s, s->d_i32a, ra));
+        TRY(upload(s, s->d_i32b, rb));
+        TRY(s->d_f32a.reserve((size_t)m));
+        if (FIELDS) TRY(s->d_fields.reserve((size_t)m * nf));
+        TRY((pairs_launch<FIELDS>(s, m, s->d_i32a.p, s->d_i32b.p, s->d_f32a.p, FIELDS ? s->d_fields.p : nullptr, nullptr, nullptr)));
+        CK(cudaMemcpyAsync(out_f.data() + p0, s->d_f32a.p, (size_t)m * 4, cudaMemcpyDeviceToHost, s->stream));
+        if (FIELDS) CK(cudaMemcpyAsync(out_fields.data() + (size_t)p0 * nf, s->d_fields.p, (size_t)m * nf * 4, cudaMemcpyDeviceToHost, s->stream));
         CK(cudaStreamSynchronize(s->stream));
+        TRY(collect_scan_time(s));
     }
     return PK_OK;
 }
@@ -2005,7 +1944,18 @@ int pk_store_load_world(pk_store* s, const pk_world* w) {
     TRY(upload(s, s->d_clubs_ptr, n ? w->clubs_ptr : one.data(), (size_t)n + 1));
     TRY(upload(s, s->d_friends_ptr, n ? w->friends_ptr : one.data(), (size_t)n + 1));
     TRY(upload(s, s->d_tok_ptr, n ? w->tok_ptr : one.data(), (size_t)n * T + 1));
-    TRY(upload(s, s->d_clubs, w->clubs, (size_t)ncl)); TRY(upload(s, s->d_friends, w->friends, (size_t)nfr));
+    {   // the packed records keep every user's club / friend ids ASCENDING (duplicates kept): the similarity only
+        // counts members (src/recommender.cpp:119-128), and the lane-per-pair kernel merges the two lists
+        std::vector<uint32_t> cs(w->clubs, w->clubs + ncl), fs(w->friends, w->friends + nfr);
+        parallel_for((n + 1023) / 1024, [&](int blk) {
+            for (int r = blk * 1024, e = std::min(n, (blk + 1) * 1024); r < e; ++r) {
+                if (w->clubs_ptr[r + 1] - w->clubs_ptr[r] > 1) std::sort(cs.begin() + w->clubs_ptr[r], cs.begin() + w->clubs_ptr[r + 1]);
+                if (w->friends_ptr[r + 1] - w->friends_ptr[r] > 1) std::sort(fs.begin() + w->friends_ptr[r], fs.begin() + w->friends_ptr[r + 1]);
+            }
+        });
+        TRY(upload(s, s->d_clubs, cs.data(), (size_t)ncl)); TRY(upload(s, s->d_friends, fs.data(), (size_t)nfr));
+        CK(cudaStreamSynchronize(s->stream));       // cs / fs are locals
+    }
     TRY(upload(s, s->d_tok_id, tok_id, (size_t)nnz)); TRY(upload(s, s->d_tok_tf, tok_tf, (size_t)nnz));
     CK(cudaStreamSynchronize(s->stream));
 
@@ -2154,9 +2104,8 @@ int pk_pair_similarity(pk_store* s, int64_t n, const int32_t* a_uid, const int32
     TRY(ensure_ready(s));
     if (n < 0 || (n > 0 && (!a_uid || !b_uid || !out))) return fail(PK_ERR_ARG, "bad argument");
     std::vector<float> f, fields;
-    std::vector<int64_t> where;
-    TRY(pairs_run<false>(s, n, a_uid, b_uid, f, fields, where));
-    for (int64_t i = 0; i < n; ++i) out[i] = where[i] < 0 ? -1.0f : f[where[i]];
+    TRY(pairs_run<false>(s, n, a_uid, b_uid, f, fields));
+    if (n > 0) memcpy(out, f.data(), (size_t)n * 4);
     return PK_OK;
 }
 
@@ -2164,11 +2113,10 @@ int pk_pair_fields(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t* 
     TRY(ensure_ready(s));
     if (n < 0 || (n > 0 && (!a_uid || !b_uid || !out))) return fail(PK_ERR_ARG, "bad argument");
     std::vector<float> f, fields;
-    std::vector<int64_t> where;
-    TRY(pairs_run<true>(s, n, a_uid, b_uid, f, fields, where));
+    TRY(pairs_run<true>(s, n, a_uid, b_uid, f, fields));
     const int nfo = 3 + s->T, nf = nfo + 2;
     for (int64_t i = 0; i < n; ++i)
-        for (int j = 0; j < nfo; ++j) out[i * nfo + j] = where[i] < 0 ? -1.0f : fields[(size_t)where[i] * nf + j];
+        for (int j = 0; j < nfo; ++j) out[i * nfo + j] = fields[(size_t)i * nf + j];
     return PK_OK;
 }
 
@@ -2192,14 +2140,10 @@ int pk_normalizers_from_pairs(pk_store* s, int64_t n, const int32_t* a_uid, cons
     s->idf_dirty = true; s->store_dirty = true;
     std::vector<float> vals((size_t)n * nfo);        // region, clubs, friends, text columns of every pair
     int rc = ensure_ready(s);
-    for (int64_t p0 = 0; rc == PK_OK && p0 < n; p0 += 32768) {       // the kernel's [32 x 32] blocks stay bounded
-        const int64_t m = std::min<int64_t>(32768, n - p0);
+    if (rc == PK_OK) {
         std::vector<float> f, fields;
-        std::vector<int64_t> where;
-        rc = pairs_run<true>(s, m, a_uid + p0, b_uid + p0, f, fields, where);
-        if (rc != PK_OK) break;
-        for (int64_t i = 0; i < m; ++i)
-            memcpy(&vals[(size_t)(p0 + i) * nfo], &fields[(size_t)where[i] * nf], (size_t)nfo * 4);
+        rc = pairs_run<true>(s, n, a_uid, b_uid, f, fields);
+        for (int64_t i = 0; rc == PK_OK && i < n; ++i) memcpy(&vals[(size_t)i * nfo], &fields[(size_t)i * nf], (size_t)nfo * 4);
     }
     s->col_state = saved;
     s->idf_dirty = true; s->store_dirty = true;
@@ -2271,12 +2215,11 @@ int pk_pair_overlap(pk_store* s, int64_t n, const int32_t* a_uid, const int32_t*
     TRY(ensure_ready(s));
     if (n < 0 || which < 0 || which > 1 || (n > 0 && (!a_uid || !b_uid || !out))) return fail(PK_ERR_ARG, "bad argument");
     std::vector<float> f, fields;
-    std::vector<int64_t> where;
-    TRY(pairs_run<true>(s, n, a_uid, b_uid, f, fields, where));
+    TRY(pairs_run<true>(s, n, a_uid, b_uid, f, fields));
     const int nf = 3 + s->T + 2;
     for (int64_t i = 0; i < n; ++i) {
-        if (where[i] < 0) { out[i] = -1; continue; }
-        float v = fields[(size_t)where[i] * nf + 3 + s->T + which];
+        if (f[(size_t)i] < 0.0f) { out[i] = -1; continue; }          // a side without a profile
+        float v = fields[(size_t)i * nf + 3 + s->T + which];
         int32_t iv;
         memcpy(&iv, &v, 4);
         // the slot keeps its -1.0f initialiser when the field is absent on either side: overlap 0

@@ -90,6 +90,9 @@ struct LeanNorm {
     float inv_total;               // 1 / total_possible
     float margin;                  // bound on |pre-filter score - exact score|
     int32_t dim_comp, dim_age;
+    // header-only upper bound of the pre-filter (pk_prefilter.cuh): the largest sigma a jointly filled text column /
+    // a clubs / a friends field can contribute, rounded up
+    float ub_text, ub_clubs, ub_friends, pad_;
 };
 
 // One group of <= 32 query users = the lanes of the scoring warps.

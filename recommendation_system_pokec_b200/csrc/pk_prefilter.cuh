@@ -82,6 +82,14 @@ struct PreParams {
     int* dyn_ninst;              // [n_dyn] instances handed out (zeroed per launch)
     const int32_t* dyn_groups;   // [n_dyn] group index of each schedulable group
     int n_dyn, max_inst;
+    // Header-only pruning.  theta = (k-th best approximate score so far) - 2 margin - slack: a candidate whose UPPER
+    // BOUND (exact scalar fields, every jointly filled text column / set field at its largest sigma) lies below
+    // theta for all 32 queries is skipped after its 64-byte header -- it cannot reach the exact top-k, so the
+    // shortlist does not need it (the proof of shortlist_check_kernel only needs the candidates >= a_k - 2 margin).
+    // dyn_theta[group][32] carries the best theta any instance of the group has reached (float bits, atomicMax).
+    unsigned int* dyn_theta;
+    int K;                       // the caller's k (theta watches list position K - 1)
+    float theta_drop;            // 2 margin + slack
     int cand_begin, cand_end;    // the shard's row range
     uint64_t* out_keys;          // TOPK: [item.out_slot][32][Ks], key = (approx score bits, candidate ROW)
     float* out_f;                // STORE (tests): [(item.out_slot + i)][32] approximate scores
@@ -98,7 +106,8 @@ __device__ __forceinline__ float lean_sigma(float4 c, float s) {
 // Warp-cooperative insertion of `key` into one query's descending shortlist (all lanes call it with the same
 // arguments; keys are unique -- one per candidate row).
 __device__ __forceinline__ void shortlist_insert(uint64_t* list, int K, uint64_t key, int* lock, volatile uint64_t* tau,
-                                                 int lane) {
+                                                 int lane, int k_user, float theta_drop, volatile float* theta,
+                                                 unsigned int* g_theta) {
     if (lane == 0) {
         while (atomicCAS(lock, 0, 1) != 0) __nanosleep(32);
     }
@@ -120,6 +129,14 @@ __device__ __forceinline__ void shortlist_insert(uint64_t* list, int K, uint64_t
         if (lane == 0) {
             vl[pos] = key;
             *tau = vl[K - 1];
+            const uint64_t kk = vl[k_user - 1];
+            if (kk != 0ull && pos < k_user) {      // the k-th best moved: raise this query's pruning threshold
+                const float th = fmaxf(__uint_as_float(key_score_bits(kk)) - theta_drop, 0.f);
+                if (th > *theta) {
+                    *theta = th;
+                    if (g_theta) atomicMax(g_theta, __float_as_uint(th));
+                }
+            }
         }
     }
     __threadfence_block();
@@ -157,7 +174,8 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
     uint64_t* lists = reinterpret_cast<uint64_t*>(smem + arena_sm + kNormBytes);   // [32][Ks]
     uint64_t* tau = lists + 32 * Ks;
     int* locks = reinterpret_cast<int*>(tau + 32);
-    int* next = locks + 32;
+    float* theta = reinterpret_cast<float*>(locks + 32);                            // [32] pruning thresholds
+    int* next = reinterpret_cast<int*>(theta + 32);
     uint4* stage = reinterpret_cast<uint4*>(next + 4) + warp * 32;                  // per-warp hit staging
     int* pick = next + 1;                                                           // {group index, instance}
 
@@ -218,7 +236,7 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
         uint4* ndst = reinterpret_cast<uint4*>(N);
         for (uint32_t i = tid; i < kNormBytes / 16; i += kPreThreads) ndst[i] = __ldg(nsrc + i);
         for (int i = tid; i < 32 * Ks; i += kPreThreads) lists[i] = 0ull;
-        if (tid < 32) { tau[tid] = 0ull; locks[tid] = 0; }
+        if (tid < 32) { tau[tid] = 0ull; locks[tid] = 0; theta[tid] = 0.f; }
         if (tid == 0) *next = it.cand_begin;
     }
     __syncthreads();
@@ -247,6 +265,9 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
     const uint32_t lanebit = 1u << lane, lane_lt = lanebit - 1u;
     const int dim_comp = N->dim_comp, dim_age = N->dim_age;
     const float inv_total = N->inv_total;
+    const float ub_text = N->ub_text, ub_clubs = N->ub_clubs, ub_friends = N->ub_friends;
+    unsigned int* const g_theta = STORE ? nullptr : P.dyn_theta + (size_t)pick[0] * 32 + lane;
+    float th_g = 0.f;               // the group's published threshold, re-read once per chunk
 
 #ifdef PK_PRE_CHUNK
     constexpr int kChunk = PK_PRE_CHUNK;
@@ -261,6 +282,7 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
         const int c0 = __shfl_sync(kFull, c_next, 0);
         if (c0 >= it.cand_end) break;
         if (lane == 0) c_next = cursor_base + atomicAdd(cursor, kChunk);
+        if (!STORE) th_g = __uint_as_float(*reinterpret_cast<volatile unsigned int*>(g_theta));
         const int c1 = min(c0 + kChunk, it.cand_end);
         uint64_t offv = 0;
         if (c0 + lane < c1) offv = __ldg(P.lrec_off + c0 + lane);
@@ -287,13 +309,8 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
             float w_n = 0.f;
             if ((uint32_t)lane < c_ntok) { key_n = __ldg(keys + lane); w_n = __ldg(tokw + lane); }
 
-            // text columns present on both sides: every one contributes sigma(z(0)) unless a token matches
-            const uint32_t b0 = q_m0 & h3.x, b1 = q_m1 & h3.y;
-            float sum = N->lut[0][b0 & 255u] + N->lut[1][(b0 >> 8) & 255u] + N->lut[2][(b0 >> 16) & 255u] + N->lut[3][b0 >> 24];
-            if (q_m1 | h3.y)
-                sum += N->lut[4][b1 & 255u] + N->lut[5][(b1 >> 8) & 255u] + N->lut[6][(b1 >> 16) & 255u] + N->lut[7][b1 >> 24];
-            int used = __popc(b0) + __popc(b1);
-
+            float sum = 0.f;
+            int used = 0;
             // fixed scalar fields (src/recommender_similarity.cpp:38-77)
             if (q_pub >= 0 && c_pub >= 0) { const float4 f = N->fld[0]; sum += (q_pub == c_pub) ? f.w : f.z; ++used; }
             if (q_gender >= 0 && c_gender >= 0) { const float4 f = N->fld[1]; sum += (q_gender == c_gender) ? f.w : f.z; ++used; }
@@ -314,6 +331,28 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                 sum += N->region[(q_acnt * 4 + c_bcnt) * 4 + matches];
                 ++used;
             }
+            // text columns present on both sides: every one contributes sigma(z(0)) unless a token matches
+            const uint32_t b0 = q_m0 & h3.x, b1 = q_m1 & h3.y;
+            const int joint = __popc(b0) + __popc(b1);
+
+            // header-only upper bound against this query's threshold (PreParams): 2 S F / (S + F) >= theta with
+            // S = s_ub / u, F = u / total  <=>  2 s_ub u / total >= theta (s_ub + u^2 / total)
+            bool alive = q_active;
+            if (!STORE) {
+                const float th = fmaxf(reinterpret_cast<volatile float*>(theta)[lane], th_g);
+                float s_ub = fmaf((float)joint, ub_text, sum);
+                int u = used + joint;
+                if (c_ncl > 0 && q_ncl > 0) { s_ub += ub_clubs; ++u; }
+                if (c_nfr > 0 && q_nfr > 0) { s_ub += ub_friends; ++u; }
+                const float fu = (float)u;
+                alive = alive && (2.0f * s_ub * fu * inv_total >= th * fmaf(fu * fu, inv_total, s_ub));
+                if (!__any_sync(kFull, alive)) continue;
+            }
+
+            sum += N->lut[0][b0 & 255u] + N->lut[1][(b0 >> 8) & 255u] + N->lut[2][(b0 >> 16) & 255u] + N->lut[3][b0 >> 24];
+            if (q_m1 | h3.y)
+                sum += N->lut[4][b1 & 255u] + N->lut[5][(b1 >> 8) & 255u] + N->lut[6][(b1 >> 16) & 255u] + N->lut[7][b1 >> 24];
+            used += joint;
 
             // clubs / friends (:79-91): the record stores them back to back ([clubs padded to 4 | friends]) and the
             // group's table holds both sets ({id | set << 31, query mask}), so one round of <= 32 elements usually
@@ -377,6 +416,7 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                     }
                     // bit j of `mine` = "token j of this chunk belongs to MY query": each lane walks only its own hits
                     uint32_t mine = transpose32(m, lane);
+                    if (!alive) mine = 0u;
                     __syncwarp();
                     while (mine) {
                         const int j = __ffs(mine) - 1;
@@ -407,7 +447,8 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
             } else {
                 const uint64_t key = make_key(__float_as_uint(fas), ci);
                 const uint64_t tl = reinterpret_cast<volatile uint64_t*>(tau)[lane];
-                uint32_t pass = __ballot_sync(kFull, q_active && key > tl);
+                // (a score below theta cannot be needed either: the list only has to hold what reaches a_k - 2 margin)
+                uint32_t pass = __ballot_sync(kFull, alive && key > tl && fas >= reinterpret_cast<volatile float*>(theta)[lane]);
                 if (pass) {
                     // exclusions only matter for the few candidates that reach a list
                     bool ok = true;
@@ -421,7 +462,8 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                         const int j = __ffs(pass) - 1;
                         pass &= pass - 1;
                         const uint64_t kj = __shfl_sync(kFull, key, j);
-                        shortlist_insert(lists + j * Ks, Ks, kj, locks + j, reinterpret_cast<volatile uint64_t*>(tau) + j, lane);
+                        shortlist_insert(lists + j * Ks, Ks, kj, locks + j, reinterpret_cast<volatile uint64_t*>(tau) + j, lane, P.K,
+                                         P.theta_drop, reinterpret_cast<volatile float*>(theta) + j, g_theta - lane + j);
                     }
                 }
             }
