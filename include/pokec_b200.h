@@ -158,6 +158,14 @@ int pk_edge_cache_row(pk_store* s, int32_t uid, float* out, int64_t cap, int64_t
  * Returns the list length in *n (may exceed cap; only cap entries are written). */
 int pk_candidates(pk_store* s, int mode, int32_t uid, int limit, int32_t* out, int64_t cap, int64_t* n);
 
+/* The same lists for nq users in one call, expanded ON THE DEVICE (adjacency CSR resident in HBM, one warp per user:
+ * ordered de-duplication against a per-warp hash set, truncation at `limit`) -- the enumeration pk_recommend uses for
+ * batches of PK_MODE_GRAPH / PK_MODE_COLLAB.  out_ids is [nq][limit] (only the first out_cnt[q] entries of a row are
+ * written), same ids in the same order as pk_candidates.  PK_ERR_UNSUPPORTED when the device path cannot take the call:
+ * limit outside [1, 16384], a neighbour row longer than 32768, or rows replaced with pk_set_adj_row (the device holds
+ * the loaded adjacency; single-user drop-in calls keep walking the caller's live rows on the host). */
+int pk_candidates_batch(pk_store* s, int mode, int nq, const int32_t* q_uid, int limit, int32_t* out_ids, int32_t* out_cnt);
+
 /* ---- multi-GPU plumbing (one process per GPU; the all-gather itself is the caller's NCCL) ----- */
 
 /* Local top-k of the shard as packed sort keys on the DEVICE: d_keys is a device buffer of

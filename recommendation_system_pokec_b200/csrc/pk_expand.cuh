@@ -1,0 +1,362 @@
+// pk_expand.cuh -- friend-of-friend candidate expansion on the device (batched list modes).
+//
+// The reference enumerates candidates by walking the adjacency in order, keeping first occurrences and stopping at
+// candidate_limit:
+//   gather_candidates_local (src/recommender_graph.cpp:10-31)  friend, then that friend's friends, for every friend
+//   recommend_collaborative (src/recommender_graph.cpp:114-125) the friends' friends only
+// Both are "the first `limit` first-occurrences of a sequence", so a warp can take the sequence 32 elements at a
+// time: probe a hash set of what earlier chunks inserted, elect one lane per distinct new id inside the chunk
+// (__match_any_sync), give the elected lanes consecutive output positions in lane order (ballot + popc) and insert
+// their ids.  The set lives in a per-warp scratch table in global memory (L2) tagged with an epoch, so it is never
+// cleared between queries.  The same primitive numbers the distinct friends that have a profile (the columns of the
+// collaborative FAS matrix).  One warp per query user; the adjacency CSR and the uid -> row maps are device-resident.
+#pragma once
+#include "pk_layout.h"
+
+namespace pk {
+
+struct DevGraph {
+    const int64_t* adj_ptr;          // [m + 1]
+    const int32_t* adj;              // neighbour uids, original order
+    const int32_t* uid;              // [n] row -> uid
+    // uid -> adjacency row / profile row: direct arrays over [uid_lo, uid_lo + range) when the uid range is dense
+    // enough, else binary search over the ascending (uid, row) pairs
+    const int32_t* adj_direct;
+    const int32_t* row_direct;
+    int32_t uid_lo;
+    int64_t range;
+    const int32_t* adj_sorted_uid;   // [m]
+    const int32_t* adj_sorted_row;
+    const int32_t* uid_sorted;       // [n]
+    const int32_t* uid_sorted_row;
+    int m, n;
+};
+
+__device__ __forceinline__ int dg_search(const int32_t* keys, const int32_t* vals, int cnt, int32_t u) {
+    int lo = 0, hi = cnt;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (__ldg(keys + mid) < u) lo = mid + 1; else hi = mid; }
+    return (lo < cnt && __ldg(keys + lo) == u) ? __ldg(vals + lo) : -1;
+}
+__device__ __forceinline__ int dg_adj_row(const DevGraph& G, int32_t u) {
+    if (G.adj_direct) { const int64_t i = (int64_t)u - G.uid_lo; return (i >= 0 && i < G.range) ? __ldg(G.adj_direct + i) : -1; }
+    return dg_search(G.adj_sorted_uid, G.adj_sorted_row, G.m, u);
+}
+__device__ __forceinline__ int dg_row(const DevGraph& G, int32_t u) {
+    if (G.row_direct) { const int64_t i = (int64_t)u - G.uid_lo; return (i >= 0 && i < G.range) ? __ldg(G.row_direct + i) : -1; }
+    return dg_search(G.uid_sorted, G.uid_sorted_row, G.n, u);
+}
+
+// ---- per-warp scratch set: slot = [epoch 8 | value 24 | key 32]; a slot belongs to the current query iff its epoch matches
+constexpr int kExpWarps = 8;                     // warps per CTA of the expansion kernel
+constexpr unsigned kExpFull = 0xffffffffu;
+
+__device__ __forceinline__ uint32_t exp_hash(uint32_t key, uint32_t mask) { return (key * 0x9E3779B1u) >> 7 & mask; }
+
+// slot index of `key`, or -1
+__device__ __forceinline__ int set_find(const unsigned long long* tab, uint32_t mask, uint32_t epoch, uint32_t key) {
+    uint32_t s = exp_hash(key, mask);
+    for (;;) {
+        const unsigned long long v = __ldcg(tab + s);
+        if ((uint32_t)(v >> 56) != epoch) return -1;
+        if ((uint32_t)v == key) return (int)s;
+        s = (s + 1) & mask;
+    }
+}
+// inserts a key that is known to be absent (one inserting lane per distinct key); returns its slot
+__device__ __forceinline__ int set_insert(unsigned long long* tab, uint32_t mask, uint32_t epoch, uint32_t key, uint32_t value) {
+    const unsigned long long nw = ((unsigned long long)epoch << 56) | ((unsigned long long)(value & 0xffffffu) << 32) | key;
+    uint32_t s = exp_hash(key, mask);
+    for (;;) {
+        unsigned long long v = __ldcg(tab + s);
+        while ((uint32_t)(v >> 56) != epoch) {
+            const unsigned long long old = atomicCAS(tab + s, v, nw);
+            if (old == v) return (int)s;
+            v = old;
+        }
+        s = (s + 1) & mask;
+    }
+}
+
+struct ExpandParams {
+    DevGraph G;
+    const int32_t* q_uid;
+    int nq;
+    int mode;                        // PK_MODE_GRAPH: gather_candidates_local; PK_MODE_COLLAB / PK_MODE_CLUBS: friends' friends
+    int limit;                       // >= 1
+    int raw;                         // 1 = emit the raw expansion (uids) without the profile / friend filters (pk_candidates_batch)
+    unsigned long long* scratch;     // [warps][tab_cap] persistent across launches
+    uint32_t* epoch;                 // [warps] last epoch used
+    uint32_t tab_cap;                // power of two >= 2 (limit + 32) and >= 2 (max friends of a query) -- see the host
+    int* next_query;                 // work queue (zeroed per launch)
+    int cand_cap;                    // per-query capacity of cand_out (= limit)
+    // outputs
+    int32_t* q_row;                  // [nq] profile row of the user, -1 = none (no result)
+    int32_t* cand_out;               // [nq][cand_cap] kept candidates in the reference's order: rows (raw: uids)
+    int32_t* cand_cnt;               // [nq]
+    // collaborative / clubs: the distinct friends that have a profile, numbered in adjacency order
+    int32_t* fr_slot;                // [E] per adjacency entry of a queried user: slot, -1 = no profile
+    int32_t* slot_row;               // [E] per slot (stored at the user's adjacency offset): profile row
+    int32_t* n_slots;                // [nq]
+    int32_t* q_adj_off;              // [nq] offset of the user's adjacency row in `adj` (-1 = no row)
+    int32_t* q_deg;                  // [nq]
+};
+
+__global__ void __launch_bounds__(kExpWarps * 32) expand_kernel(const ExpandParams P) {
+    const int lane = threadIdx.x & 31;
+    const int wslot = blockIdx.x * kExpWarps + (threadIdx.x >> 5);
+    unsigned long long* tab = P.scratch + (size_t)wslot * P.tab_cap;
+    const uint32_t mask = P.tab_cap - 1u;
+    const uint32_t lane_lt = (1u << lane) - 1u;
+    const DevGraph& G = P.G;
+    uint32_t epoch = P.epoch[wslot];
+    auto next_epoch = [&]() {
+        if (++epoch > 255u) {                       // wrapped: every old tag would alias -- clear the table once
+            for (uint32_t i = lane; i < P.tab_cap; i += 32) tab[i] = 0ull;
+            __syncwarp();
+            epoch = 1u;
+        }
+    };
+    for (;;) {
+        int q = 0;
+        if (lane == 0) q = atomicAdd(P.next_query, 1);
+        q = __shfl_sync(kExpFull, q, 0);
+        if (q >= P.nq) break;
+        const int32_t user = P.q_uid[q];
+        const int urow = dg_row(G, user);
+        const int arow = dg_adj_row(G, user);
+        const int64_t ub = arow >= 0 ? G.adj_ptr[arow] : 0;
+        const int deg = arow >= 0 ? (int)(G.adj_ptr[arow + 1] - ub) : 0;
+        if (lane == 0) {
+            P.q_row[q] = urow;
+            P.cand_cnt[q] = 0;
+            if (P.n_slots) { P.n_slots[q] = 0; P.q_adj_off[q] = arow >= 0 ? (int32_t)ub : -1; P.q_deg[q] = deg; }
+        }
+        // src/recommender_graph.cpp:40,130, src/recommender_clubs.cpp:16: no profile, no result (the raw lists of
+        // pk_candidates do not depend on the profile)
+        if ((urow < 0 && !P.raw) || deg == 0) continue;
+
+        // ---- the distinct friends that have a profile, in adjacency order (collaborative / clubs) ----
+        if (P.n_slots && !P.raw) {
+            next_epoch();
+            int ns = 0;
+            for (int i0 = 0; i0 < deg; i0 += 32) {
+                const int i = i0 + lane;
+                int32_t f = 0;
+                int rf = -1;
+                if (i < deg) { f = __ldg(G.adj + ub + i); rf = dg_row(G, f); }
+                const bool valid = rf >= 0;                                   // src/recommender_graph.cpp:134
+                int sl = valid ? set_find(tab, mask, epoch, (uint32_t)f) : -1;
+                int slot = sl >= 0 ? (int)((__ldcg(tab + sl) >> 32) & 0xffffffu) : -1;
+                const bool fresh = valid && sl < 0;
+                const uint32_t fresh_m = __ballot_sync(kExpFull, fresh);
+                // one lane per distinct new friend: the lowest lane holding that uid
+                const uint32_t same = __match_any_sync(kExpFull, fresh ? f : (int32_t)(0x80000000u | (uint32_t)lane)) & fresh_m;
+                const bool leader = fresh && (__ffs(same) - 1) == lane;
+                const uint32_t lead_m = __ballot_sync(kExpFull, leader);
+                const int pos = ns + __popc(lead_m & lane_lt);
+                if (leader) {
+                    set_insert(tab, mask, epoch, (uint32_t)f, (uint32_t)pos);
+                    P.slot_row[ub + pos] = rf;
+                }
+                const int lpos = __shfl_sync(kExpFull, pos, fresh ? (__ffs(same) - 1) : 0);
+                if (fresh) slot = lpos;
+                if (i < deg) P.fr_slot[ub + i] = slot;
+                ns += __popc(lead_m);
+                __syncwarp();
+            }
+            if (lane == 0) P.n_slots[q] = ns;
+        }
+
+        // ---- candidate expansion: first `limit` first-occurrences of the reference's visiting sequence ----
+        next_epoch();
+        int count = 0;
+        int32_t* out = P.cand_out + (size_t)q * P.cand_cap;
+        const bool graph = P.mode == PK_MODE_GRAPH;
+        for (int fi = 0; fi < deg && count < P.limit; ++fi) {
+            const int32_t f = __ldg(G.adj + ub + fi);
+            if (graph && f == user) continue;                                 // src/recommender_graph.cpp:18
+            const int frow = dg_adj_row(G, f);
+            const int64_t fb = frow >= 0 ? G.adj_ptr[frow] : 0;
+            const int fdeg = frow >= 0 ? (int)(G.adj_ptr[frow + 1] - fb) : 0;
+            // graph: the friend itself, then its row (:19-29); collaborative: the row only (:116-124)
+            const int total = fdeg + (graph ? 1 : 0);
+            for (int e0 = 0; e0 < total && count < P.limit; e0 += 32) {
+                const int e = e0 + lane;
+                int32_t x = 0;
+                bool valid = e < total;
+                if (valid) {
+                    x = (graph && e == 0) ? f : __ldg(G.adj + fb + e - (graph ? 1 : 0));
+                    valid = x != user;                                        // :23 / :120
+                }
+                const bool fresh = valid && set_find(tab, mask, epoch, (uint32_t)x) < 0;
+                const uint32_t fresh_m = __ballot_sync(kExpFull, fresh);
+                const uint32_t same = __match_any_sync(kExpFull, fresh ? x : (int32_t)(0x80000000u | (uint32_t)lane)) & fresh_m;
+                const bool leader = fresh && (__ffs(same) - 1) == lane;
+                const uint32_t lead_m = __ballot_sync(kExpFull, leader);
+                const int pos = count + __popc(lead_m & lane_lt);
+                if (leader && pos < P.limit) {
+                    set_insert(tab, mask, epoch, (uint32_t)x, 0u);
+                    out[pos] = x;
+                }
+                count += __popc(lead_m);
+                __syncwarp();
+            }
+        }
+        count = min(count, P.limit);
+        if (P.raw) {
+            if (lane == 0) P.cand_cnt[q] = count;
+            continue;
+        }
+        // ---- filters: a profile must exist (:54 / :172); graph also drops the user's existing friends (:46-52) ----
+        if (graph) {
+            for (int i = lane; i < deg; i += 32) {
+                const int sl = set_find(tab, mask, epoch, (uint32_t)__ldg(G.adj + ub + i));
+                if (sl >= 0) atomicOr(tab + sl, 1ull << 32);                  // value bit 0 = "is a friend"
+            }
+            __syncwarp();
+        }
+        int kept = 0;
+        for (int i0 = 0; i0 < count; i0 += 32) {
+            const int i = i0 + lane;
+            int rc = -1;
+            if (i < count) {
+                const int32_t c = out[i];
+                rc = dg_row(G, c);
+                if (graph && rc >= 0) {
+                    const int sl = set_find(tab, mask, epoch, (uint32_t)c);
+                    if (sl >= 0 && ((__ldcg(tab + sl) >> 32) & 1ull)) rc = -1;
+                }
+            }
+            const uint32_t keep_m = __ballot_sync(kExpFull, rc >= 0);
+            __syncwarp();                                                     // every lane has read out[i0 .. i0 + 32)
+            if (rc >= 0) out[kept + __popc(keep_m & lane_lt)] = rc;           // in place: kept <= i0
+            kept += __popc(keep_m);
+            __syncwarp();
+        }
+        if (lane == 0) P.cand_cnt[q] = kept;
+    }
+    if (lane == 0) P.epoch[wslot] = epoch;
+}
+
+// ---- offsets: exclusive scan of per-query counts (single CTA; nq is a batch, not a world) ----
+// in: cnt_a[nq] (candidates), cnt_b[nq] (slots, may be null).  out: cand_off[nq + 1]; pair_off[nq + 1] with per-query
+// pair count = graph: cnt_a; collaborative: cnt_b (the w_f pairs) + cnt_a * cnt_b (the FAS(f, c) matrix)
+__global__ void __launch_bounds__(1024) offsets_kernel(int nq, const int32_t* __restrict__ cnt_a, const int32_t* __restrict__ cnt_b,
+                                                       int32_t* __restrict__ cand_off, int64_t* __restrict__ pair_off) {
+    __shared__ long long wsum_a[32], wsum_p[32];
+    __shared__ long long run_a, run_p;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) { run_a = 0; run_p = 0; }
+    __syncthreads();
+    for (int base = 0; base < nq; base += 1024) {
+        const int q = base + tid;
+        long long a = 0, p = 0;
+        if (q < nq) {
+            a = cnt_a[q];
+            p = cnt_b ? (long long)cnt_b[q] * (1 + a) : a;
+        }
+        long long ia = a, ip = p;
+        for (int o = 1; o < 32; o <<= 1) {
+            const long long va = __shfl_up_sync(0xffffffffu, ia, o), vp = __shfl_up_sync(0xffffffffu, ip, o);
+            if (lane >= o) { ia += va; ip += vp; }
+        }
+        if (lane == 31) { wsum_a[warp] = ia; wsum_p[warp] = ip; }
+        __syncthreads();
+        long long oa = run_a, op = run_p;
+        for (int w = 0; w < warp; ++w) { oa += wsum_a[w]; op += wsum_p[w]; }
+        if (q < nq) { cand_off[q] = (int32_t)(oa + ia - a); pair_off[q] = op + ip - p; }
+        __syncthreads();
+        if (tid == 1023) { run_a = oa + ia; run_p = op + ip; }
+        __syncthreads();
+    }
+    if (tid == 0) { cand_off[nq] = (int32_t)run_a; pair_off[nq] = run_p; }
+}
+
+// ---- pair emission: one CTA per query ----
+struct EmitParams {
+    int nq, mode, cand_cap;
+    const int32_t* q_row;
+    const int32_t* cand_out;     // [nq][cand_cap] candidate rows
+    const int32_t* cand_cnt;
+    const int32_t* cand_off;     // [nq + 1]
+    const int64_t* pair_off;     // [nq + 1]
+    const int32_t* n_slots;      // collaborative
+    const int32_t* q_adj_off;
+    const int32_t* slot_row;
+    const int32_t* uid;          // row -> uid
+    int32_t* a_row;              // [pairs]
+    int32_t* b_row;
+    int32_t* key_id;             // graph: [pairs] candidate uid of each pair; collaborative: [cands] candidate uid
+    int32_t* cand_row_flat;      // collaborative: [cands] candidate rows, compacted
+};
+
+__global__ void __launch_bounds__(256) emit_pairs_kernel(const EmitParams P) {
+    const int q = blockIdx.x;
+    const int nc = P.cand_cnt[q];
+    const int32_t* cand = P.cand_out + (size_t)q * P.cand_cap;
+    const int64_t p0 = P.pair_off[q];
+    const int c0 = P.cand_off[q];
+    const int urow = P.q_row[q];
+    if (P.mode == PK_MODE_GRAPH) {
+        for (int i = threadIdx.x; i < nc; i += blockDim.x) {
+            const int rc = cand[i];
+            P.a_row[p0 + i] = urow;
+            P.b_row[p0 + i] = rc;
+            P.key_id[p0 + i] = P.uid[rc];
+        }
+        return;
+    }
+    const int ns = P.n_slots[q];
+    const int32_t* srow = P.slot_row + (P.q_adj_off[q] >= 0 ? P.q_adj_off[q] : 0);
+    for (int i = threadIdx.x; i < nc; i += blockDim.x) {
+        const int rc = cand[i];
+        P.cand_row_flat[c0 + i] = rc;
+        P.key_id[c0 + i] = P.uid[rc];
+    }
+    // w_f = FAS(user, f) for every distinct friend with a profile, then FAS(f, c): pair index = c * ns + slot
+    for (int s = threadIdx.x; s < ns; s += blockDim.x) { P.a_row[p0 + s] = urow; P.b_row[p0 + s] = srow[s]; }
+    const int64_t m0 = p0 + ns;
+    const int64_t total = (int64_t)nc * ns;
+    for (int64_t t = threadIdx.x; t < total; t += blockDim.x) {
+        const int c = (int)(t / ns), s = (int)(t - (int64_t)c * ns);
+        P.a_row[m0 + t] = srow[s];
+        P.b_row[m0 + t] = cand[c];
+    }
+}
+
+// collaborative reduce on the pair layout above (src/recommender_graph.cpp:167-180,213): score(c) = sum over the
+// user's friends IN ADJACENCY ORDER (duplicates counted again, friends without a profile skipped) of
+// (double)w_f * (double)FAS(f, c), rounded to float once
+struct CollabReduce2Params {
+    int nq;
+    const float* fas;            // pair scores
+    const int64_t* pair_off;
+    const int32_t* cand_off;
+    const int32_t* n_slots;
+    const int32_t* q_adj_off;
+    const int32_t* q_deg;
+    const int32_t* fr_slot;      // [E]
+    const int32_t* key_id;       // [cands]
+    uint64_t* out_keys;          // [cands]
+};
+
+__global__ void __launch_bounds__(128) collab_reduce2_kernel(const CollabReduce2Params P) {
+    const int q = blockIdx.y;
+    const int c0 = P.cand_off[q], nc = P.cand_off[q + 1] - c0;
+    if (nc == 0) return;
+    const int ns = P.n_slots[q], deg = P.q_deg[q];
+    const float* w = P.fas + P.pair_off[q];
+    const float* mat = w + ns;
+    const int32_t* fs = P.fr_slot + (P.q_adj_off[q] >= 0 ? P.q_adj_off[q] : 0);
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < nc; c += gridDim.x * blockDim.x) {
+        double score = 0.0;
+        for (int i = 0; i < deg; ++i) {
+            const int sl = fs[i];
+            if (sl < 0) continue;
+            score = __dadd_rn(score, __dmul_rn((double)w[sl], (double)mat[(int64_t)c * ns + sl]));
+        }
+        P.out_keys[c0 + c] = make_key(__float_as_uint((float)score), P.key_id[c0 + c]);
+    }
+}
+
+}  // namespace pk

@@ -32,6 +32,7 @@
 #include "pk_prefilter.cuh"
 #include "pk_clubs.cuh"
 #include "pk_pairs.cuh"
+#include "pk_expand.cuh"
 
 using namespace pk;
 
@@ -193,6 +194,7 @@ struct pk_store {
     bool wide_ids = false;   // a club / friend id >= 2^31: the pre-filter's combined set table cannot tag it
     DevBuf<uint4> d_lrec;
     DevBuf<uint64_t> d_lrec_off;
+    DevBuf<uint2> d_lmask;
     uint64_t lean_u4 = 0;
     DevBuf<LeanNorm> d_lnorm;
     DevBuf<float> d_tab_comp32, d_tab_age32;
@@ -223,6 +225,18 @@ struct pk_store {
     DevBuf<float> d_edge_fas;
     std::vector<float> h_edge_fas;
     bool edge_cache_valid = false;
+    // ---- device-resident graph for the batched list modes (pk_expand.cuh) -------------------------------------
+    bool graph_dirty = true;
+    int64_t max_deg = 0;
+    DevBuf<int64_t> g_adj_ptr;
+    DevBuf<int32_t> g_adj, g_adj_direct, g_row_direct, g_adj_suid, g_adj_srow, g_uid_s, g_uid_srow;
+    DevBuf<unsigned long long> g_scratch;
+    DevBuf<uint32_t> g_epoch;
+    uint32_t g_tab_cap = 0;
+    int g_warps = 0;
+    DevBuf<int32_t> g_fr_slot, g_slot_row;           // [E] per adjacency entry of a queried user
+    DevBuf<int32_t> g_qrow, g_cand, g_cnt, g_nslots, g_qoff, g_qdeg, g_cand_off, g_next;
+    DevBuf<int64_t> g_pair_off;
     FullscanJob job;
     // bumped by every call that changes what a prepared full-scan plan depends on (world, shard, normalizers, idf,
     // adjacency overrides): a plan stamped with an older value is refused by execute / finish / fetch / keys
@@ -514,9 +528,10 @@ int rebuild_lean(pk_store* s) {
     s->lean_u4 = off[n];
     TRY(s->d_lrec.reserve(s->lean_u4 + 16));      // + 256 B: the pre-filter reads the first 32 set words of a record speculatively
     TRY(upload(s, s->d_lrec_off, off));
+    TRY(s->d_lmask.reserve((size_t)std::max(n, 1)));
     if (n > 0) {
         const unsigned blocks = (unsigned)(((int64_t)n * 32 + 255) / 256);
-        lean_pack_kernel<<<blocks, 256, 0, s->stream>>>(n, s->d_rec.p, s->d_rec_off.p, s->d_lrec_off.p, s->d_lrec.p);
+        lean_pack_kernel<<<blocks, 256, 0, s->stream>>>(n, s->d_rec.p, s->d_rec_off.p, s->d_lrec_off.p, s->d_lrec.p, s->d_lmask.p);
         ++s->stat_launches;
     }
     CK(cudaStreamSynchronize(s->stream));
@@ -715,7 +730,8 @@ ScanParams base_scan_params(pk_store* s, int K) {
 
 uint32_t lean_fixed_smem(int Ks) {
     const uint32_t norm = (uint32_t)((sizeof(LeanNorm) + 15) & ~15u);
-    return norm + 32u * Ks * 8u + 32u * 8u + 32u * 4u + 32u * 4u + 16u + (uint32_t)kPreWarps * 32u * 16u;
+    // lists, tau, locks, theta, level-1 tables {l1q 32 x 16, l1f 32 x 32, l1b 32 x 4}, next / pick, per-warp hit staging
+    return norm + 32u * Ks * 8u + 32u * 8u + 32u * 4u + 32u * 4u + (512u + 1024u + 128u) + 16u + (uint32_t)kPreWarps * 32u * 16u;
 }
 
 void finish_group(pk_store* s, Plan& plan, GroupDesc& g, const uint32_t* excl_n, int Kp, bool with_lean = false, int Ks = 0) {
@@ -1014,7 +1030,7 @@ int launch_prefilter(pk_store* s, const PreParams& P, size_t n_items, uint32_t l
 PreParams base_pre_params(pk_store* s) {
     PreParams P;
     memset(&P, 0, sizeof(P));
-    P.lrec = s->d_lrec.p; P.lrec_off = s->d_lrec_off.p; P.ln = s->d_lnorm.p;
+    P.lrec = s->d_lrec.p; P.lrec_off = s->d_lrec_off.p; P.lmask = s->d_lmask.p; P.ln = s->d_lnorm.p;
     P.tab_comp = s->d_tab_comp32.p; P.tab_age = s->d_tab_age32.p;
     return P;
 }
@@ -1301,6 +1317,151 @@ int recommend_graph(pk_store* s, int nq, const int32_t* q_uid, int k, int limit,
         TRY((pairs_launch<false>(s, np, s->d_i32a.p, s->d_i32b.p, s->d_f32a.p, nullptr, s->d_i32c.p, s->d_keys_a.p)));
         TRY(launch_slice_topk(s, s->d_keys_a.p, s->d_i32d.p, nq, K, s->d_keys_b.p));
         CK(cudaMemcpyAsync(keys.data(), s->d_keys_b.p, (size_t)nq * K * 8, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+        TRY(collect_scan_time(s));
+    }
+    memcpy(h_keys, keys.data(), (size_t)nq * K * 8);
+    return PK_OK;
+}
+
+// ---- batched list modes with the candidate expansion on the device (pk_expand.cuh) ---------------------
+int ensure_graph(pk_store* s) {
+    if (!s->graph_dirty) return PK_OK;
+    TRY(upload(s, s->g_adj_ptr, s->adj_ptr));
+    TRY(upload(s, s->g_adj, s->adj));
+    if (!s->row_direct.empty()) {
+        TRY(upload(s, s->g_row_direct, s->row_direct));
+        TRY(upload(s, s->g_adj_direct, s->adj_direct));
+    } else {
+        std::vector<int32_t> ku(s->uid_sorted.size()), kr(s->uid_sorted.size());
+        for (size_t i = 0; i < ku.size(); ++i) { ku[i] = s->uid_sorted[i].first; kr[i] = s->uid_sorted[i].second; }
+        TRY(upload(s, s->g_uid_s, ku)); TRY(upload(s, s->g_uid_srow, kr));
+        std::vector<std::pair<int32_t, int32_t>> a(s->adj_uid.size());
+        for (size_t r = 0; r < a.size(); ++r) a[r] = {s->adj_uid[r], (int32_t)r};
+        std::sort(a.begin(), a.end());
+        std::vector<int32_t> au(a.size()), ar(a.size());
+        for (size_t i = 0; i < a.size(); ++i) { au[i] = a[i].first; ar[i] = a[i].second; }
+        TRY(upload(s, s->g_adj_suid, au)); TRY(upload(s, s->g_adj_srow, ar));
+        CK(cudaStreamSynchronize(s->stream));       // locals
+    }
+    const size_t E = std::max<size_t>(s->adj.size(), 1);
+    TRY(s->g_fr_slot.reserve(E)); TRY(s->g_slot_row.reserve(E));
+    CK(cudaStreamSynchronize(s->stream));
+    s->graph_dirty = false;
+    return PK_OK;
+}
+
+DevGraph dev_graph(pk_store* s) {
+    DevGraph G;
+    memset(&G, 0, sizeof(G));
+    G.adj_ptr = s->g_adj_ptr.p; G.adj = s->g_adj.p; G.uid = s->d_uid.p;
+    if (!s->row_direct.empty()) {
+        G.adj_direct = s->g_adj_direct.p; G.row_direct = s->g_row_direct.p;
+        G.uid_lo = s->uid_lo; G.range = (int64_t)s->row_direct.size();
+    } else {
+        G.adj_sorted_uid = s->g_adj_suid.p; G.adj_sorted_row = s->g_adj_srow.p;
+        G.uid_sorted = s->g_uid_s.p; G.uid_sorted_row = s->g_uid_srow.p;
+    }
+    G.m = (int)s->adj_uid.size(); G.n = s->n;
+    return G;
+}
+
+// the device pipeline takes a batch when nothing it mirrors was overridden behind the store and the per-warp scratch
+// set stays small; single-user drop-in calls keep the host walk (they must read the caller's LIVE adjacency)
+bool device_lists_usable(pk_store* s, int mode, int nq, int limit) {
+    if (const char* e = getenv("POKEC_B200_HOST_LISTS")) if (e[0] == '1') return false;
+    if (mode == PK_MODE_CLUBS) return false;
+    if (!s->adj_override.empty() || nq < 16) return false;
+    if (limit < 1 || limit > 16384 || s->max_deg > 32768) return false;
+    if (s->adj.size() > 0x7fffff00ull) return false;
+    return true;
+}
+
+// expansion of a batch: fills g_qrow / g_cand / g_cnt (+ friend slots for the collaborative mode)
+int expand_batch(pk_store* s, int mode, int nq, const int32_t* q_uid, int limit, bool raw) {
+    TRY(ensure_graph(s));
+    uint32_t cap = 1024;
+    while (cap < 2u * (uint32_t)(limit + 32) || cap < 2u * (uint32_t)(s->max_deg + 32)) cap <<= 1;
+    int sm_count = 148;
+    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, s->device);
+    const int ctas = std::max(1, std::min(sm_count * 2, (nq + kExpWarps - 1) / kExpWarps));
+    const int warps = sm_count * 2 * kExpWarps;
+    if (cap != s->g_tab_cap || warps != s->g_warps) {     // new table geometry: every tag is meaningless
+        TRY(s->g_scratch.reserve((size_t)warps * cap));
+        TRY(s->g_epoch.reserve((size_t)warps));
+        CK(cudaMemsetAsync(s->g_scratch.p, 0, (size_t)warps * cap * 8, s->stream));
+        CK(cudaMemsetAsync(s->g_epoch.p, 0, (size_t)warps * 4, s->stream));
+        s->g_tab_cap = cap; s->g_warps = warps;
+    }
+    TRY(upload(s, s->d_i32e, q_uid, (size_t)nq));
+    TRY(s->g_qrow.reserve(nq)); TRY(s->g_cnt.reserve(nq)); TRY(s->g_nslots.reserve(nq)); TRY(s->g_qoff.reserve(nq));
+    TRY(s->g_qdeg.reserve(nq)); TRY(s->g_next.reserve(4));
+    TRY(s->g_cand.reserve((size_t)nq * limit));
+    CK(cudaMemsetAsync(s->g_next.p, 0, 16, s->stream));
+    ExpandParams X;
+    memset(&X, 0, sizeof(X));
+    X.G = dev_graph(s);
+    X.q_uid = s->d_i32e.p; X.nq = nq; X.mode = mode; X.limit = limit; X.raw = raw ? 1 : 0;
+    X.scratch = s->g_scratch.p; X.epoch = s->g_epoch.p; X.tab_cap = cap; X.next_query = s->g_next.p; X.cand_cap = limit;
+    X.q_row = s->g_qrow.p; X.cand_out = s->g_cand.p; X.cand_cnt = s->g_cnt.p;
+    if (mode != PK_MODE_GRAPH) {
+        X.fr_slot = s->g_fr_slot.p; X.slot_row = s->g_slot_row.p; X.n_slots = s->g_nslots.p;
+        X.q_adj_off = s->g_qoff.p; X.q_deg = s->g_qdeg.p;
+    }
+    expand_kernel<<<ctas, kExpWarps * 32, 0, s->stream>>>(X);
+    ++s->stat_launches;
+    CK(cudaGetLastError());
+    return PK_OK;
+}
+
+int recommend_lists_device(pk_store* s, int mode, int nq, const int32_t* q_uid, int k, int limit, uint64_t* h_keys) {
+    const int K = std::max(k, 1);
+    std::vector<uint64_t> keys((size_t)nq * K, 0ull);
+    // batches bounded so that the [nq][limit] candidate block and the pair arrays stay moderate
+    const int kQ = 8192;
+    for (int q0 = 0; q0 < nq; q0 += kQ) {
+        const int m = std::min(kQ, nq - q0);
+        TRY(expand_batch(s, mode, m, q_uid + q0, limit, false));
+        const bool collab = mode != PK_MODE_GRAPH;
+        TRY(s->g_cand_off.reserve((size_t)m + 1)); TRY(s->g_pair_off.reserve((size_t)m + 1));
+        offsets_kernel<<<1, 1024, 0, s->stream>>>(m, s->g_cnt.p, collab ? s->g_nslots.p : nullptr, s->g_cand_off.p, s->g_pair_off.p);
+        ++s->stat_launches;
+        int32_t n_cands = 0;
+        int64_t n_pairs = 0;
+        CK(cudaMemcpyAsync(&n_cands, s->g_cand_off.p + m, 4, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaMemcpyAsync(&n_pairs, s->g_pair_off.p + m, 8, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+        if (n_pairs > 0x7fffff00ll) return fail(PK_ERR_UNSUPPORTED, "list-mode batch too large (%lld pairs; split the batch)", (long long)n_pairs);
+        s->stat_pairs += n_pairs;
+        if (n_cands == 0) continue;
+        TRY(s->d_i32a.reserve((size_t)std::max<int64_t>(n_pairs, 1))); TRY(s->d_i32b.reserve((size_t)std::max<int64_t>(n_pairs, 1)));
+        TRY(s->d_i32c.reserve((size_t)std::max<int64_t>(collab ? n_cands : n_pairs, 1)));
+        TRY(s->d_i32d.reserve((size_t)n_cands));
+        TRY(s->d_f32a.reserve((size_t)std::max<int64_t>(n_pairs, 1)));
+        TRY(s->d_keys_a.reserve((size_t)n_cands));
+        TRY(s->d_keys_b.reserve((size_t)m * K));
+        EmitParams E;
+        memset(&E, 0, sizeof(E));
+        E.nq = m; E.mode = mode; E.cand_cap = limit; E.q_row = s->g_qrow.p; E.cand_out = s->g_cand.p; E.cand_cnt = s->g_cnt.p;
+        E.cand_off = s->g_cand_off.p; E.pair_off = s->g_pair_off.p; E.n_slots = s->g_nslots.p; E.q_adj_off = s->g_qoff.p;
+        E.slot_row = s->g_slot_row.p; E.uid = s->d_uid.p; E.a_row = s->d_i32a.p; E.b_row = s->d_i32b.p; E.key_id = s->d_i32c.p;
+        E.cand_row_flat = s->d_i32d.p;
+        emit_pairs_kernel<<<m, 256, 0, s->stream>>>(E);
+        ++s->stat_launches;
+        CK(cudaGetLastError());
+        if (!collab) {
+            TRY((pairs_launch<false>(s, n_pairs, s->d_i32a.p, s->d_i32b.p, s->d_f32a.p, nullptr, s->d_i32c.p, s->d_keys_a.p)));
+        } else {
+            TRY((pairs_launch<false>(s, n_pairs, s->d_i32a.p, s->d_i32b.p, s->d_f32a.p, nullptr, nullptr, nullptr)));
+            CollabReduce2Params R;
+            R.nq = m; R.fas = s->d_f32a.p; R.pair_off = s->g_pair_off.p; R.cand_off = s->g_cand_off.p; R.n_slots = s->g_nslots.p;
+            R.q_adj_off = s->g_qoff.p; R.q_deg = s->g_qdeg.p; R.fr_slot = s->g_fr_slot.p; R.key_id = s->d_i32c.p; R.out_keys = s->d_keys_a.p;
+            collab_reduce2_kernel<<<dim3(8, m), 128, 0, s->stream>>>(R);
+            ++s->stat_launches;
+            CK(cudaGetLastError());
+        }
+        TRY(launch_slice_topk(s, s->d_keys_a.p, s->g_cand_off.p, m, K, s->d_keys_b.p));
+        CK(cudaMemcpyAsync(keys.data() + (size_t)q0 * K, s->d_keys_b.p, (size_t)m * K * 8, cudaMemcpyDeviceToHost, s->stream));
         CK(cudaStreamSynchronize(s->stream));
         TRY(collect_scan_time(s));
     }
@@ -1924,6 +2085,9 @@ int pk_store_load_world(pk_store* s, const pk_world* w) {
     s->adj_row.reserve((size_t)m * 2);
     for (int r = 0; r < m; ++r) s->adj_row[w->adj_uid[r]] = r;
     s->adj_override.clear();
+    s->graph_dirty = true;
+    s->max_deg = 0;
+    for (int r = 0; r < m; ++r) s->max_deg = std::max<int64_t>(s->max_deg, w->adj_ptr[r + 1] - w->adj_ptr[r]);
     s->row_direct.clear(); s->adj_direct.clear();
     {
         int64_t lo = INT64_MAX, hi = INT64_MIN;
@@ -2327,7 +2491,8 @@ int pk_recommend(pk_store* s, int mode, int nq, const int32_t* q_uid, int k, int
     if (k == 0) { for (int q = 0; q < nq; ++q) out_cnt[q] = 0; return PK_OK; }
     s->stat_scan_ns = 0; s->stat_scan_launches = 0; s->stat_pairs = 0; s->stat_groups = 0;
     std::vector<uint64_t> keys((size_t)nq * k, 0ull);
-    if (mode == PK_MODE_GRAPH) TRY(recommend_graph(s, nq, q_uid, k, limit, keys.data()));
+    if (device_lists_usable(s, mode, nq, limit)) TRY(recommend_lists_device(s, mode, nq, q_uid, k, limit, keys.data()));
+    else if (mode == PK_MODE_GRAPH) TRY(recommend_graph(s, nq, q_uid, k, limit, keys.data()));
     else if (mode == PK_MODE_COLLAB) TRY(recommend_collab(s, nq, q_uid, k, limit, keys.data()));
     else TRY(recommend_clubs(s, nq, q_uid, k, keys.data()));
     decode_keys(keys.data(), nq, k, out_id, out_score, out_cnt);
@@ -2345,6 +2510,24 @@ int pk_candidates(pk_store* s, int mode, int32_t uid, int limit, int32_t* out, i
     } else return fail(PK_ERR_ARG, "bad mode %d", mode);
     *n = (int64_t)c.size();
     for (int64_t i = 0; i < (int64_t)c.size() && i < cap; ++i) out[i] = c[i];
+    return PK_OK;
+}
+
+int pk_candidates_batch(pk_store* s, int mode, int nq, const int32_t* q_uid, int limit, int32_t* out_ids, int32_t* out_cnt) {
+    if (!s || nq < 0 || (nq > 0 && (!q_uid || !out_ids || !out_cnt))) return fail(PK_ERR_ARG, "bad argument");
+    if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
+    if (mode != PK_MODE_GRAPH && mode != PK_MODE_COLLAB) return fail(PK_ERR_ARG, "bad mode %d", mode);
+    if (limit < 1 || limit > 16384 || s->max_deg > 32768 || !s->adj_override.empty() || s->adj.size() > 0x7fffff00ull)
+        return fail(PK_ERR_UNSUPPORTED, "the device expansion takes limits in [1, 16384] on an adjacency without overridden rows");
+    if (nq == 0) return PK_OK;
+    CK(cudaSetDevice(s->device));
+    for (int q0 = 0; q0 < nq; q0 += 8192) {
+        const int m = std::min(8192, nq - q0);
+        TRY(expand_batch(s, mode, m, q_uid + q0, limit, true));
+        CK(cudaMemcpyAsync(out_ids + (size_t)q0 * limit, s->g_cand.p, (size_t)m * limit * 4, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaMemcpyAsync(out_cnt + q0, s->g_cnt.p, (size_t)m * 4, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+    }
     return PK_OK;
 }
 

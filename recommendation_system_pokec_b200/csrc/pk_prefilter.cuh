@@ -23,7 +23,7 @@ constexpr int kPreWarps = kPreThreads / 32;
 
 // one warp per row: lean record from the packed (exact) record
 __global__ void lean_pack_kernel(int n, const uint4* __restrict__ rec, const uint64_t* __restrict__ rec_off,
-                                 const uint64_t* __restrict__ lrec_off, uint4* __restrict__ lrec) {
+                                 const uint64_t* __restrict__ lrec_off, uint4* __restrict__ lrec, uint2* __restrict__ lmask) {
     const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (row >= n) return;
@@ -40,6 +40,7 @@ __global__ void lean_pack_kernel(int n, const uint4* __restrict__ rec, const uin
     if (lane == 10) out[10] = ntok;
     if (lane == 11) out[11] = r[14];
     if (lane == 12) out[12] = r[12];
+    if (lane == 16) lmask[row] = make_uint2(r[12], r[13]);     // the column masks again, 8 bytes per row (level-1 test)
     if (lane == 13) out[13] = r[13];
     if (lane == 14) out[14] = __float_as_uint(ncl ? (float)(1.0 / sqrt((double)ncl)) : 0.0f);
     if (lane == 15) out[15] = __float_as_uint(nfr ? (float)(1.0 / sqrt((double)nfr)) : 0.0f);
@@ -64,6 +65,7 @@ __global__ void lean_pack_kernel(int n, const uint4* __restrict__ rec, const uin
 struct PreParams {
     const uint4* lrec;
     const uint64_t* lrec_off;
+    const uint2* lmask;          // [row] 64-bit mask of non-empty text columns (8 bytes per candidate: the level-1 test)
     const GroupDesc* groups;
     const WorkItem* items;
     const uint8_t* arena;
@@ -103,11 +105,43 @@ __device__ __forceinline__ float lean_sigma(float4 c, float s) {
     return r;
 }
 
+// Level-1 bound of the header-only pruning: which counts j of jointly filled text columns could still reach theta
+// for this query, whatever the candidate's scalar fields are.  frow = {n, the largest sigmas of the query's own
+// n fixed / set fields, DESCENDING}: a candidate shares some subset of them -- for every subset size p the best
+// case is the top-p prefix -- plus j text columns at ub_text.  Writes the 64-bit mask of admissible j into q4->z/w
+// and the smallest bound among the admissible counts into *bnd (the mask is unchanged while theta stays below it).
+__device__ __noinline__ void l1_update(float th, const float* frow, float ub_text, float inv_total, volatile uint4* q4,
+                                       volatile float* bnd) {
+    const int nf = __float_as_int(frow[0]);
+    uint32_t lo = 0u, hi = 0u;
+    float nb = 3.0e38f;
+    for (int j = 0; j <= kMaxT; ++j) {
+        float pre = 0.f, best = 0.f;
+        for (int p = 0; p <= nf; ++p) {
+            const float sm = fmaf((float)j, ub_text, pre), u = (float)(p + j);
+            if (u > 0.f) {
+                const float S = sm / u, F = u * inv_total;
+                best = fmaxf(best, 2.0f * S * F / (S + F));
+            }
+            if (p < nf) pre += frow[1 + p];
+        }
+        best = best * (1.0f + 2e-6f) + 2e-6f;
+        if (best >= th) {
+            const int bit = min(j, 63);                 // j = 64 (T = 64, every column joint) shares bit 63
+            if (bit < 32) lo |= 1u << bit; else hi |= 1u << (bit - 32);
+            nb = fminf(nb, best);
+        }
+    }
+    q4->z = lo; q4->w = hi;
+    *bnd = nb;
+}
+
 // Warp-cooperative insertion of `key` into one query's descending shortlist (all lanes call it with the same
 // arguments; keys are unique -- one per candidate row).
 __device__ __forceinline__ void shortlist_insert(uint64_t* list, int K, uint64_t key, int* lock, volatile uint64_t* tau,
                                                  int lane, int k_user, float theta_drop, volatile float* theta,
-                                                 unsigned int* g_theta) {
+                                                 unsigned int* g_theta, const float* frow, float ub_text, float inv_total,
+                                                 volatile uint4* q4, volatile float* bnd) {
     if (lane == 0) {
         while (atomicCAS(lock, 0, 1) != 0) __nanosleep(32);
     }
@@ -135,6 +169,7 @@ __device__ __forceinline__ void shortlist_insert(uint64_t* list, int K, uint64_t
                 if (th > *theta) {
                     *theta = th;
                     if (g_theta) atomicMax(g_theta, __float_as_uint(th));
+                    if (th > *bnd) l1_update(th, frow, ub_text, inv_total, q4, bnd);
                 }
             }
         }
@@ -175,7 +210,10 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
     uint64_t* tau = lists + 32 * Ks;
     int* locks = reinterpret_cast<int*>(tau + 32);
     float* theta = reinterpret_cast<float*>(locks + 32);                            // [32] pruning thresholds
-    int* next = reinterpret_cast<int*>(theta + 32);
+    uint4* l1q = reinterpret_cast<uint4*>(theta + 32);                              // [32] {query mask lo, hi, jmin, -}
+    float* l1f = reinterpret_cast<float*>(l1q + 32);                                // [32][8] {n, largest sigmas descending}
+    float* l1b = l1f + 32 * 8;                                                      // [32] theta up to which l1q[].z/w hold
+    int* next = reinterpret_cast<int*>(l1b + 32);
     uint4* stage = reinterpret_cast<uint4*>(next + 4) + warp * 32;                  // per-warp hit staging
     int* pick = next + 1;                                                           // {group index, instance}
 
@@ -266,14 +304,38 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
     const int dim_comp = N->dim_comp, dim_age = N->dim_age;
     const float inv_total = N->inv_total;
     const float ub_text = N->ub_text, ub_clubs = N->ub_clubs, ub_friends = N->ub_friends;
+    if (!STORE && warp == 0) {
+        // level-1 tables of the group: the query's column mask, and the largest sigma of each fixed / set field the
+        // query has (a candidate can only share those), sorted descending for jmin_of
+        float fm[7];
+        int nfm = 0;
+        if (q_active) {
+            const float e = 2e-6f;
+            if (q_pub >= 0) fm[nfm++] = fmaxf(N->fld[0].z, N->fld[0].w) + e;
+            if (q_gender >= 0) fm[nfm++] = fmaxf(N->fld[1].z, N->fld[1].w) + e;
+            if (q_comp > 0) fm[nfm++] = fmaxf(N->fld[2].z, N->fld[2].w) + e;
+            if (q_age > 0) fm[nfm++] = fmaxf(N->fld[3].z, N->fld[3].w) + e;
+            if (q_acnt > 0) fm[nfm++] = fmaxf(N->fld[4].z, N->fld[4].w) + e;
+            if (q_ncl > 0) fm[nfm++] = ub_clubs;
+            if (q_nfr > 0) fm[nfm++] = ub_friends;
+            for (int a = 1; a < nfm; ++a)
+                for (int b = a; b > 0 && fm[b] > fm[b - 1]; --b) { const float t = fm[b]; fm[b] = fm[b - 1]; fm[b - 1] = t; }
+        }
+        l1f[lane * 8] = __int_as_float(nfm);
+        for (int a = 0; a < 7; ++a) l1f[lane * 8 + 1 + a] = (a < nfm) ? fm[a] : 0.f;
+        l1q[lane] = q_active ? make_uint4(q_m0, q_m1, 0xffffffffu, 0xffffffffu) : make_uint4(0u, 0u, 0u, 0u);
+        l1b[lane] = q_active ? 0.f : 3.0e38f;        // theta = 0: every count admissible
+    }
+    __syncthreads();
     unsigned int* const g_theta = STORE ? nullptr : P.dyn_theta + (size_t)pick[0] * 32 + lane;
     float th_g = 0.f;               // the group's published threshold, re-read once per chunk
 
 #ifdef PK_PRE_CHUNK
     constexpr int kChunk = PK_PRE_CHUNK;
 #else
-    constexpr int kChunk = 8;
+    constexpr int kChunk = 32;
 #endif
+    static_assert(kChunk <= 32, "a chunk is tested one candidate per lane");
     // the claim of the NEXT chunk is issued before the current one is scored: the cursor of the dynamic schedule
     // lives in global memory (shared by the CTAs working on the group) and its latency must not stall the warp
     int c_next = 0;
@@ -282,12 +344,39 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
         const int c0 = __shfl_sync(kFull, c_next, 0);
         if (c0 >= it.cand_end) break;
         if (lane == 0) c_next = cursor_base + atomicAdd(cursor, kChunk);
-        if (!STORE) th_g = __uint_as_float(*reinterpret_cast<volatile unsigned int*>(g_theta));
         const int c1 = min(c0 + kChunk, it.cand_end);
         uint64_t offv = 0;
-        if (c0 + lane < c1) offv = __ldg(P.lrec_off + c0 + lane);
-        for (int ci = c0; ci < c1; ++ci) {
-            const uint64_t off = __shfl_sync(kFull, offv, ci - c0);
+        uint2 cm = make_uint2(0u, 0u);
+        if (c0 + lane < c1) { offv = __ldg(P.lrec_off + c0 + lane); if (!STORE) cm = __ldg(P.lmask + c0 + lane); }
+        uint32_t surv = (c1 - c0 >= 32) ? kFull : ((1u << (c1 - c0)) - 1u);
+        if (!STORE) {
+            // thresholds published by the other instances of the group
+            th_g = __uint_as_float(*reinterpret_cast<volatile unsigned int*>(g_theta));
+            if (th_g > reinterpret_cast<volatile float*>(theta)[lane]) {
+                reinterpret_cast<volatile float*>(theta)[lane] = th_g;
+                if (th_g > reinterpret_cast<volatile float*>(l1b)[lane])
+                    l1_update(th_g, l1f + lane * 8, ub_text, inv_total, reinterpret_cast<volatile uint4*>(l1q) + lane,
+                              reinterpret_cast<volatile float*>(l1b) + lane);
+            }
+            __syncwarp();
+            // level 1, lane = candidate: can ANY query of the group still want it, judged by the number of jointly
+            // filled text columns alone?  (8 bytes per candidate; two thirds of the candidates end here)
+            bool any = false;
+            const int nl = gd->n_lanes;
+            #pragma unroll 4
+            for (int q = 0; q < nl; ++q) {
+                const uint4 qq = l1q[q];        // (re-read every chunk: the __syncwarp above orders it after the updates)
+                const int j = min(__popc(qq.x & cm.x) + __popc(qq.y & cm.y), 63);
+                const uint64_t adm = ((uint64_t)qq.w << 32) | qq.z;
+                any = any || ((adm >> j) & 1ull);
+            }
+            surv &= __ballot_sync(kFull, any);
+        }
+        while (surv) {
+            const int si = __ffs(surv) - 1;
+            surv &= surv - 1;
+            const int ci = c0 + si;
+            const uint64_t off = __shfl_sync(kFull, offv, si);
             const uint4* cr = P.lrec + off;
             const uint32_t* cw = reinterpret_cast<const uint32_t*>(cr);
             const uint4 h0 = __ldg(cr), h1 = __ldg(cr + 1), h2 = __ldg(cr + 2), h3 = __ldg(cr + 3);
@@ -463,7 +552,9 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                         pass &= pass - 1;
                         const uint64_t kj = __shfl_sync(kFull, key, j);
                         shortlist_insert(lists + j * Ks, Ks, kj, locks + j, reinterpret_cast<volatile uint64_t*>(tau) + j, lane, P.K,
-                                         P.theta_drop, reinterpret_cast<volatile float*>(theta) + j, g_theta - lane + j);
+                                         P.theta_drop, reinterpret_cast<volatile float*>(theta) + j, g_theta - lane + j,
+                                         l1f + j * 8, ub_text, inv_total, reinterpret_cast<volatile uint4*>(l1q) + j,
+                                         reinterpret_cast<volatile float*>(l1b) + j);
                     }
                 }
             }

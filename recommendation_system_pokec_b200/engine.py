@@ -26,7 +26,7 @@ ABI_SYMBOLS = (
     "pk_idf_size", "pk_get_idf", "pk_set_adj_row", "pk_pair_similarity", "pk_pair_fields", "pk_pair_overlap",
     "pk_fullscan_topk", "pk_fullscan_prepare", "pk_fullscan_execute", "pk_fullscan_fetch", "pk_fullscan_keys", "pk_recommend", "pk_candidates", "pk_fullscan_local_keys", "pk_merge_keys", "pk_sync",
     "pk_normalizers_from_pairs", "pk_edge_cache_build", "pk_edge_cache_drop", "pk_edge_cache_row", "pk_fullscan_execute_shortlists", "pk_fullscan_shortlist_keys", "pk_fullscan_execute_finish",
-    "pk_stream", "pk_stat", "pk_debug_prefilter", "pk_world_save", "pk_world_open", "pk_world_close",
+    "pk_stream", "pk_stat", "pk_debug_prefilter", "pk_world_save", "pk_world_open", "pk_world_close", "pk_candidates_batch",
 )
 STAT_KERNEL_LAUNCHES, STAT_PAIRS_SCORED, STAT_STORE_BYTES, STAT_SCAN_KERNEL_NS, STAT_SCAN_LAUNCHES, STAT_GROUPS, \
     STAT_SHARD_RECORD_BYTES, STAT_H2D_BYTES, STAT_D2H_BYTES, STAT_PREFILTER, STAT_FALLBACK_QUERIES, STAT_RESCORE_NS, \
@@ -326,6 +326,14 @@ class DeviceRecommender:
         n = C.c_int64()
         _check(self.lib, self.lib.pk_candidates(self.h, int(mode), int(user), int(limit), ptr(out, i32p), C.c_int64(cap), C.byref(n)))
         return out[:min(int(n.value), cap)].copy()
+
+    def candidates_batch(self, mode, users, limit):
+        """raw candidate lists of many users, expanded on the device -> (ids [nq][limit], counts [nq])"""
+        q = np.ascontiguousarray(users, np.int32)
+        ids = np.full((len(q), int(limit)), -1, np.int32)
+        cnt = np.zeros(len(q), np.int32)
+        _check(self.lib, self.lib.pk_candidates_batch(self.h, int(mode), len(q), ptr(q, i32p), int(limit), ptr(ids, i32p), ptr(cnt, i32p)))
+        return ids, cnt
 
     # ---- multi-GPU plumbing --------------------------------------------------------------------------
     def fullscan_local_keys(self, q, k, exclude_mode, d_keys_ptr: int):

@@ -231,3 +231,49 @@ def test_prepared_scan_is_refused_after_a_setter(small_world):
     for x, y in zip(ref, again):
         assert np.array_equal(x, y)
     dev.close()
+
+
+def test_device_expansion_equals_host_lists(small_world, gap_world, oracle_libs):
+    """the friend-of-friend expansion on the device (pk_candidates_batch: adjacency CSR in HBM, one
+    warp per user, ordered de-duplication + truncation) against the host walk (pk_candidates) and the restatement --
+    every list bit for bit, at limits that truncate (1, 17), that do not (5000, 10000), on dense and on gapped uids,
+    with neighbours that have no profile, self loops and duplicated neighbours."""
+    from oracle.oracle import CpuOracle
+    worlds = [small_world, gap_world, duplicate_world()[0]]
+    hub_w, hub = hub_world()
+    for wi, w in enumerate(worlds + [hub_w]):
+        dev, port = _dev(w), CpuOracle(w, "port", compute_idf=False)
+        users = sample_queries(w, 300, seed=60 + wi)
+        if w is hub_w:
+            users = np.concatenate([[hub], users[:40]]).astype(np.int32)
+        users = np.concatenate([users, np.array([-7, 2_000_000_001], np.int32)])          # unknown users: empty lists
+        for mode in (MODE_GRAPH, MODE_COLLAB):
+            for limit in (1, 17, 401, 5000, 10000):
+                ids, cnt = dev.candidates_batch(mode, users, limit)
+                for qi, u in enumerate(users):
+                    want = dev.candidates(mode, int(u), limit)
+                    assert cnt[qi] == len(want) and np.array_equal(ids[qi, :cnt[qi]], want), (wi, mode, limit, int(u))
+                for qi in (0, 5, 11):
+                    assert np.array_equal(ids[qi, :cnt[qi]], port.candidates(mode, int(users[qi]), limit))
+        dev.close()
+        port.close()
+
+
+def test_batched_list_modes_device_pipeline_equals_host_pipeline(small_world, oracle_libs, monkeypatch):
+    """pk_recommend on a batch (device expansion -> lane-per-pair FAS -> reduce -> selection) against the host
+    enumeration path (POKEC_B200_HOST_LISTS=1, the path single-user drop-in calls take) and the oracle"""
+    w = small_world
+    dev, orc = _dev(w), best_oracle(w)
+    q = np.concatenate([sample_queries(w, 200, seed=77), np.array([-1, 123456789], np.int32)])
+    for mode in (MODE_GRAPH, MODE_COLLAB):
+        for k, limit in ((50, 5000), (20, 40), (300, 10000)):
+            monkeypatch.delenv("POKEC_B200_HOST_LISTS", raising=False)
+            a = dev.recommend(mode, q, k, limit)
+            monkeypatch.setenv("POKEC_B200_HOST_LISTS", "1")
+            b = dev.recommend(mode, q, k, limit)
+            monkeypatch.delenv("POKEC_B200_HOST_LISTS")
+            for x, y in zip(a, b):
+                assert np.array_equal(x, y), (mode, k, limit)
+            assert_topk_equal(a, orc.recommend(mode, q, k, limit, NT), f"device pipeline mode {mode} k={k} limit={limit}")
+    dev.close()
+    orc.close()
