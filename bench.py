@@ -458,12 +458,6 @@ def main():
     def device_step():
         return scan_and_exchange(False)
 
-    def e2e_step():
-        if world_size == 1:
-            return dev.fullscan(q, k, EXCLUDE_SELF_AND_ADJ)
-        dev.fullscan_prepare(q, k, EXCLUDE_SELF_AND_ADJ)     # host planning + H2D of the plan, every step
-        return scan_and_exchange(True)
-
     def barrier():
         dev.sync()
         torch.cuda.synchronize()
@@ -504,20 +498,17 @@ def main():
                  "rescore_ms": max_over_ranks(dev.stat(engine.STAT_RESCORE_NS) / 1e6)}
 
     # ---- end to end: host uids in, host top-k out, every step -------------------------------------
-    for _ in range(1):
-        e2e_step()
-    barrier()
-    h2d0, d2h0 = dev.stat(engine.STAT_H2D_BYTES), dev.stat(engine.STAT_D2H_BYTES)
-    t = time.perf_counter()
-    for _ in range(args.steps):
-        res = e2e_step()
-    barrier()
-    e2e_s = max_over_ranks(time.perf_counter() - t)
-    h2d = (dev.stat(engine.STAT_H2D_BYTES) - h2d0) // args.steps + q.nbytes
-    d2h = (dev.stat(engine.STAT_D2H_BYTES) - d2h0) // args.steps
-    e2e_value = nq * args.steps / e2e_s
+    # The public calls with HOST buffers, every step: host planning, H2D of the plan + exclusion ids, the kernels, both
+    # all-gathers (N > 1), D2H of the merged keys, decode.  Two batches are kept in flight on two stores / streams (as the
+    # all-users sweep does): the host planning of step i + 1 overlaps the scan of step i.
+    from tools.bench_allusers import sweep
+    e2e_stats = {}
+    e2e_value, e2e_s, kept = sweep(world, world_size, rank, local_rank, nq, k, args.steps, depth=2, keep_batches=(args.steps - 1,),
+                                   batch_fn=lambda b: q, stats=e2e_stats)
+    res = kept[-1][1]
+    h2d, d2h = e2e_stats["h2d_bytes_per_batch"], e2e_stats["d2h_bytes_per_batch"]
     assert res is not None and int(res[2].min()) == k, "e2e step returned incomplete top-k lists"
-    fallback_q = dev.stat(engine.STAT_FALLBACK_QUERIES)
+    fallback_q = e2e_stats["fallback_queries_last"]
 
     # one more (untimed) step with marks around the host planning and the two all-gathers
     t = time.perf_counter()
@@ -582,7 +573,7 @@ def main():
            "dtype": "f32 pre-filter + f64 exact re-score (every returned score is the f64 path's)", "data": "synthetic",
            "config": config, "clocks": clocks,
            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                   "ms_per_step": e2e_s / args.steps * 1e3},
+                   "ms_per_step": e2e_s / args.steps * 1e3, "batches_in_flight": 2},
            "gpu_launches": int(launches), "roofline": roofline, "breakdown": breakdown,
            "pipeline": {"two_stage": two_stage, "shortlist": dev.stat(engine.STAT_SHORTLIST),
                         "prefilter_margin": dev.stat(engine.STAT_MARGIN_E9) / 1e9,

@@ -40,6 +40,7 @@ struct ClubParams {
 __global__ void __launch_bounds__(kClubThreads) clubs_scatter_kernel(const ClubParams P) {
     const int u = blockIdx.x, tid = threadIdx.x;
     const int eb = P.user_edge_begin[u], ee = P.user_edge_begin[u + 1];
+    if (eb == ee) return;                 // no entries (unknown user, no profiled friend): the slice stays empty
     const int sb = P.user_slot_begin[u];
     const uint32_t cap = (uint32_t)(P.user_slot_begin[u + 1] - sb);
     const uint32_t msk = cap - 1u;

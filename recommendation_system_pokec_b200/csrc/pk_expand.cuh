@@ -84,6 +84,7 @@ struct ExpandParams {
     int mode;                        // PK_MODE_GRAPH: gather_candidates_local; PK_MODE_COLLAB / PK_MODE_CLUBS: friends' friends
     int limit;                       // >= 1
     int raw;                         // 1 = emit the raw expansion (uids) without the profile / friend filters (pk_candidates_batch)
+    int slots_only;                  // 1 = only number the friends (recommend_clubs_collab enumerates edges, not candidates)
     unsigned long long* scratch;     // [warps][tab_cap] persistent across launches
     uint32_t* epoch;                 // [warps] last epoch used
     uint32_t tab_cap;                // power of two >= 2 (limit + 32) and >= 2 (max friends of a query) -- see the host
@@ -167,6 +168,7 @@ __global__ void __launch_bounds__(kExpWarps * 32) expand_kernel(const ExpandPara
             if (lane == 0) P.n_slots[q] = ns;
         }
 
+        if (P.slots_only) continue;
         // ---- candidate expansion: first `limit` first-occurrences of the reference's visiting sequence ----
         next_epoch();
         int count = 0;
@@ -356,6 +358,149 @@ __global__ void __launch_bounds__(128) collab_reduce2_kernel(const CollabReduce2
             score = __dadd_rn(score, __dmul_rn((double)w[sl], (double)mat[(int64_t)c * ns + sl]));
         }
         P.out_keys[c0 + c] = make_key(__float_as_uint((float)score), P.key_id[c0 + c]);
+    }
+}
+
+// ---- clubs (src/recommender_clubs.cpp:23-64): every user's ordered edge stream, built on the device ----------
+// 1-hop entries (every friend entry whose friend has a profile, :34-43), then 2-hop entries (for every such friend
+// with an adjacency row, every neighbour != user that has a profile, :45-64), each with the indices of the FAS values
+// it needs and the offset of its club contributions.  COUNT pass: sizes per user; FILL pass: the stream itself and
+// the (A, B) pairs the lane-per-pair kernel scores (none when the per-edge FAS cache serves them).
+struct ClubsPlanParams {
+    DevGraph G;
+    const int32_t* q_uid;
+    int nq;
+    const int32_t *q_row, *n_slots, *q_adj_off, *q_deg, *fr_slot, *slot_row;     // from expand_kernel
+    const uint32_t* ncl;             // [n] clubs per profile row
+    int cached;                      // FAS values come from the per-edge cache: indices are adjacency offsets
+    int32_t* n_edges;                // COUNT out [nq]
+    int32_t* n_two;                  // COUNT out [nq] 2-hop entries
+    unsigned long long* n_con;       // COUNT out [nq] club contributions
+    const int32_t* edge_off;         // FILL in [nq + 1]
+    const int64_t* pair_off;         // FILL in [nq + 1]
+    ClubEdge* edges;                 // FILL out
+    uint32_t* con_off;               // FILL out, per edge, relative to the user
+    int32_t *a_row, *b_row;          // FILL out (not cached)
+};
+
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, int lane) {
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(kExpFull, v, o); if (lane >= o) v += t; }
+    return v;
+}
+
+template <bool FILL>
+__global__ void __launch_bounds__(kExpWarps * 32) clubs_plan_kernel(const ClubsPlanParams P) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t lane_lt = (1u << lane) - 1u;
+    const DevGraph& G = P.G;
+    for (int q = blockIdx.x * kExpWarps + (threadIdx.x >> 5); q < P.nq; q += gridDim.x * kExpWarps) {
+        const int urow = P.q_row[q], deg = P.q_deg[q], ns = P.n_slots[q];
+        const int64_t ub = P.q_adj_off[q];
+        int ne = 0, n2 = 0;
+        unsigned long long con = 0ull;
+        if (urow >= 0 && ub >= 0 && deg > 0 && ns > 0) {
+            const int32_t user = P.q_uid[q];
+            const int64_t e0 = FILL ? P.edge_off[q] : 0, p0 = FILL ? P.pair_off[q] : 0;
+            if (FILL && !P.cached)
+                for (int s = lane; s < ns; s += 32) { P.a_row[p0 + s] = urow; P.b_row[p0 + s] = P.slot_row[ub + s]; }
+            // 1-hop
+            for (int i0 = 0; i0 < deg; i0 += 32) {
+                const int i = i0 + lane;
+                const int sl = (i < deg) ? P.fr_slot[ub + i] : -1;
+                const bool valid = sl >= 0;
+                const int tr = valid ? P.slot_row[ub + sl] : 0;
+                const uint32_t c = valid ? __ldg(P.ncl + tr) : 0u;
+                const uint32_t vm = __ballot_sync(kExpFull, valid);
+                const uint32_t inc = warp_incl_scan(c, lane);
+                if (FILL && valid) {
+                    const int pos = ne + __popc(vm & lane_lt);
+                    ClubEdge ed;
+                    ed.w_idx = P.cached ? ub + i : p0 + sl; ed.s_idx = -1; ed.target_row = tr; ed.pad_ = 0;
+                    P.edges[e0 + pos] = ed;
+                    P.con_off[e0 + pos] = (uint32_t)min(con + inc - c, 0xffffffffull);
+                }
+                ne += __popc(vm);
+                con += __shfl_sync(kExpFull, inc, 31);
+            }
+            // 2-hop
+            for (int i = 0; i < deg; ++i) {
+                const int sl = P.fr_slot[ub + i];
+                if (sl < 0) continue;                                         // no profile (:49)
+                const int32_t f = __ldg(G.adj + ub + i);
+                const int fa = dg_adj_row(G, f);
+                if (fa < 0) continue;                                         // no adjacency row (:47)
+                const int64_t fb = G.adj_ptr[fa];
+                const int fdeg = (int)(G.adj_ptr[fa + 1] - fb);
+                const int frow = P.slot_row[ub + sl];
+                for (int j0 = 0; j0 < fdeg; j0 += 32) {
+                    const int j = j0 + lane;
+                    int rx = -1;
+                    if (j < fdeg) { const int32_t x = __ldg(G.adj + fb + j); if (x != user) rx = dg_row(G, x); }   // :53-55
+                    const bool valid = rx >= 0;
+                    const uint32_t c = valid ? __ldg(P.ncl + rx) : 0u;
+                    const uint32_t vm = __ballot_sync(kExpFull, valid);
+                    const uint32_t inc = warp_incl_scan(c, lane);
+                    if (FILL && valid) {
+                        const int k2 = n2 + __popc(vm & lane_lt);
+                        ClubEdge ed;
+                        ed.w_idx = P.cached ? ub + i : p0 + sl;
+                        ed.s_idx = P.cached ? fb + j : p0 + ns + k2;
+                        ed.target_row = rx; ed.pad_ = 0;
+                        P.edges[e0 + ne + k2 - n2 + 0] = ed;
+                        P.con_off[e0 + ne + k2 - n2] = (uint32_t)min(con + inc - c, 0xffffffffull);
+                        if (!P.cached) { P.a_row[p0 + ns + k2] = frow; P.b_row[p0 + ns + k2] = rx; }
+                    }
+                    const int add = __popc(vm);
+                    ne += add; n2 += add;
+                    con += __shfl_sync(kExpFull, inc, 31);
+                }
+            }
+        }
+        if (!FILL && lane == 0) { P.n_edges[q] = ne; P.n_two[q] = n2; P.n_con[q] = con; }
+    }
+}
+
+// offsets of the clubs plan: edges, pairs (n_slots + 2-hop entries per user unless cached) and the per-user club
+// table slices (power of two >= 2 x contributions, as the scatter kernel expects)
+__global__ void __launch_bounds__(1024) clubs_offsets_kernel(int nq, int cached, const int32_t* __restrict__ n_edges,
+                                                             const int32_t* __restrict__ n_two, const int32_t* __restrict__ n_slots,
+                                                             const unsigned long long* __restrict__ n_con, int32_t* __restrict__ edge_off,
+                                                             int64_t* __restrict__ pair_off, int32_t* __restrict__ slot_begin,
+                                                             int64_t* __restrict__ totals) {
+    __shared__ long long ws[3][32];
+    __shared__ long long run[3];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid < 3) run[tid] = 0;
+    __syncthreads();
+    for (int base = 0; base < nq; base += 1024) {
+        const int q = base + tid;
+        long long v[3] = {0, 0, 0};
+        if (q < nq) {
+            v[0] = n_edges[q];
+            v[1] = (cached || n_edges[q] == 0) ? 0 : (long long)n_slots[q] + n_two[q];
+            unsigned long long c = n_con[q] < 1ull ? 1ull : n_con[q], cap = 2;
+            while (cap < 2 * c) cap <<= 1;
+            v[2] = (long long)cap;
+        }
+        long long inc[3] = {v[0], v[1], v[2]};
+        for (int o = 1; o < 32; o <<= 1)
+            for (int k = 0; k < 3; ++k) { const long long t = __shfl_up_sync(0xffffffffu, inc[k], o); if (lane >= o) inc[k] += t; }
+        if (lane == 31) for (int k = 0; k < 3; ++k) ws[k][warp] = inc[k];
+        __syncthreads();
+        long long off[3] = {run[0], run[1], run[2]};
+        for (int w = 0; w < warp; ++w) for (int k = 0; k < 3; ++k) off[k] += ws[k][w];
+        if (q < nq) {
+            edge_off[q] = (int32_t)min(off[0] + inc[0] - v[0], 0x7fffffffll);
+            pair_off[q] = off[1] + inc[1] - v[1];
+            slot_begin[q] = (int32_t)min(off[2] + inc[2] - v[2], 0x7fffffffll);
+        }
+        __syncthreads();
+        if (tid == 1023) for (int k = 0; k < 3; ++k) run[k] = off[k] + inc[k];
+        __syncthreads();
+    }
+    if (tid == 0) {
+        edge_off[nq] = (int32_t)min(run[0], 0x7fffffffll); pair_off[nq] = run[1]; slot_begin[nq] = (int32_t)min(run[2], 0x7fffffffll);
+        totals[0] = run[0]; totals[1] = run[1]; totals[2] = run[2];
     }
 }
 

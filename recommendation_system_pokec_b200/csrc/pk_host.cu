@@ -135,6 +135,8 @@ struct FullscanJob {
     int n_dyn = 0, n_slices = 1, sm_count = 148;
     int64_t cand_begin = 0, cand_end = 0;     // the shard the job was planned for
     DevBuf<int32_t> q_group, q_flag, q_flag0, group_flag, group_flag0, short_rows, rr_slot0, rr_nl, pre_slot0, pre_nl;
+    DevBuf<int32_t> rs_a, rs_b, rs_id, rs_seg;  // exact re-score of the shortlists as (query, candidate) pairs: [nq][Ks]
+    DevBuf<float> rs_f;
     DevBuf<int32_t> lean_fail;                // [group] the pre-filter's token table could not be built -> exact scan
 };
 
@@ -236,7 +238,10 @@ struct pk_store {
     int g_warps = 0;
     DevBuf<int32_t> g_fr_slot, g_slot_row;           // [E] per adjacency entry of a queried user
     DevBuf<int32_t> g_qrow, g_cand, g_cnt, g_nslots, g_qoff, g_qdeg, g_cand_off, g_next;
-    DevBuf<int64_t> g_pair_off;
+    DevBuf<int64_t> g_pair_off, g_totals;
+    DevBuf<uint32_t> g_ncl;
+    DevBuf<int32_t> g_nedges, g_ntwo, g_edge_off, g_slot_begin;
+    DevBuf<unsigned long long> g_ncon;
     FullscanJob job;
     // bumped by every call that changes what a prepared full-scan plan depends on (world, shard, normalizers, idf,
     // adjacency overrides): a plan stamped with an older value is refused by execute / finish / fetch / keys
@@ -795,6 +800,10 @@ int check_topk_args(pk_store* s, int nq, const int32_t* q_uid, int k, int max_k 
     return PK_OK;
 }
 
+template <bool FIELDS>
+int pairs_launch(pk_store* s, int64_t n, const int32_t* d_a_row, const int32_t* d_b_row, float* d_out_f, float* d_out_fields,
+                 const int32_t* d_key_id, uint64_t* d_out_keys, bool timed = true);
+
 // ---- full scan ---------------------------------------------------------------------------------------
 // prepare: host planning + upload (queries -> groups -> work items); execute: arena clear, group_prep,
 // scan, merge -- all asynchronous on the store's stream, device-resident inputs only; fetch: D2H + decode.
@@ -1003,6 +1012,14 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
         TRY(J.keys_rr.reserve(std::max<size_t>(rr.size(), 1) * 32 * (size_t)Kp));
         J.n_rr = rr.size();
         TRY(J.short_rows.reserve((size_t)ng * 32 * Ks));
+        {
+            std::vector<int32_t> seg((size_t)nq + 1);
+            for (int q = 0; q <= nq; ++q) seg[(size_t)q] = q * Ks;
+            TRY(upload(s, J.rs_seg, seg));
+            TRY(J.rs_a.reserve((size_t)nq * Ks)); TRY(J.rs_b.reserve((size_t)nq * Ks)); TRY(J.rs_id.reserve((size_t)nq * Ks));
+            TRY(J.rs_f.reserve((size_t)nq * Ks));
+            TRY(J.keys_rr.reserve((size_t)nq * Ks));
+        }
     }
     CK(cudaStreamSynchronize(s->stream));
     J.valid = true;
@@ -1135,26 +1152,24 @@ int fullscan_finish(pk_store* s, const uint64_t* d_all_short, int n_lists, int r
     CheckParams C;
     C.short_keys = short_keys; C.q_group = J.q_group.p; C.q_lane = J.q_lane.p; C.cand_rows = J.short_rows.p;
     C.q_flag = J.q_flag.p; C.group_flag = J.group_flag.p; C.lean_fail = J.lean_fail.p; C.nq = J.nq; C.K = J.K; C.Ks = Ks; C.margin = s->margin;
+    // the candidates that can still reach the top-k become (query, candidate) pairs of the lane-per-pair kernel;
+    // with several ranks each rank re-scores the query groups it owns (the others' slots stay empty)
+    CK(cudaMemsetAsync(J.rs_b.p, 0xFF, (size_t)J.nq * Ks * 4, s->stream));       // queries without a profile write nothing
+    C.pa_row = J.rs_a.p; C.pb_row = J.rs_b.p; C.pkey_id = J.rs_id.p; C.uid = s->d_uid.p; C.groups = J.groups.p;
+    C.own_lo = (int)((int64_t)J.n_groups * rank / n_ranks); C.own_hi = (int)((int64_t)J.n_groups * (rank + 1) / n_ranks);
     shortlist_check_kernel<<<J.nq, 64, 0, s->stream>>>(C);
     ++s->stat_launches;
     CK(cudaGetLastError());
     // 3. exact arithmetic on the shortlists; 4. exact full scan for the groups with a flagged query
     CK(cudaEventRecord(s->ev2, s->stream));
-    ScanParams R = P;
-    R.cand_rows = J.short_rows.p; R.out_keys = J.keys_rr.p;
-    if (n_ranks > 1) {   // groups of other ranks are not re-scored here: their lists must read as empty
-        R.group_lo = (int)((int64_t)J.n_groups * rank / n_ranks);
-        R.group_hi = (int)((int64_t)J.n_groups * (rank + 1) / n_ranks);
-        CK(cudaMemsetAsync(J.keys_rr.p, 0, J.n_rr * 32 * (size_t)J.Kp * 8, s->stream));
-    }
-    TRY((launch_scan_plain<EPI_TOPK, false>(s, R, J.rr_items.p, J.n_rr_sm, J.n_rr_gl, J.max_smem_arena)));
+    TRY((pairs_launch<false>(s, (int64_t)J.nq * Ks, J.rs_a.p, J.rs_b.p, J.rs_f.p, nullptr, J.rs_id.p, J.keys_rr.p, false)));
     ScanParams F = P;
     F.out_keys = J.keys_a.p; F.group_flag = J.group_flag.p;
     TRY((launch_scan_plain<EPI_TOPK, false>(s, F, J.items.p, J.n_sm, J.n_gl, J.max_smem_arena)));
     CK(cudaEventRecord(s->ev3, s->stream));
     s->rescore_time_pending = true;
     // 5. final merge: the re-scored shortlist, or the full exact scan where the shortlist was not proven
-    M.keys = J.keys_rr.p; M.slot0 = J.rr_slot0.p; M.n_lists_q = J.rr_nl.p; M.stride_k = J.Kp;
+    M.keys = J.keys_rr.p; M.seg_begin = J.rs_seg.p;
     M.q_flag = J.q_flag.p; M.alt_keys = J.keys_a.p; M.alt_slot0 = J.q_slot0.p; M.alt_n_lists_q = J.q_nl.p; M.alt_stride_k = J.Kp;
     TRY(launch_merge(s, M, J.nq));
     CK(cudaEventRecord(s->pev[5], s->stream));
@@ -1265,10 +1280,6 @@ GroupDesc empty_group() {
 // recommend_graph_registration == recommend_by_interest (src/recommender_graph.cpp:33-103,224-227): every
 // (query, candidate) of the batch is one pair of the lane-per-pair kernel, which also emits the sort keys; the
 // sort-based selection then takes each query's top-k from its slice (any k: src/test.cpp:75 passes |friends| / 5).
-template <bool FIELDS>
-int pairs_launch(pk_store* s, int64_t n, const int32_t* d_a_row, const int32_t* d_b_row, float* d_out_f, float* d_out_fields,
-                 const int32_t* d_key_id, uint64_t* d_out_keys);
-
 int recommend_graph(pk_store* s, int nq, const int32_t* q_uid, int k, int limit, uint64_t* h_keys) {
     const int K = std::max(k, 1);
     // phase 1 (host threads): the candidate rows of every query, in the reference's order
@@ -1346,6 +1357,7 @@ int ensure_graph(pk_store* s) {
     }
     const size_t E = std::max<size_t>(s->adj.size(), 1);
     TRY(s->g_fr_slot.reserve(E)); TRY(s->g_slot_row.reserve(E));
+    TRY(upload(s, s->g_ncl, s->h_ncl));
     CK(cudaStreamSynchronize(s->stream));
     s->graph_dirty = false;
     return PK_OK;
@@ -1370,7 +1382,6 @@ DevGraph dev_graph(pk_store* s) {
 // set stays small; single-user drop-in calls keep the host walk (they must read the caller's LIVE adjacency)
 bool device_lists_usable(pk_store* s, int mode, int nq, int limit) {
     if (const char* e = getenv("POKEC_B200_HOST_LISTS")) if (e[0] == '1') return false;
-    if (mode == PK_MODE_CLUBS) return false;
     if (!s->adj_override.empty() || nq < 16) return false;
     if (limit < 1 || limit > 16384 || s->max_deg > 32768) return false;
     if (s->adj.size() > 0x7fffff00ull) return false;
@@ -1378,7 +1389,7 @@ bool device_lists_usable(pk_store* s, int mode, int nq, int limit) {
 }
 
 // expansion of a batch: fills g_qrow / g_cand / g_cnt (+ friend slots for the collaborative mode)
-int expand_batch(pk_store* s, int mode, int nq, const int32_t* q_uid, int limit, bool raw) {
+int expand_batch(pk_store* s, int mode, int nq, const int32_t* q_uid, int limit, bool raw, bool slots_only = false) {
     TRY(ensure_graph(s));
     uint32_t cap = 1024;
     while (cap < 2u * (uint32_t)(limit + 32) || cap < 2u * (uint32_t)(s->max_deg + 32)) cap <<= 1;
@@ -1401,7 +1412,7 @@ int expand_batch(pk_store* s, int mode, int nq, const int32_t* q_uid, int limit,
     ExpandParams X;
     memset(&X, 0, sizeof(X));
     X.G = dev_graph(s);
-    X.q_uid = s->d_i32e.p; X.nq = nq; X.mode = mode; X.limit = limit; X.raw = raw ? 1 : 0;
+    X.q_uid = s->d_i32e.p; X.nq = nq; X.mode = mode; X.limit = limit; X.raw = raw ? 1 : 0; X.slots_only = slots_only ? 1 : 0;
     X.scratch = s->g_scratch.p; X.epoch = s->g_epoch.p; X.tab_cap = cap; X.next_query = s->g_next.p; X.cand_cap = limit;
     X.q_row = s->g_qrow.p; X.cand_out = s->g_cand.p; X.cand_cnt = s->g_cnt.p;
     if (mode != PK_MODE_GRAPH) {
@@ -1461,6 +1472,71 @@ int recommend_lists_device(pk_store* s, int mode, int nq, const int32_t* q_uid, 
             CK(cudaGetLastError());
         }
         TRY(launch_slice_topk(s, s->d_keys_a.p, s->g_cand_off.p, m, K, s->d_keys_b.p));
+        CK(cudaMemcpyAsync(keys.data() + (size_t)q0 * K, s->d_keys_b.p, (size_t)m * K * 8, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+        TRY(collect_scan_time(s));
+    }
+    memcpy(h_keys, keys.data(), (size_t)nq * K * 8);
+    return PK_OK;
+}
+
+// recommend_clubs_collab for a batch, the edge stream built on the device (clubs_plan_kernel); the FAS values come
+// from the per-edge cache when it is valid, else from the lane-per-pair kernel
+int recommend_clubs_device(pk_store* s, int nq, const int32_t* q_uid, int k, uint64_t* h_keys) {
+    const int K = std::max(k, 1);
+    std::vector<uint64_t> keys((size_t)nq * K, 0ull);
+    const bool cached = s->edge_cache_valid;
+    int sm_count = 148;
+    cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, s->device);
+    const int kQ = 8192;
+    for (int q0 = 0; q0 < nq; q0 += kQ) {
+        const int m = std::min(kQ, nq - q0);
+        TRY(expand_batch(s, PK_MODE_CLUBS, m, q_uid + q0, 1, false, true));
+        TRY(s->g_nedges.reserve(m)); TRY(s->g_ntwo.reserve(m)); TRY(s->g_ncon.reserve(m));
+        TRY(s->g_edge_off.reserve((size_t)m + 1)); TRY(s->g_pair_off.reserve((size_t)m + 1)); TRY(s->g_slot_begin.reserve((size_t)m + 1));
+        TRY(s->g_totals.reserve(4));
+        ClubsPlanParams C;
+        memset(&C, 0, sizeof(C));
+        C.G = dev_graph(s); C.q_uid = s->d_i32e.p; C.nq = m;
+        C.q_row = s->g_qrow.p; C.n_slots = s->g_nslots.p; C.q_adj_off = s->g_qoff.p; C.q_deg = s->g_qdeg.p;
+        C.fr_slot = s->g_fr_slot.p; C.slot_row = s->g_slot_row.p; C.ncl = s->g_ncl.p; C.cached = cached ? 1 : 0;
+        C.n_edges = s->g_nedges.p; C.n_two = s->g_ntwo.p; C.n_con = s->g_ncon.p;
+        const int ctas = std::max(1, std::min(sm_count * 4, (m + kExpWarps - 1) / kExpWarps));
+        clubs_plan_kernel<false><<<ctas, kExpWarps * 32, 0, s->stream>>>(C);
+        clubs_offsets_kernel<<<1, 1024, 0, s->stream>>>(m, cached ? 1 : 0, s->g_nedges.p, s->g_ntwo.p, s->g_nslots.p, s->g_ncon.p,
+                                                      s->g_edge_off.p, s->g_pair_off.p, s->g_slot_begin.p, s->g_totals.p);
+        s->stat_launches += 2;
+        int64_t tot[3] = {0, 0, 0};
+        CK(cudaMemcpyAsync(tot, s->g_totals.p, 24, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+        CK(cudaGetLastError());
+        const int64_t n_edges = tot[0], n_pairs = tot[1], n_slots = tot[2];
+        if (n_edges > 0x7fffff00ll || n_pairs > 0x7fffff00ll || n_slots > 0x7fffff00ll)
+            return fail(PK_ERR_UNSUPPORTED, "club batch too large (split the batch)");
+        s->stat_pairs += n_pairs;
+        if (n_edges == 0) continue;
+        TRY(s->d_edges.reserve((size_t)n_edges));
+        TRY(s->d_u32a.reserve((size_t)n_edges));
+        TRY(s->d_i32a.reserve((size_t)std::max<int64_t>(n_pairs, 1))); TRY(s->d_i32b.reserve((size_t)std::max<int64_t>(n_pairs, 1)));
+        TRY(s->d_f32a.reserve((size_t)std::max<int64_t>(n_pairs, 1)));
+        TRY(s->d_i32d.reserve((size_t)n_slots)); TRY(s->d_keys_a.reserve((size_t)n_slots)); TRY(s->d_f64a.reserve((size_t)n_slots));
+        TRY(s->d_keys_b.reserve((size_t)m * K));
+        C.edge_off = s->g_edge_off.p; C.pair_off = s->g_pair_off.p; C.edges = s->d_edges.p; C.con_off = s->d_u32a.p;
+        C.a_row = s->d_i32a.p; C.b_row = s->d_i32b.p;
+        clubs_plan_kernel<true><<<ctas, kExpWarps * 32, 0, s->stream>>>(C);
+        ++s->stat_launches;
+        CK(cudaGetLastError());
+        if (!cached) TRY((pairs_launch<false>(s, n_pairs, s->d_i32a.p, s->d_i32b.p, s->d_f32a.p, nullptr, nullptr, nullptr)));
+        CK(cudaMemsetAsync(s->d_keys_a.p, 0, (size_t)n_slots * 8, s->stream));
+        CK(cudaMemsetAsync(s->d_f64a.p, 0, (size_t)n_slots * 8, s->stream));
+        ClubParams P;
+        P.rec = s->d_rec.p; P.rec_off = s->d_rec_off.p; P.fas = cached ? s->d_edge_fas.p : s->d_f32a.p; P.edges = s->d_edges.p;
+        P.con_off = s->d_u32a.p; P.user_edge_begin = s->g_edge_off.p; P.user_slot_begin = s->g_slot_begin.p;
+        P.user_row = s->g_qrow.p; P.con_slot = s->d_i32d.p; P.slot_key = s->d_keys_a.p; P.slot_acc = s->d_f64a.p;
+        clubs_scatter_kernel<<<m, kClubThreads, 0, s->stream>>>(P);
+        ++s->stat_launches;
+        CK(cudaGetLastError());
+        TRY(launch_slice_topk(s, s->d_keys_a.p, s->g_slot_begin.p, m, K, s->d_keys_b.p));
         CK(cudaMemcpyAsync(keys.data() + (size_t)q0 * K, s->d_keys_b.p, (size_t)m * K * 8, cudaMemcpyDeviceToHost, s->stream));
         CK(cudaStreamSynchronize(s->stream));
         TRY(collect_scan_time(s));
@@ -1898,19 +1974,19 @@ int recommend_clubs(pk_store* s, int nq, const int32_t* q_uid, int k, uint64_t* 
 // one lane per pair (pk_pairs.cuh): a_row / b_row on the device, scores (and per-field floats) written in pair order
 template <bool FIELDS>
 int pairs_launch(pk_store* s, int64_t n, const int32_t* d_a_row, const int32_t* d_b_row, float* d_out_f, float* d_out_fields,
-                 const int32_t* d_key_id, uint64_t* d_out_keys) {
+                 const int32_t* d_key_id, uint64_t* d_out_keys, bool timed) {
     if (n <= 0) return PK_OK;
     PairParams P;
     memset(&P, 0, sizeof(P));
     P.rec = s->d_rec.p; P.rec_off = s->d_rec_off.p; P.norm = s->d_norm.p; P.tab_comp = s->d_tab_comp.p; P.tab_age = s->d_tab_age.p;
     P.a_row = d_a_row; P.b_row = d_b_row; P.n = n; P.T = s->T; P.nf = 3 + s->T + 2;
     P.out_f = d_out_f; P.out_fields = d_out_fields; P.key_id = d_key_id; P.out_keys = d_out_keys;
-    CK(cudaEventRecord(s->ev0, s->stream));
+    if (timed) CK(cudaEventRecord(s->ev0, s->stream));
     fas_pairs_kernel<FIELDS><<<(unsigned)((n + 255) / 256), 256, 0, s->stream>>>(P);
-    CK(cudaEventRecord(s->ev1, s->stream));
+    if (timed) CK(cudaEventRecord(s->ev1, s->stream));
     CK(cudaGetLastError());
-    ++s->stat_launches; ++s->stat_scan_launches;
-    s->scan_time_pending = true;
+    ++s->stat_launches;
+    if (timed) { ++s->stat_scan_launches; s->scan_time_pending = true; }
     return PK_OK;
 }
 
@@ -2491,7 +2567,8 @@ int pk_recommend(pk_store* s, int mode, int nq, const int32_t* q_uid, int k, int
     if (k == 0) { for (int q = 0; q < nq; ++q) out_cnt[q] = 0; return PK_OK; }
     s->stat_scan_ns = 0; s->stat_scan_launches = 0; s->stat_pairs = 0; s->stat_groups = 0;
     std::vector<uint64_t> keys((size_t)nq * k, 0ull);
-    if (device_lists_usable(s, mode, nq, limit)) TRY(recommend_lists_device(s, mode, nq, q_uid, k, limit, keys.data()));
+    if (mode == PK_MODE_CLUBS && device_lists_usable(s, mode, nq, 1)) TRY(recommend_clubs_device(s, nq, q_uid, k, keys.data()));
+    else if (mode != PK_MODE_CLUBS && device_lists_usable(s, mode, nq, limit)) TRY(recommend_lists_device(s, mode, nq, q_uid, k, limit, keys.data()));
     else if (mode == PK_MODE_GRAPH) TRY(recommend_graph(s, nq, q_uid, k, limit, keys.data()));
     else if (mode == PK_MODE_COLLAB) TRY(recommend_collab(s, nq, q_uid, k, limit, keys.data()));
     else TRY(recommend_clubs(s, nq, q_uid, k, keys.data()));

@@ -583,6 +583,11 @@ struct CheckParams {
     const int32_t* lean_fail;     // [group] the group's pre-filter table was not built (group_prep_kernel): nothing is proven
     int nq, K, Ks;
     float margin;
+    // the exact re-score as pairs of the lane-per-pair kernel: slot q * Ks + i = (query row, candidate row or -1, uid)
+    int32_t *pa_row, *pb_row, *pkey_id;
+    const int32_t* uid;
+    const GroupDesc* groups;
+    int own_lo, own_hi;           // query groups this rank re-scores
 };
 
 __global__ void shortlist_check_kernel(const CheckParams P) {
@@ -591,8 +596,13 @@ __global__ void shortlist_check_kernel(const CheckParams P) {
     if (g < 0) return;
     const uint64_t* keys = P.short_keys + (size_t)q * P.Ks;
     int32_t* rows = P.cand_rows + ((size_t)g * 32 + P.q_lane[q]) * P.Ks;
+    const int qrow = P.groups[g].row[P.q_lane[q]];
+    const bool own = g >= P.own_lo && g < P.own_hi;
+    int32_t* pa = P.pa_row + (size_t)q * P.Ks;
+    int32_t* pb = P.pb_row + (size_t)q * P.Ks;
+    int32_t* pid = P.pkey_id + (size_t)q * P.Ks;
     if (keys[0] == kPoisonKey) {          // some rank could not build this group's fp32 tables (MergeParams): nothing is proven
-        for (int i = threadIdx.x; i < P.Ks; i += blockDim.x) rows[i] = -1;
+        for (int i = threadIdx.x; i < P.Ks; i += blockDim.x) { rows[i] = -1; pa[i] = qrow; pb[i] = -1; pid[i] = 0; }
         if (threadIdx.x == 0) { P.q_flag[q] = 1; atomicOr(P.group_flag + g, 1); }
         return;
     }
@@ -601,7 +611,11 @@ __global__ void shortlist_check_kernel(const CheckParams P) {
     const float keep_from = a_k0 - 2.0f * P.margin - 1e-7f;
     for (int i = threadIdx.x; i < P.Ks; i += blockDim.x) {
         const uint64_t k = keys[i];
-        rows[i] = (k && __uint_as_float(key_score_bits(k)) >= keep_from) ? key_id(k) : -1;
+        const int r = (k && __uint_as_float(key_score_bits(k)) >= keep_from) ? key_id(k) : -1;
+        rows[i] = r;
+        pa[i] = qrow;
+        pb[i] = own ? r : -1;
+        pid[i] = r >= 0 ? P.uid[r] : 0;
     }
     if (threadIdx.x == 0) {
         const uint64_t last = keys[P.Ks - 1];

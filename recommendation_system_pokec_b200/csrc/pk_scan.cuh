@@ -604,9 +604,10 @@ __global__ void __launch_bounds__(kMergeThreads) merge_topk_kernel(const MergePa
     __shared__ int wsum[kMergeThreads / 32];
     const int q = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const bool modeC = P.seg_begin != nullptr;
-    const bool modeA = !modeC && P.slot0 != nullptr;
-    const bool alt = modeA && P.q_flag != nullptr && P.q_flag[q] != 0;
+    // a flagged query (two-stage full scan) always takes its lists from the fallback pass, in mode-A addressing
+    const bool alt = P.q_flag != nullptr && P.alt_keys != nullptr && P.q_flag[q] != 0;
+    const bool modeC = !alt && P.seg_begin != nullptr;
+    const bool modeA = alt || (!modeC && P.slot0 != nullptr);
     const uint64_t* kbase = alt ? P.alt_keys : P.keys;
     const int stride = alt ? P.alt_stride_k : P.stride_k;
     const int K = P.K;

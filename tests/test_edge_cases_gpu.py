@@ -275,5 +275,18 @@ def test_batched_list_modes_device_pipeline_equals_host_pipeline(small_world, or
             for x, y in zip(a, b):
                 assert np.array_equal(x, y), (mode, k, limit)
             assert_topk_equal(a, orc.recommend(mode, q, k, limit, NT), f"device pipeline mode {mode} k={k} limit={limit}")
+    # clubs: the edge stream built on the device, FAS values from the pair kernel or from the per-edge cache
+    for cached in (False, True):
+        if cached:
+            dev.edge_cache_build()
+        for k in (50, 700):
+            monkeypatch.delenv("POKEC_B200_HOST_LISTS", raising=False)
+            a = dev.recommend(MODE_CLUBS, q, k, 5000)
+            monkeypatch.setenv("POKEC_B200_HOST_LISTS", "1")
+            b = dev.recommend(MODE_CLUBS, q, k, 5000)
+            monkeypatch.delenv("POKEC_B200_HOST_LISTS")
+            for x, y in zip(a, b):
+                assert np.array_equal(x, y), ("clubs", cached, k)
+            assert_topk_equal(a, orc.recommend(MODE_CLUBS, q, k, 5000, NT), f"device clubs pipeline cached={cached} k={k}")
     dev.close()
     orc.close()

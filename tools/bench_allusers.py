@@ -28,13 +28,14 @@ from recommendation_system_pokec_b200.cabi import EXCLUDE_SELF_AND_ADJ  # noqa: 
 from recommendation_system_pokec_b200.sharding import shard_rows  # noqa: E402
 
 
-def sweep(w, ws, rank, lr, B, k, n_batches, depth=2, keep_batches=()):
+def sweep(w, ws, rank, lr, B, k, n_batches, depth=2, keep_batches=(), batch_fn=None, stats=None):
     """`n_batches` consecutive batches of B distinct query users (walked in uid order) through the end-to-end calls --
     host uids in, host top-k out, host planning + H2D, both all-gathers and the merge every batch.  `depth` stores on the
     same GPU take the batches in turn, each on its own stream: the host planning and H2D of batch i + 1 overlap the
     kernels of batch i, and its all-gather overlaps the next scan.  Returns (query-users/s, seconds,
     [(uids, lists) of the batches named in keep_batches]); timed with a barrier + synchronize on both sides, max over
-    ranks."""
+    ranks.  batch_fn(b) overrides the uid walk (bench.py's end-to-end leg repeats its query batch); `stats` (a dict)
+    receives the host<->device bytes per batch counted by the stores."""
     import torch
     import torch.distributed as dist
     from recommendation_system_pokec_b200 import engine
@@ -42,6 +43,8 @@ def sweep(w, ws, rank, lr, B, k, n_batches, depth=2, keep_batches=()):
     lo, hi = shard_rows(w.n, rank, ws)
 
     def batch_uids(b):
+        if batch_fn is not None:
+            return np.ascontiguousarray(batch_fn(b), np.int32)
         q = w.uid[(b * B) % w.n:(b * B) % w.n + B].astype(np.int32)
         if len(q) < B:
             q = np.concatenate([q, w.uid[:B - len(q)].astype(np.int32)])
@@ -123,6 +126,8 @@ def sweep(w, ws, rank, lr, B, k, n_batches, depth=2, keep_batches=()):
 
     run_window(n_batches, len(slots), False)       # warm-up on batches past the window (wrapping around)
     barrier()
+    h2d0 = sum(sl.dev.stat(engine.STAT_H2D_BYTES) for sl in slots)
+    d2h0 = sum(sl.dev.stat(engine.STAT_D2H_BYTES) for sl in slots)
     t = time.perf_counter()
     run_window(0, n_batches, True)
     barrier()
@@ -131,6 +136,10 @@ def sweep(w, ws, rank, lr, B, k, n_batches, depth=2, keep_batches=()):
         tt = torch.tensor([dt], dtype=torch.float64, device=f"cuda:{lr}")
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dt = float(tt.item())
+    if stats is not None:
+        stats["h2d_bytes_per_batch"] = (sum(sl.dev.stat(engine.STAT_H2D_BYTES) for sl in slots) - h2d0) // max(n_batches, 1) + 4 * B
+        stats["d2h_bytes_per_batch"] = (sum(sl.dev.stat(engine.STAT_D2H_BYTES) for sl in slots) - d2h0) // max(n_batches, 1)
+        stats["fallback_queries_last"] = slots[(n_batches - 1) % len(slots)].dev.stat(engine.STAT_FALLBACK_QUERIES)
     for sl in slots:
         sl.dev.close()
     assert state["complete"], "a batch of the sweep returned incomplete top-k lists"
