@@ -1982,7 +1982,7 @@ int pairs_launch(pk_store* s, int64_t n, const int32_t* d_a_row, const int32_t* 
     P.a_row = d_a_row; P.b_row = d_b_row; P.n = n; P.T = s->T; P.nf = 3 + s->T + 2;
     P.out_f = d_out_f; P.out_fields = d_out_fields; P.key_id = d_key_id; P.out_keys = d_out_keys;
     if (timed) CK(cudaEventRecord(s->ev0, s->stream));
-    fas_pairs_kernel<FIELDS><<<(unsigned)((n + 255) / 256), 256, 0, s->stream>>>(P);
+    fas_pairs_kernel<FIELDS><<<(unsigned)((n + 127) / 128), 128, 0, s->stream>>>(P);
     if (timed) CK(cudaEventRecord(s->ev1, s->stream));
     CK(cudaGetLastError());
     ++s->stat_launches;

@@ -31,7 +31,8 @@ struct PairParams {
 };
 
 // |{b in B : b in set(A)}| for two ascending id lists (duplicates allowed on either side; src/recommender.cpp:119-128
-// builds a set of A and walks B with multiplicity)
+// builds a set of A and walks B with multiplicity).  One flat two-pointer loop (lanes of a warp stay in the same
+// loop whatever their lengths); binary search when one side is much longer.
 __device__ __forceinline__ int overlap_sorted(const uint32_t* __restrict__ A, uint32_t nA, const uint32_t* __restrict__ B,
                                               uint32_t nB) {
     int cnt = 0;
@@ -54,21 +55,28 @@ __device__ __forceinline__ int overlap_sorted(const uint32_t* __restrict__ A, ui
             while (lo2 < hi2) { const uint32_t mid = (lo2 + hi2) >> 1; if (__ldg(B + mid) <= a) lo2 = mid + 1; else hi2 = mid; }
             cnt += (int)(lo2 - lo);
         }
-    } else {                                   // comparable lengths: two-pointer merge
-        uint32_t i = 0;
-        uint32_t a = (nA > 0) ? __ldg(A) : 0u;
-        for (uint32_t j = 0; j < nB; ++j) {
-            const uint32_t b = __ldg(B + j);
-            while (i < nA && a < b) { ++i; if (i < nA) a = __ldg(A + i); }
-            if (i >= nA) break;
-            cnt += (a == b) ? 1 : 0;
+    } else {
+        uint32_t i = 0, j = 0;
+        while (i < nA && j < nB) {
+            const uint32_t a = __ldg(A + i), b = __ldg(B + j);
+            cnt += (a == b) ? 1 : 0;           // this b is a member; the next b may equal a again, so only j moves
+            i += (a < b) ? 1u : 0u;
+            j += (a >= b) ? 1u : 0u;
         }
     }
     return cnt;
 }
 
+// The sigma(z(s)) chain -- an fp64 division, exp and another division -- is what a pair spends most instructions
+// on, and only a few fields per pair need it (those with a non-zero similarity).  Executed where it arises it runs
+// with a handful of lanes active.  So a lane QUEUES its pending fields {field, numerator, denominator} in order
+// (clubs, friends, matched text columns ascending), the warp evaluates queue entry k of every lane together, and
+// the lane then adds sigma values in the reference's field order, taking sigma(z(0)) for the joint fields that are
+// not in the queue.
+constexpr int kPairQueue = 2 + kMaxT;
+
 template <bool FIELDS>
-__global__ void __launch_bounds__(256) fas_pairs_kernel(const PairParams P) {
+__global__ void __launch_bounds__(128) fas_pairs_kernel(const PairParams P) {
     const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= P.n) return;
     const NormTables* N = P.norm;
@@ -124,68 +132,94 @@ __global__ void __launch_bounds__(256) fas_pairs_kernel(const PairParams P) {
         ++used;
         if (FIELDS) fo[0] = (float)((double)matches / (sqrt((double)q_acnt) * sqrt((double)c_bcnt)));
     }
-    // clubs / friends (:79-91, src/recommender.cpp:119-128); the packed lists are ascending
     const uint32_t qo_clubs = kHdrWords, qo_friends = qo_clubs + pad4(q_ncl), qo_cells = qo_friends + pad4(q_nfr),
                    qo_keys = qo_cells + 4 * q_ncells, qo_w = qo_keys + pad4(q_ntok);
     const uint32_t co_clubs = kHdrWords, co_friends = co_clubs + pad4(c_ncl), co_cells = co_friends + pad4(c_nfr),
                    co_keys = co_cells + 4 * c_ncells, co_w = co_keys + pad4(c_ntok);
-    #pragma unroll
-    for (int which = 0; which < 2; ++which) {
-        const uint32_t q_n = which ? q_nfr : q_ncl, c_n = which ? c_nfr : c_ncl;
-        if (q_n == 0 || c_n == 0) continue;
-        const int inter = overlap_sorted(aw + (which ? qo_friends : qo_clubs), q_n, bw + (which ? co_friends : co_clubs), c_n);
-        const int f = 5 + which;
-        double sg = N->sig0[f];
-        if (inter > 0) {
-            const double denom = __hiloint2double(which ? (int)a4.w : (int)a4.y, which ? (int)a4.z : (int)a4.x) *
-                                 __hiloint2double(which ? (int)b4.w : (int)b4.y, which ? (int)b4.z : (int)b4.x);
-            const float s = (denom > 0.0) ? (float)((double)inter / denom) : 0.0f;
-            sg = pk_sigmoid(pk_z(N, f, (double)s));
-            if (FIELDS) fo[1 + which] = s;
-        } else if (FIELDS) fo[1 + which] = 0.0f;
-        if (FIELDS) fo[3 + P.T + which] = __int_as_float(inter);
-        sum += sg; ++used;
+
+    // ---- the pending fields of this pair: q_f = field index, q_num / q_den = similarity numerator / denominator;
+    //      after the evaluation pass q_num holds sigma(z(s)) ----
+    double q_num[kPairQueue], q_den[2];       // (only the two set fields carry a denominator; a text column's comes from its cells)
+    uint8_t q_f[kPairQueue];
+    int qn = 0;
+
+    // clubs / friends (:79-91, src/recommender.cpp:119-128); the packed lists are ascending
+    const bool has_c = q_ncl > 0 && c_ncl > 0, has_f = q_nfr > 0 && c_nfr > 0;
+    int inter_c = 0, inter_f = 0;
+    if (has_c) inter_c = overlap_sorted(aw + qo_clubs, q_ncl, bw + co_clubs, c_ncl);
+    if (has_f) inter_f = overlap_sorted(aw + qo_friends, q_nfr, bw + co_friends, c_nfr);
+    if (inter_c > 0) {
+        q_f[qn] = 5; q_num[qn] = (double)inter_c;
+        q_den[qn] = __hiloint2double((int)a4.y, (int)a4.x) * __hiloint2double((int)b4.y, (int)b4.x); ++qn;
     }
-    // text columns (:93-114): every jointly filled column, ascending; the dot product walks the common tokens in
-    // ascending token order (the order fas_scan_kernel meets them in)
-    uint64_t joint = q_mask & c_mask;
-    used += __popcll(joint);
-    const double* qwt = reinterpret_cast<const double*>(aw + qo_w);
-    const double* cwt = reinterpret_cast<const double*>(bw + co_w);
-    while (joint) {
-        const int ct = __ffsll((long long)joint) - 1;
-        joint &= joint - 1;
-        const uint64_t below = (1ull << ct) - 1ull;
-        const uint32_t qk = (uint32_t)__popcll(q_mask & below), ck = (uint32_t)__popcll(c_mask & below);
-        const uint4 qc = __ldg(ar + (qo_cells >> 2) + qk), cc = __ldg(br + (co_cells >> 2) + ck);
-        uint32_t i = qk ? __ldg(aw + qo_cells + 4 * (qk - 1) + 1) : 0u, j = ck ? __ldg(bw + co_cells + 4 * (ck - 1) + 1) : 0u;
-        const uint32_t ie = qc.y, je = cc.y;
+    if (inter_f > 0) {
+        q_f[qn] = 6; q_num[qn] = (double)inter_f;
+        q_den[qn] = __hiloint2double((int)a4.w, (int)a4.z) * __hiloint2double((int)b4.w, (int)b4.z); ++qn;
+    }
+    if (FIELDS) {
+        if (has_c) { fo[1] = 0.0f; fo[3 + P.T] = __int_as_float(inter_c); }
+        if (has_f) { fo[2] = 0.0f; fo[3 + P.T + 1] = __int_as_float(inter_f); }
+    }
+
+    // text columns (:93-114): the token keys (column << 26 | id) of a record ascend over the whole record, so ONE
+    // merge of the two key arrays meets every common token of every column, in ascending token order inside a column
+    // (the order fas_scan_kernel adds the products in).  A column's dot product is queued when the next column starts.
+    const uint64_t joint = q_mask & c_mask;
+    used += (has_c ? 1 : 0) + (has_f ? 1 : 0) + __popcll(joint);
+    uint64_t matched = 0ull;
+    if (joint != 0ull) {
+        const double* qwt = reinterpret_cast<const double*>(aw + qo_w);
+        const double* cwt = reinterpret_cast<const double*>(bw + co_w);
+        const uint32_t* ka_p = aw + qo_keys;
+        const uint32_t* kb_p = bw + co_keys;
+        uint32_t i = 0, j = 0;
+        int cur = -1;
         double dot = 0.0;
-        uint32_t ka = __ldg(aw + qo_keys + i), kb = __ldg(bw + co_keys + j);
-        while (true) {
+        while (i < q_ntok && j < c_ntok) {
+            const uint32_t ka = __ldg(ka_p + i), kb = __ldg(kb_p + j);
             if (ka == kb) {
+                const int ct = (int)(ka >> kTokBits);
+                if (ct != cur) {
+                    if (dot != 0.0) { q_f[qn] = (uint8_t)(kNumFixed + cur); q_num[qn] = dot; ++qn; matched |= 1ull << cur; }
+                    cur = ct; dot = 0.0;
+                }
                 dot = __dadd_rn(dot, __dmul_rn(__ldg(qwt + i), __ldg(cwt + j)));
-                ++i; ++j;
-                if (i >= ie || j >= je) break;
-                ka = __ldg(aw + qo_keys + i); kb = __ldg(bw + co_keys + j);
-            } else if (ka < kb) {
-                if (++i >= ie) break;
-                ka = __ldg(aw + qo_keys + i);
-            } else {
-                if (++j >= je) break;
-                kb = __ldg(bw + co_keys + j);
             }
+            i += (ka <= kb) ? 1u : 0u;
+            j += (kb <= ka) ? 1u : 0u;
         }
-        const int f = kNumFixed + ct;
-        double sg = N->sig0[f];
-        float s = 0.0f;
-        if (dot != 0.0) {
-            const double denom = __hiloint2double((int)qc.w, (int)qc.z) * __hiloint2double((int)cc.w, (int)cc.z);
-            s = (denom > 0.0) ? (float)(dot / denom) : 0.0f;
-            sg = (s == 1.0f) ? N->sig1[f] : pk_sigmoid(pk_z(N, f, (double)s));
+        if (dot != 0.0) { q_f[qn] = (uint8_t)(kNumFixed + cur); q_num[qn] = dot; ++qn; matched |= 1ull << cur; }
+    }
+
+    // ---- evaluation pass: entry k of every lane of the warp together ----
+    for (int k = 0; k < qn; ++k) {
+        const int f = q_f[k];
+        double den = 0.0;
+        if (f >= kNumFixed) {                    // text: the two cell norms (cells are indexed by the rank of the column)
+            const int ct = f - kNumFixed;
+            const uint64_t below = (1ull << ct) - 1ull;
+            const uint4 qc = __ldg(ar + (qo_cells >> 2) + __popcll(q_mask & below));
+            const uint4 cc = __ldg(br + (co_cells >> 2) + __popcll(c_mask & below));
+            den = __hiloint2double((int)qc.w, (int)qc.z) * __hiloint2double((int)cc.w, (int)cc.z);
+        } else den = q_den[k & 1];
+        const float s = (den > 0.0) ? (float)(q_num[k] / den) : 0.0f;
+        q_num[k] = (f >= kNumFixed && s == 1.0f) ? N->sig1[f] : pk_sigmoid(pk_z(N, f, (double)s));
+        if (FIELDS) fo[f >= kNumFixed ? 3 + (f - kNumFixed) : f - 4] = s;
+    }
+
+    // ---- sum in the reference's field order: clubs, friends, text columns ascending ----
+    int k = 0;
+    if (has_c) sum += (inter_c > 0) ? q_num[k++] : N->sig0[5];
+    if (has_f) sum += (inter_f > 0) ? q_num[k++] : N->sig0[6];
+    uint64_t jm = joint;
+    while (jm) {
+        const int ct = __ffsll((long long)jm) - 1;
+        jm &= jm - 1;
+        if ((matched >> ct) & 1ull) sum += q_num[k++];
+        else {
+            sum += N->sig0[kNumFixed + ct];
+            if (FIELDS) fo[3 + ct] = 0.0f;
         }
-        if (FIELDS) fo[3 + ct] = s;
-        sum += sg;
     }
     // S, F, harmonic mean (:116-123)
     float fas = 0.0f;

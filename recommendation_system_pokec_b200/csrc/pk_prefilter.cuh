@@ -110,22 +110,25 @@ __device__ __forceinline__ float lean_sigma(float4 c, float s) {
 // n fixed / set fields, DESCENDING}: a candidate shares some subset of them -- for every subset size p the best
 // case is the top-p prefix -- plus j text columns at ub_text.  Writes the 64-bit mask of admissible j into q4->z/w
 // and the smallest bound among the admissible counts into *bnd (the mask is unchanged while theta stays below it).
+__device__ __forceinline__ float l1_bound(int j, const float* frow, int nf, float ub_text, float inv_total) {
+    float pre = 0.f, best = 0.f;
+    for (int p = 0; p <= nf; ++p) {
+        const float sm = fmaf((float)j, ub_text, pre), u = (float)(p + j);
+        if (u > 0.f) {
+            const float S = sm / u, F = u * inv_total;
+            best = fmaxf(best, 2.0f * S * F / (S + F));
+        }
+        if (p < nf) pre += frow[1 + p];
+    }
+    return best * (1.0f + 2e-6f) + 2e-6f;
+}
 __device__ __noinline__ void l1_update(float th, const float* frow, float ub_text, float inv_total, volatile uint4* q4,
                                        volatile float* bnd) {
     const int nf = __float_as_int(frow[0]);
     uint32_t lo = 0u, hi = 0u;
     float nb = 3.0e38f;
     for (int j = 0; j <= kMaxT; ++j) {
-        float pre = 0.f, best = 0.f;
-        for (int p = 0; p <= nf; ++p) {
-            const float sm = fmaf((float)j, ub_text, pre), u = (float)(p + j);
-            if (u > 0.f) {
-                const float S = sm / u, F = u * inv_total;
-                best = fmaxf(best, 2.0f * S * F / (S + F));
-            }
-            if (p < nf) pre += frow[1 + p];
-        }
-        best = best * (1.0f + 2e-6f) + 2e-6f;
+        const float best = l1_bound(j, frow, nf, ub_text, inv_total);
         if (best >= th) {
             const int bit = min(j, 63);                 // j = 64 (T = 64, every column joint) shares bit 63
             if (bit < 32) lo |= 1u << bit; else hi |= 1u << (bit - 32);
@@ -134,6 +137,19 @@ __device__ __noinline__ void l1_update(float th, const float* frow, float ub_tex
     }
     q4->z = lo; q4->w = hi;
     *bnd = nb;
+}
+
+// the same update by a whole warp (lane l evaluates the counts l and l + 32): used after an insertion moved a threshold
+__device__ __forceinline__ void l1_update_warp(float th, const float* frow, float ub_text, float inv_total, volatile uint4* q4,
+                                               volatile float* bnd, int lane) {
+    const int nf = __float_as_int(frow[0]);
+    const float b0 = l1_bound(lane, frow, nf, ub_text, inv_total);
+    float b1 = l1_bound(lane + 32, frow, nf, ub_text, inv_total);
+    if (lane == 31) b1 = fmaxf(b1, l1_bound(64, frow, nf, ub_text, inv_total));      // j = 64 shares bit 63
+    const uint32_t lo = __ballot_sync(kFull, b0 >= th), hi = __ballot_sync(kFull, b1 >= th);
+    float nb = fminf(b0 >= th ? b0 : 3.0e38f, b1 >= th ? b1 : 3.0e38f);
+    for (int o = 16; o; o >>= 1) nb = fminf(nb, __shfl_xor_sync(kFull, nb, o));
+    if (lane == 0) { q4->z = lo; q4->w = hi; *bnd = nb; }
 }
 
 // Warp-cooperative insertion of `key` into one query's descending shortlist (all lanes call it with the same
@@ -148,6 +164,7 @@ __device__ __forceinline__ void shortlist_insert(uint64_t* list, int K, uint64_t
     __syncwarp();
     __threadfence_block();
     volatile uint64_t* vl = list;
+    float th_moved = -1.f;                 // lane 0: the new pruning threshold, when the insertion moved the k-th best
     if (key > vl[K - 1]) {
         int pos = 0;
         for (int s0 = 0; s0 < K; s0 += 32) pos += __popc(__ballot_sync(kFull, vl[s0 + lane] > key));
@@ -169,7 +186,7 @@ __device__ __forceinline__ void shortlist_insert(uint64_t* list, int K, uint64_t
                 if (th > *theta) {
                     *theta = th;
                     if (g_theta) atomicMax(g_theta, __float_as_uint(th));
-                    if (th > *bnd) l1_update(th, frow, ub_text, inv_total, q4, bnd);
+                    th_moved = th;
                 }
             }
         }
@@ -177,6 +194,11 @@ __device__ __forceinline__ void shortlist_insert(uint64_t* list, int K, uint64_t
     __threadfence_block();
     __syncwarp();
     if (lane == 0) atomicExch(lock, 0);
+    // the level-1 mask follows outside the lock (a stale mask only admits more candidates)
+    // (lane 0 decides: *bnd may be rewritten by another warp between two lanes' reads, and the update uses full-warp votes)
+    th_moved = (lane == 0 && th_moved > *bnd) ? th_moved : -1.f;
+    th_moved = __shfl_sync(kFull, th_moved, 0);
+    if (th_moved >= 0.f) l1_update_warp(th_moved, frow, ub_text, inv_total, q4, bnd, lane);
 }
 
 // 32 x 32 bit transpose across the warp: bit j of the result in lane l = bit l of x in lane j.
