@@ -41,7 +41,7 @@ sys.path.insert(0, ROOT)
 from recommendation_system_pokec_b200.synth import (make_world, sample_normalizers, sample_queries, normalizer_pair_sample,  # noqa: E402
                                                     POKEC_N, SEED)
 from recommendation_system_pokec_b200.cabi import EXCLUDE_SELF_AND_ADJ, MODE_GRAPH, MODE_COLLAB, MODE_CLUBS  # noqa: E402
-from recommendation_system_pokec_b200.sharding import shard_rows  # noqa: E402
+from recommendation_system_pokec_b200.sharding import shard_rows, share_thetas  # noqa: E402
 
 METRIC = "query-users/sec, FAS top-50 full scan vs 1.63M users"
 UNIT = "query-users/s"
@@ -411,6 +411,7 @@ def main():
     dev.set_shard(lo, hi)
     q = sample_queries(world, args.queries, seed=2)
     nq, k = len(q), args.topk
+    thetas_shared = share_thetas(dev, rank, world_size, f"cuda:{local_rank}")     # pruning thresholds over NVLink peer memory
     dev.fullscan_prepare(q, k, EXCLUDE_SELF_AND_ADJ)       # builds idf, packed store, plan
     dev.sync()
     log(f"[bench] rank {rank}: store {dev.stat(engine.STAT_STORE_BYTES) / 1e9:.2f} GB packed, shard rows [{lo},{hi}) "
@@ -581,7 +582,8 @@ def main():
                         "rescore_and_fallback_ms": dev.stat(engine.STAT_RESCORE_NS) / 1e6,
                         "lean_record_bytes_shard": dev.stat(engine.STAT_SHARD_LEAN_BYTES),
                         "exact_record_bytes_shard": dev.stat(engine.STAT_SHARD_RECORD_BYTES),
-                        "normalizer_pairs": n_norm_pairs}}
+                        "normalizer_pairs": n_norm_pairs,
+                        "thresholds_shared_over_nvlink": bool(thetas_shared)}}
 
     # ---- C5 (N > 1): the all-users sweep through the end-to-end calls, two batches in flight ----------------
     extra = {}

@@ -192,6 +192,20 @@ int pk_merge_keys(pk_store* s, const uint64_t* d_keys, int n_lists, int nq, int 
  *                       yields this rank's [nq][k] keys (empty lists for queries it does not own) for the final
  *                       all-gather + pk_merge_keys.
  * pk_fullscan_execute == execute_shortlists + execute_finish(NULL, 1, 0, 1).  All asynchronous on the store's stream. */
+/* Pruning thresholds across ranks, over NVLink peer memory.  The pre-filter skips a candidate whose header-only upper
+ * bound is below theta = (k-th best approximate score so far) - 2 margin for every query of a group.  Every rank's k-th
+ * best is a lower bound of the merged k-th best, so another rank's theta is valid on this shard too: the kernel polls the
+ * peers' threshold arrays while it scans (no collective, no extra launch) and accepts entries tagged with the same plan
+ * fingerprint and execution count.
+ *   theta_export   the cudaIpc handle (64 bytes) of this store's threshold array, to be all-gathered by the caller
+ *   theta_peers    maps the other ranks' arrays: `handles` = n_ranks x 64 bytes in rank order (own entry ignored); or, for
+ *                  stores of the same process, `d_ptrs` = their pk_fullscan_theta_ptr values (handles NULL).  Resets the
+ *                  execution counter -- call it on every rank at the same point.  On failure (PK_ERR_CUDA: no peer access)
+ *                  the scan simply runs without sharing.
+ * Ranks must prepare the same queries and execute in lock-step for entries to be accepted; nothing else is required. */
+int pk_fullscan_theta_export(pk_store* s, void* handle64);
+void* pk_fullscan_theta_ptr(pk_store* s);
+int pk_fullscan_theta_peers(pk_store* s, const void* handles, int n_ranks, int rank, const void* const* d_ptrs);
 int pk_fullscan_execute_shortlists(pk_store* s);
 int pk_fullscan_shortlist_keys(pk_store* s, uint64_t* d_short);
 int pk_fullscan_execute_finish(pk_store* s, const uint64_t* d_all_short, int n_lists, int rank, int n_ranks);

@@ -15,7 +15,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libpokec_b200.so")
 SOURCES = ["pk_host.cu"]
-DEPS = ["pk_host.cu", "pk_scan.cuh", "pk_prefilter.cuh", "pk_build.cuh", "pk_clubs.cuh", "pk_layout.h"]
+DEPS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h")))     # every source under csrc/
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     # the reference is built for baseline x86-64: separately rounded multiply and add

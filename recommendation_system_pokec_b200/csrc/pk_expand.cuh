@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(kExpWarps * 32) expand_kernel(const ExpandPara
 // in: cnt_a[nq] (candidates), cnt_b[nq] (slots, may be null).  out: cand_off[nq + 1]; pair_off[nq + 1] with per-query
 // pair count = graph: cnt_a; collaborative: cnt_b (the w_f pairs) + cnt_a * cnt_b (the FAS(f, c) matrix)
 __global__ void __launch_bounds__(1024) offsets_kernel(int nq, const int32_t* __restrict__ cnt_a, const int32_t* __restrict__ cnt_b,
-                                                       int32_t* __restrict__ cand_off, int64_t* __restrict__ pair_off) {
+                                                       int32_t* __restrict__ cand_off, int64_t* __restrict__ pair_off, int matrix_pairs) {
     __shared__ long long wsum_a[32], wsum_p[32];
     __shared__ long long run_a, run_p;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(1024) offsets_kernel(int nq, const int32_t* __
         long long a = 0, p = 0;
         if (q < nq) {
             a = cnt_a[q];
-            p = cnt_b ? (long long)cnt_b[q] * (1 + a) : a;
+            p = cnt_b ? (long long)cnt_b[q] * (matrix_pairs ? 1 + a : 1) : a;
         }
         long long ia = a, ip = p;
         for (int o = 1; o < 32; o <<= 1) {
@@ -289,7 +289,10 @@ struct EmitParams {
     int32_t* a_row;              // [pairs]
     int32_t* b_row;
     int32_t* key_id;             // graph: [pairs] candidate uid of each pair; collaborative: [cands] candidate uid
-    int32_t* cand_row_flat;      // collaborative: [cands] candidate rows, compacted
+    int32_t* cand_row_flat;      // collaborative: [cands] candidate rows, compacted (grouped by cost class)
+    const uint32_t* cost;        // [n] per profile row: tokens + friends + clubs (what a pair's merges walk)
+    int friend_major;            // matrix pair index = slot * nc + c (a warp holds one friend) or c * ns + slot
+    int matrix_pairs;            // 0: the FAS(f, c) matrix goes to the group kernel (collab_groups_*), only the w_f pairs are emitted
 };
 
 __global__ void __launch_bounds__(256) emit_pairs_kernel(const EmitParams P) {
@@ -310,19 +313,39 @@ __global__ void __launch_bounds__(256) emit_pairs_kernel(const EmitParams P) {
     }
     const int ns = P.n_slots[q];
     const int32_t* srow = P.slot_row + (P.q_adj_off[q] >= 0 ? P.q_adj_off[q] : 0);
+    // The candidates of a user are scored in any order (only their keys matter afterwards), so they are grouped by
+    // cost class (power-of-two bands of tokens + friends + clubs): the 32 lanes of a warp of the pair kernel then
+    // walk records of similar length instead of all waiting for the longest one.
+    __shared__ int cls_cnt[16], cls_base[16];
+    if (threadIdx.x < 16) cls_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    auto cls_of = [&](int rc) { const uint32_t c = __ldg(P.cost + rc) >> 4; return c ? min(15, 32 - __clz(c)) : 0; };
+    for (int i = threadIdx.x; i < nc; i += blockDim.x) atomicAdd(&cls_cnt[cls_of(cand[i])], 1);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int run = 0;
+        for (int k = 0; k < 16; ++k) { cls_base[k] = run; run += cls_cnt[k]; cls_cnt[k] = 0; }
+    }
+    __syncthreads();
     for (int i = threadIdx.x; i < nc; i += blockDim.x) {
         const int rc = cand[i];
-        P.cand_row_flat[c0 + i] = rc;
-        P.key_id[c0 + i] = P.uid[rc];
+        const int k = cls_of(rc);
+        const int pos = cls_base[k] + atomicAdd(&cls_cnt[k], 1);
+        P.cand_row_flat[c0 + pos] = rc;
+        P.key_id[c0 + pos] = P.uid[rc];
     }
-    // w_f = FAS(user, f) for every distinct friend with a profile, then FAS(f, c): pair index = c * ns + slot
+    __syncthreads();
+    // w_f = FAS(user, f) for every distinct friend with a profile, then FAS(f, c) friend-major: pair index =
+    // slot * nc + c, so that a warp holds ONE friend (broadcast loads of the A side) and 32 candidates of one class
     for (int s = threadIdx.x; s < ns; s += blockDim.x) { P.a_row[p0 + s] = urow; P.b_row[p0 + s] = srow[s]; }
     const int64_t m0 = p0 + ns;
-    const int64_t total = (int64_t)nc * ns;
+    const int64_t total = P.matrix_pairs ? (int64_t)nc * ns : 0;
     for (int64_t t = threadIdx.x; t < total; t += blockDim.x) {
-        const int c = (int)(t / ns), s = (int)(t - (int64_t)c * ns);
-        P.a_row[m0 + t] = srow[s];
-        P.b_row[m0 + t] = cand[c];
+        int sl, c;
+        if (P.friend_major) { sl = (int)(t / nc); c = (int)(t - (int64_t)sl * nc); }
+        else { c = (int)(t / ns); sl = (int)(t - (int64_t)c * ns); }
+        P.a_row[m0 + t] = srow[sl];
+        P.b_row[m0 + t] = P.cand_row_flat[c0 + c];
     }
 }
 
@@ -340,6 +363,7 @@ struct CollabReduce2Params {
     const int32_t* fr_slot;      // [E]
     const int32_t* key_id;       // [cands]
     uint64_t* out_keys;          // [cands]
+    int friend_major;
 };
 
 __global__ void __launch_bounds__(128) collab_reduce2_kernel(const CollabReduce2Params P) {
@@ -355,7 +379,7 @@ __global__ void __launch_bounds__(128) collab_reduce2_kernel(const CollabReduce2
         for (int i = 0; i < deg; ++i) {
             const int sl = fs[i];
             if (sl < 0) continue;
-            score = __dadd_rn(score, __dmul_rn((double)w[sl], (double)mat[(int64_t)c * ns + sl]));
+            score = __dadd_rn(score, __dmul_rn((double)w[sl], (double)mat[P.friend_major ? (int64_t)sl * nc + c : (int64_t)c * ns + sl]));
         }
         P.out_keys[c0 + c] = make_key(__float_as_uint((float)score), P.key_id[c0 + c]);
     }
@@ -501,6 +525,165 @@ __global__ void __launch_bounds__(1024) clubs_offsets_kernel(int nq, int cached,
     if (tid == 0) {
         edge_off[nq] = (int32_t)min(run[0], 0x7fffffffll); pair_off[nq] = run[1]; slot_begin[nq] = (int32_t)min(run[2], 0x7fffffffll);
         totals[0] = run[0]; totals[1] = run[1]; totals[2] = run[2];
+    }
+}
+
+// ---- the FAS(f, c) matrix of recommend_collaborative through fas_scan_kernel: group planning on the device ----
+// Per query, every block of 32 distinct friends is a group of the exact scan kernel (lane = friend) and the query's
+// candidates are streamed past it once: 32 pairs share every candidate record and every table probe, which the
+// lane-per-pair kernel cannot do.  What the host planner does for single-user calls (pk_host.cu: layout_group,
+// collab_prepare) is done here for a whole batch: group descriptors, arena offsets, work items.
+__host__ __device__ inline int pk_log2_table(unsigned long long entries) {       // smallest L >= 1 with 2^L >= 2 * entries
+    int L = 1;
+    while ((1ull << L) < 2ull * entries) ++L;
+    return L;
+}
+__host__ __device__ inline uint32_t pk_align16(uint32_t x) { return (x + 15u) & ~15u; }
+
+// table layout of a group of the EXACT kernel without exclusion ids (the layout pk_host.cu:layout_group produces with
+// with_lean = false and no exclusion ids)
+__host__ __device__ inline void pk_layout_exact_group(GroupDesc& g, unsigned long long ncl, unsigned long long nfr,
+                                                      unsigned long long ntok, int T) {
+    g.log_sc = pk_log2_table(ncl); g.log_sf = pk_log2_table(nfr); g.log_sa = pk_log2_table(0); g.log_st = pk_log2_table(ntok);
+    uint32_t off = 0;
+    g.off_text2 = g.off_base = g.off_vals32 = g.off_sets2 = 0; g.log_cb = g.log_cs = 0;
+    g.exact_begin = off;
+    g.off_adj = off; off += (8u << g.log_sa);
+    off = pk_align16(off);
+    g.lean_end = 0u;
+    g.off_clubs = off; off += (8u << g.log_sc);
+    g.off_friends = off; off += (8u << g.log_sf);
+    off = pk_align16(off);
+    g.off_nq = off; off += pk_align16((uint32_t)T * 32u * 8u);
+    g.off_text = off; off += (16u << g.log_st);
+    g.off_vals = off; off += pk_align16((uint32_t)ntok * 8u);
+    g.n_vals = (uint32_t)ntok;
+    g.arena_bytes = pk_align16(off);
+}
+
+struct CollabGroupsParams {
+    int nq, T;
+    uint32_t smem_budget;            // largest table block the scan kernel can stage in shared memory
+    const int32_t *cand_cnt, *cand_off, *n_slots, *q_adj_off, *slot_row;
+    const uint32_t *ncl, *nfr, *ntok;    // [n] per profile row
+    int32_t* group_off;              // [nq + 1] first group of each query
+    // per group
+    GroupDesc* groups;
+    WorkItem* items;
+    unsigned long long* totals;      // {groups, arena bytes, output rows, max shared-memory block, groups outside shared memory}
+};
+
+// pass 1 (one CTA): groups per query -> group_off
+__global__ void __launch_bounds__(1024) collab_groups_count_kernel(const CollabGroupsParams P) {
+    __shared__ int wsum[32];
+    __shared__ int run;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) run = 0;
+    __syncthreads();
+    for (int base = 0; base < P.nq; base += 1024) {
+        const int q = base + tid;
+        int v = 0;
+        if (q < P.nq && P.cand_cnt[q] > 0) v = (P.n_slots[q] + 31) >> 5;
+        int inc = v;
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+        if (lane == 31) wsum[warp] = inc;
+        __syncthreads();
+        int off = run;
+        for (int w = 0; w < warp; ++w) off += wsum[w];
+        if (q < P.nq) P.group_off[q] = off + inc - v;
+        __syncthreads();
+        if (tid == 1023) run = off + inc;
+        __syncthreads();
+    }
+    if (tid == 0) { P.group_off[P.nq] = run; P.totals[0] = (unsigned long long)run; }
+}
+
+// pass 2 (one CTA, sequential over the groups in chunks of 1024 threads): descriptors, arena offsets, work items.
+// The running offsets are carried across the chunks by a block scan.
+__global__ void __launch_bounds__(1024) collab_groups_fill_kernel(const CollabGroupsParams P) {
+    __shared__ unsigned long long ws_a[32], ws_r[32];
+    __shared__ unsigned long long run_a, run_r, max_sm, n_gl;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) { run_a = 0; run_r = 0; max_sm = 0; n_gl = 0; }
+    __syncthreads();
+    const int G = P.group_off[P.nq];
+    for (int base = 0; base < G; base += 1024) {
+        const int g = base + tid;
+        GroupDesc gd;
+        unsigned long long a = 0, r = 0;
+        int q = 0;
+        if (g < G) {
+            int lo = 0, hi = P.nq;                      // the query whose group range holds g
+            while (lo < hi) { const int mid = (lo + hi) >> 1; if (P.group_off[mid + 1] <= g) lo = mid + 1; else hi = mid; }
+            q = lo;
+            const int b = g - P.group_off[q];
+            const int ns = P.n_slots[q];
+            const int32_t* srow = P.slot_row + P.q_adj_off[q];
+            memset(&gd, 0, sizeof(gd));
+            gd.n_lanes = min(32, ns - 32 * b);
+            unsigned long long ncl = 0, nfr = 0, ntok = 0;
+            for (int l = 0; l < 32; ++l) {
+                int row = -1;
+                if (l < gd.n_lanes) { row = srow[32 * b + l]; ncl += P.ncl[row]; nfr += P.nfr[row]; ntok += P.ntok[row]; }
+                gd.row[l] = row; gd.qidx[l] = q;
+            }
+            pk_layout_exact_group(gd, ncl, nfr, ntok, P.T);
+            gd.in_smem = gd.arena_bytes <= P.smem_budget ? 1 : 0;
+            a = gd.arena_bytes;
+            r = (unsigned long long)P.cand_cnt[q];
+            if (gd.in_smem) atomicMax(&max_sm, (unsigned long long)gd.arena_bytes); else atomicAdd(&n_gl, 1ull);
+        }
+        unsigned long long ia = a, ir = r;
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long ta = __shfl_up_sync(0xffffffffu, ia, o), tr = __shfl_up_sync(0xffffffffu, ir, o);
+            if (lane >= o) { ia += ta; ir += tr; }
+        }
+        if (lane == 31) { ws_a[warp] = ia; ws_r[warp] = ir; }
+        __syncthreads();
+        unsigned long long oa = run_a, orr = run_r;
+        for (int w = 0; w < warp; ++w) { oa += ws_a[w]; orr += ws_r[w]; }
+        if (g < G) {
+            gd.arena_off = (uint32_t)min(oa + ia - a, 0xffffffffull);
+            P.groups[g] = gd;
+            WorkItem it;
+            it.group = g; it.cand_begin = P.cand_off[q]; it.cand_end = P.cand_off[q] + P.cand_cnt[q];
+            it.out_slot = (int32_t)min(orr + ir - r, 0x7fffffffull);
+            P.items[g] = it;
+        }
+        __syncthreads();
+        if (tid == 1023) { run_a = oa + ia; run_r = orr + ir; }
+        __syncthreads();
+    }
+    if (tid == 0) { P.totals[1] = run_a; P.totals[2] = run_r; P.totals[3] = max_sm; P.totals[4] = n_gl; }
+}
+
+// reduce on the group kernel's [row][32] output: FAS(f, c) of slot sl sits at (out_slot(group of sl) + c) * 32 + sl % 32
+struct CollabReduce3Params {
+    int nq;
+    const float* w;              // pair scores: w_f of slot sl of query q at pair_off[q] + sl
+    const float* mat;            // store-mode output of fas_scan_kernel
+    const int64_t* pair_off;
+    const int32_t *cand_off, *n_slots, *q_adj_off, *q_deg, *fr_slot, *group_off, *key_id;
+    const WorkItem* items;
+    uint64_t* out_keys;
+};
+
+__global__ void __launch_bounds__(128) collab_reduce3_kernel(const CollabReduce3Params P) {
+    const int q = blockIdx.y;
+    const int c0 = P.cand_off[q], nc = P.cand_off[q + 1] - c0;
+    if (nc == 0) return;
+    const int deg = P.q_deg[q], g0 = P.group_off[q];
+    const float* w = P.w + P.pair_off[q];
+    const int32_t* fs = P.fr_slot + (P.q_adj_off[q] >= 0 ? P.q_adj_off[q] : 0);
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < nc; c += gridDim.x * blockDim.x) {
+        double score = 0.0;
+        for (int i = 0; i < deg; ++i) {
+            const int sl = fs[i];
+            if (sl < 0) continue;
+            const int64_t row = (int64_t)P.items[g0 + (sl >> 5)].out_slot + c;
+            score = __dadd_rn(score, __dmul_rn((double)w[sl], (double)P.mat[row * 32 + (sl & 31)]));
+        }
+        P.out_keys[c0 + c] = make_key(__float_as_uint((float)score), P.key_id[c0 + c]);
     }
 }
 

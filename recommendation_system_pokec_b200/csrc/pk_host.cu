@@ -135,6 +135,9 @@ struct FullscanJob {
     int n_dyn = 0, n_slices = 1, sm_count = 148;
     int64_t cand_begin = 0, cand_end = 0;     // the shard the job was planned for
     DevBuf<int32_t> q_group, q_flag, q_flag0, group_flag, group_flag0, short_rows, rr_slot0, rr_nl, pre_slot0, pre_nl;
+    // seed pass of the pruning thresholds: the rows of the shard with the most tokens (ascending row order)
+    int n_seed = 0;
+    uint32_t plan_fp = 0;                     // fingerprint of (queries, k, exclusion): part of the threshold tag
     DevBuf<int32_t> rs_a, rs_b, rs_id, rs_seg;  // exact re-score of the shortlists as (query, candidate) pairs: [nq][Ks]
     DevBuf<float> rs_f;
     DevBuf<int32_t> lean_fail;                // [group] the pre-filter's token table could not be built -> exact scan
@@ -239,14 +242,29 @@ struct pk_store {
     DevBuf<int32_t> g_fr_slot, g_slot_row;           // [E] per adjacency entry of a queried user
     DevBuf<int32_t> g_qrow, g_cand, g_cnt, g_nslots, g_qoff, g_qdeg, g_cand_off, g_next;
     DevBuf<int64_t> g_pair_off, g_totals;
-    DevBuf<uint32_t> g_ncl;
+    DevBuf<uint32_t> g_ncl, g_cost, g_nfr, g_ntok;
+    DevBuf<int32_t> g_group_off;
+    DevBuf<unsigned long long> g_gtotals;
     DevBuf<int32_t> g_nedges, g_ntwo, g_edge_off, g_slot_begin;
     DevBuf<unsigned long long> g_ncon;
     FullscanJob job;
     // bumped by every call that changes what a prepared full-scan plan depends on (world, shard, normalizers, idf,
     // adjacency overrides): a plan stamped with an older value is refused by execute / finish / fetch / keys
     int64_t gen = 0;
-    int64_t max_cell = 0;     // longest token cell of the loaded world (scales the pre-filter's error bound)
+    int64_t max_cell = 0;
+    // pruning thresholds of the running full scan: one fixed allocation per store (its cudaIpc handle is handed to the
+    // other ranks of a sharded scan, pk_fullscan_theta_export / _peers), zeroed per execution
+    static constexpr size_t kThetaCap = (size_t)8192 * 32;
+    DevBuf<unsigned long long> d_theta_x;
+    const unsigned long long* peer_theta[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    void* peer_mapped[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // cudaIpcOpenMemHandle results
+    int n_peers = 0;
+    uint32_t exec_counter = 0;
+    DevBuf<int32_t> d_seed_rows;
+    DevBuf<uint8_t> d_seed_skip;
+    std::vector<int32_t> seed_cache;          // seed rows of the shard [seed_b, seed_e) with divisor seed_div
+    int64_t seed_b = -1, seed_e = -1;
+    int seed_div = 0;     // longest token cell of the loaded world (scales the pre-filter's error bound)
     bool scan_time_pending = false;
     int64_t stat_h2d = 0, stat_d2h = 0;
     int64_t last_idf_n = 0;
@@ -730,6 +748,7 @@ ScanParams base_scan_params(pk_store* s, int K) {
     P.T = s->T; P.K = K; P.Kp = (K + 31) / 32 * 32; P.exclude_mode = PK_EXCLUDE_NONE;
     P.nf = 3 + s->T + 2;
     P.group_lo = 0; P.group_hi = 0x7fffffff;
+    P.want_smem = -1;
     return P;
 }
 
@@ -834,6 +853,13 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
     FullscanJob& J = s->job;
     J.valid = false;
     J.nq = nq; J.k = k; J.exclude = exclude_mode;
+    {
+        uint32_t h = 2166136261u;
+        auto mixin = [&](uint32_t v) { h = (h ^ v) * 16777619u; };
+        mixin((uint32_t)nq); mixin((uint32_t)k); mixin((uint32_t)exclude_mode);
+        for (int q = 0; q < nq; ++q) mixin((uint32_t)q_uid[q]);
+        J.plan_fp = h;
+    }
     const int K = std::max(k, 1), Kp = (K + 31) / 32 * 32;
     J.K = K; J.Kp = Kp;
     J.n_groups = 0; J.n_sm = J.n_gl = 0; J.pairs = 0;
@@ -972,7 +998,9 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
         }
         J.n_dyn = (int)dyn_groups.size();
         TRY(upload(s, J.dyn_groups, dyn_groups));
-        TRY(J.dyn_state.reserve(std::max<size_t>(34 * dyn_groups.size(), 1)));     // cursor, instances, theta[32] per group
+        TRY(J.dyn_state.reserve(std::max<size_t>(2 * dyn_groups.size(), 1)));      // cursor, instances per group
+        if (dyn_groups.size() * 32 > pk_store::kThetaCap) return fail(PK_ERR_UNSUPPORTED, "more than 8192 query groups in one full-scan batch (split the batch)");
+        TRY(s->d_theta_x.reserve(pk_store::kThetaCap));
         // exact re-score items: the 32 x Ks shortlist rows of each group, in list mode
         int rr_splits = 4;      // measured: 8 splits (6.92 waves) cost 4.7 ms against 3.9 ms (table staging per CTA)
         if (const char* e = getenv("POKEC_B200_RR_SPLITS")) rr_splits = std::max(1, atoi(e));
@@ -1020,6 +1048,32 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
             TRY(J.rs_f.reserve((size_t)nq * Ks));
             TRY(J.keys_rr.reserve((size_t)nq * Ks));
         }
+        {   // Scan order (PreParams): the 1/16 of the shard's rows with the most tokens come first (measured on the
+            // bench world, pre-filter ms at 1 GPU / on a 1/8 shard: none 85.0 / 14.4, 1/256 81.5 / 13.6, 1/64 79.7 / 13.3, 1/16 78.4 / 13.0)
+            int div = 16;
+            if (const char* e = getenv("POKEC_B200_SEED_DIV")) div = atoi(e);
+            J.n_seed = 0;
+            if (div > 0 && n_cand >= 65536) {
+                if (s->seed_b != s->shard_begin || s->seed_e != s->shard_end || s->seed_div != div) {
+                    const int64_t want = n_cand / div;
+                    std::vector<int32_t> rows((size_t)n_cand);
+                    for (int64_t i = 0; i < n_cand; ++i) rows[(size_t)i] = (int32_t)(s->shard_begin + i);
+                    std::nth_element(rows.begin(), rows.begin() + want, rows.end(),
+                                     [&](int32_t a, int32_t b) { return s->h_ntok[a] != s->h_ntok[b] ? s->h_ntok[a] > s->h_ntok[b] : a < b; });
+                    rows.resize((size_t)want);
+                    std::sort(rows.begin(), rows.end(),
+                              [&](int32_t a, int32_t b) { return s->h_ntok[a] != s->h_ntok[b] ? s->h_ntok[a] > s->h_ntok[b] : a < b; });
+                    std::vector<uint8_t> skip((size_t)s->n, 0);
+                    for (int32_t r : rows) skip[(size_t)r] = 1;
+                    TRY(upload(s, s->d_seed_rows, rows));
+                    TRY(upload(s, s->d_seed_skip, skip));
+                    CK(cudaStreamSynchronize(s->stream));
+                    s->seed_cache.swap(rows);
+                    s->seed_b = s->shard_begin; s->seed_e = s->shard_end; s->seed_div = div;
+                }
+                J.n_seed = (int)s->seed_cache.size();
+            }
+        }
     }
     CK(cudaStreamSynchronize(s->stream));
     J.valid = true;
@@ -1052,7 +1106,26 @@ PreParams base_pre_params(pk_store* s) {
     return P;
 }
 
-int fullscan_shortlists(pk_store* s) {
+PreParams job_pre_params(pk_store* s) {
+    FullscanJob& J = s->job;
+    PreParams Q = base_pre_params(s);
+    Q.groups = J.groups.p; Q.items = J.pre_items.p; Q.arena = J.arena.p;
+    Q.Ks = J.Ks; Q.exclude_mode = J.exclude; Q.smem_arena_bytes = J.max_smem_lean; Q.out_keys = J.keys_pre.p;
+    Q.dyn_cursor = J.dyn_state.p; Q.dyn_ninst = J.dyn_state.p + J.n_dyn; Q.dyn_groups = J.dyn_groups.p;
+    Q.n_dyn = J.n_dyn; Q.max_inst = J.n_slices;
+    Q.dyn_theta = s->d_theta_x.p;
+    Q.n_peers = s->n_peers;
+    for (int r = 0; r < 7; ++r) Q.peer_theta[r] = s->peer_theta[r];
+    Q.theta_tag = (J.plan_fp ^ (s->exec_counter * 0x9E3779B1u)) | 1u;
+    Q.K = J.K;
+    Q.theta_drop = (getenv("POKEC_B200_NO_PRUNE") && getenv("POKEC_B200_NO_PRUNE")[0] == '1') ? 1e9f : 2.0f * s->margin + 1e-5f;
+    Q.cand_begin = (int)J.cand_begin; Q.cand_end = (int)J.cand_end;
+    if (J.n_seed > 0) { Q.row_list = s->d_seed_rows.p; Q.skip = s->d_seed_skip.p; Q.n_list = J.n_seed; }
+    return Q;
+}
+
+// query tables (+ the per-execution state of the two-stage scan)
+int fullscan_begin(pk_store* s) {
     FullscanJob& J = s->job;
     TRY(job_ok(s));
     s->stat_scan_ns = 0; s->stat_scan_launches = 0; s->stat_prefilter_ns = 0;
@@ -1073,41 +1146,44 @@ int fullscan_shortlists(pk_store* s) {
     group_prep_kernel<<<(unsigned)J.n_groups, kPrepThreads, 0, s->stream>>>(PP);
     ++s->stat_launches;
     CK(cudaGetLastError());
-    ScanParams P = base_scan_params(s, J.K);
-    P.groups = J.groups.p; P.arena = J.arena.p;
-    P.exclude_mode = J.exclude;
-    MergeParams M;
-    memset(&M, 0, sizeof(M));
-    M.lane = J.q_lane.p; M.nq = J.nq; M.K = J.K; M.out_keys = J.keys_b.p;
-
-    if (!J.lean) {   // exact arithmetic on every pair
-        P.out_keys = J.keys_a.p;
-        TRY((launch_scan<EPI_TOPK, false>(s, P, J.items.p, J.n_sm, J.n_gl, J.max_smem_arena)));
-        M.keys = J.keys_a.p; M.slot0 = J.q_slot0.p; M.n_lists_q = J.q_nl.p; M.stride_k = J.Kp;
-        return launch_merge(s, M, J.nq);
-    }
-
-    // 1. pre-filter: fp32 scores of every pair, Ks best per query and slice
+    if (!J.lean) return PK_OK;
     const int Ks = J.Ks;
     CK(cudaMemcpyAsync(J.q_flag.p, J.q_flag0.p, (size_t)J.nq * 4, cudaMemcpyDeviceToDevice, s->stream));
     CK(cudaMemcpyAsync(J.group_flag.p, J.group_flag0.p, (size_t)J.n_groups * 4, cudaMemcpyDeviceToDevice, s->stream));
     CK(cudaMemsetAsync(J.short_rows.p, 0xFF, (size_t)J.n_groups * 32 * Ks * 4, s->stream));
     CK(cudaMemsetAsync(J.keys_short.p, 0, (size_t)J.nq * Ks * 8, s->stream));
-    PreParams Q = base_pre_params(s);
-    Q.groups = J.groups.p; Q.items = J.pre_items.p; Q.arena = J.arena.p;
-    Q.Ks = Ks; Q.exclude_mode = J.exclude; Q.smem_arena_bytes = J.max_smem_lean; Q.out_keys = J.keys_pre.p;
-    // shortlist instances a CTA never takes stay empty; cursors and instance counters start at 0
-    CK(cudaMemsetAsync(J.keys_pre.p, 0, std::max<size_t>(J.n_pre, 1) * 32 * (size_t)Ks * 8, s->stream));
-    CK(cudaMemsetAsync(J.dyn_state.p, 0, std::max<size_t>(34 * (size_t)J.n_dyn, 1) * 4, s->stream));
-    Q.dyn_cursor = J.dyn_state.p; Q.dyn_ninst = J.dyn_state.p + J.n_dyn; Q.dyn_groups = J.dyn_groups.p;
-    Q.n_dyn = J.n_dyn; Q.max_inst = J.n_slices;
-    Q.dyn_theta = reinterpret_cast<unsigned int*>(J.dyn_state.p + 2 * J.n_dyn);
-    Q.K = J.K;
-    Q.theta_drop = (getenv("POKEC_B200_NO_PRUNE") && getenv("POKEC_B200_NO_PRUNE")[0] == '1') ? 1e9f : 2.0f * s->margin + 1e-5f;
-    Q.cand_begin = (int)J.cand_begin; Q.cand_end = (int)J.cand_end;
-    const size_t pre_grid = std::min<size_t>((size_t)J.sm_count, J.n_pre);     // one persistent CTA per SM
+    // cursors, instance counters and thresholds start at 0; a new execution, a new threshold tag
+    CK(cudaMemsetAsync(J.dyn_state.p, 0, std::max<size_t>(2 * (size_t)J.n_dyn, 1) * 4, s->stream));
+    CK(cudaMemsetAsync(s->d_theta_x.p, 0, std::max<size_t>((size_t)J.n_dyn * 32, 1) * 8, s->stream));
+    ++s->exec_counter;
     CK(cudaEventRecord(s->pev[1], s->stream));
     CK(cudaEventRecord(s->ev0, s->stream));
+    return PK_OK;
+}
+
+int fullscan_shortlists(pk_store* s) {
+    FullscanJob& J = s->job;
+    TRY(job_ok(s));
+    TRY(fullscan_begin(s));
+    if (J.n_groups == 0) return PK_OK;
+    MergeParams M;
+    memset(&M, 0, sizeof(M));
+    M.lane = J.q_lane.p; M.nq = J.nq; M.K = J.K; M.out_keys = J.keys_b.p;
+    if (!J.lean) {   // exact arithmetic on every pair
+        ScanParams P = base_scan_params(s, J.K);
+        P.groups = J.groups.p; P.arena = J.arena.p;
+        P.exclude_mode = J.exclude;
+        P.out_keys = J.keys_a.p;
+        TRY((launch_scan<EPI_TOPK, false>(s, P, J.items.p, J.n_sm, J.n_gl, J.max_smem_arena)));
+        M.keys = J.keys_a.p; M.slot0 = J.q_slot0.p; M.n_lists_q = J.q_nl.p; M.stride_k = J.Kp;
+        return launch_merge(s, M, J.nq);
+    }
+    // 1. pre-filter: fp32 scores of the shard (heaviest rows first), Ks best per query and instance
+    const int Ks = J.Ks;
+    PreParams Q = job_pre_params(s);
+    // shortlist instances a CTA never takes stay empty; cursors and instance counters restart at 0
+    CK(cudaMemsetAsync(J.keys_pre.p, 0, std::max<size_t>(J.n_pre, 1) * 32 * (size_t)Ks * 8, s->stream));
+    const size_t pre_grid = std::min<size_t>((size_t)J.sm_count, J.n_pre);     // one persistent CTA per SM
     TRY(launch_prefilter(s, Q, pre_grid, J.max_smem_lean, Ks, false));
     CK(cudaEventRecord(s->ev1, s->stream));
     if (J.n_pre) { s->scan_time_pending = true; ++s->stat_scan_launches; }
@@ -1358,6 +1434,14 @@ int ensure_graph(pk_store* s) {
     const size_t E = std::max<size_t>(s->adj.size(), 1);
     TRY(s->g_fr_slot.reserve(E)); TRY(s->g_slot_row.reserve(E));
     TRY(upload(s, s->g_ncl, s->h_ncl));
+    {
+        std::vector<uint32_t> cost((size_t)s->n);
+        for (int r = 0; r < s->n; ++r) cost[(size_t)r] = s->h_ntok[r] + s->h_nfr[r] + s->h_ncl[r];
+        TRY(upload(s, s->g_cost, cost));
+        TRY(upload(s, s->g_nfr, s->h_nfr));
+        TRY(upload(s, s->g_ntok, s->h_ntok));
+        CK(cudaStreamSynchronize(s->stream));
+    }
     CK(cudaStreamSynchronize(s->stream));
     s->graph_dirty = false;
     return PK_OK;
@@ -1434,8 +1518,12 @@ int recommend_lists_device(pk_store* s, int mode, int nq, const int32_t* q_uid, 
         const int m = std::min(kQ, nq - q0);
         TRY(expand_batch(s, mode, m, q_uid + q0, limit, false));
         const bool collab = mode != PK_MODE_GRAPH;
+        // the FAS(f, c) matrix: groups of 32 friends through fas_scan_kernel (planned on the device), or -- A/B switch --
+        // one lane per (f, c) pair
+        const char* pm = getenv("POKEC_B200_COLLAB_PAIRS");
+        const bool pair_matrix = collab && pm && pm[0] == '1';
         TRY(s->g_cand_off.reserve((size_t)m + 1)); TRY(s->g_pair_off.reserve((size_t)m + 1));
-        offsets_kernel<<<1, 1024, 0, s->stream>>>(m, s->g_cnt.p, collab ? s->g_nslots.p : nullptr, s->g_cand_off.p, s->g_pair_off.p);
+        offsets_kernel<<<1, 1024, 0, s->stream>>>(m, s->g_cnt.p, collab ? s->g_nslots.p : nullptr, s->g_cand_off.p, s->g_pair_off.p, pair_matrix ? 1 : 0);
         ++s->stat_launches;
         int32_t n_cands = 0;
         int64_t n_pairs = 0;
@@ -1456,7 +1544,10 @@ int recommend_lists_device(pk_store* s, int mode, int nq, const int32_t* q_uid, 
         E.nq = m; E.mode = mode; E.cand_cap = limit; E.q_row = s->g_qrow.p; E.cand_out = s->g_cand.p; E.cand_cnt = s->g_cnt.p;
         E.cand_off = s->g_cand_off.p; E.pair_off = s->g_pair_off.p; E.n_slots = s->g_nslots.p; E.q_adj_off = s->g_qoff.p;
         E.slot_row = s->g_slot_row.p; E.uid = s->d_uid.p; E.a_row = s->d_i32a.p; E.b_row = s->d_i32b.p; E.key_id = s->d_i32c.p;
-        E.cand_row_flat = s->d_i32d.p;
+        E.cand_row_flat = s->d_i32d.p; E.cost = s->g_cost.p;
+        const char* lay = getenv("POKEC_B200_COLLAB_LAYOUT");
+        E.matrix_pairs = pair_matrix ? 1 : 0;
+        E.friend_major = (lay && lay[0] == 'f') ? 1 : 0;      // measured: candidate-major 28.9 ms, friend-major 32.0 ms (72.9 M pairs)
         emit_pairs_kernel<<<m, 256, 0, s->stream>>>(E);
         ++s->stat_launches;
         CK(cudaGetLastError());
@@ -1464,12 +1555,81 @@ int recommend_lists_device(pk_store* s, int mode, int nq, const int32_t* q_uid, 
             TRY((pairs_launch<false>(s, n_pairs, s->d_i32a.p, s->d_i32b.p, s->d_f32a.p, nullptr, s->d_i32c.p, s->d_keys_a.p)));
         } else {
             TRY((pairs_launch<false>(s, n_pairs, s->d_i32a.p, s->d_i32b.p, s->d_f32a.p, nullptr, nullptr, nullptr)));
-            CollabReduce2Params R;
-            R.nq = m; R.fas = s->d_f32a.p; R.pair_off = s->g_pair_off.p; R.cand_off = s->g_cand_off.p; R.n_slots = s->g_nslots.p;
-            R.q_adj_off = s->g_qoff.p; R.q_deg = s->g_qdeg.p; R.fr_slot = s->g_fr_slot.p; R.key_id = s->d_i32c.p; R.out_keys = s->d_keys_a.p;
-            collab_reduce2_kernel<<<dim3(8, m), 128, 0, s->stream>>>(R);
-            ++s->stat_launches;
-            CK(cudaGetLastError());
+            if (pair_matrix) {
+                CollabReduce2Params R;
+                R.nq = m; R.fas = s->d_f32a.p; R.pair_off = s->g_pair_off.p; R.cand_off = s->g_cand_off.p; R.n_slots = s->g_nslots.p;
+                R.q_adj_off = s->g_qoff.p; R.q_deg = s->g_qdeg.p; R.fr_slot = s->g_fr_slot.p; R.key_id = s->d_i32c.p; R.out_keys = s->d_keys_a.p;
+                R.friend_major = E.friend_major;
+                collab_reduce2_kernel<<<dim3(8, m), 128, 0, s->stream>>>(R);
+                ++s->stat_launches;
+                CK(cudaGetLastError());
+            } else {
+                // group planning on the device, then the exact scan kernel in store mode over the candidates of each query
+                TRY(s->g_group_off.reserve((size_t)m + 1)); TRY(s->g_gtotals.reserve(8));
+                CollabGroupsParams G;
+                memset(&G, 0, sizeof(G));
+                G.nq = m; G.T = s->T; G.smem_budget = (uint32_t)s->max_smem - scan_fixed_smem(0) - 256u;
+                G.cand_cnt = s->g_cnt.p; G.cand_off = s->g_cand_off.p; G.n_slots = s->g_nslots.p; G.q_adj_off = s->g_qoff.p;
+                G.slot_row = s->g_slot_row.p; G.ncl = s->g_ncl.p; G.nfr = s->g_nfr.p; G.ntok = s->g_ntok.p;
+                G.group_off = s->g_group_off.p; G.totals = s->g_gtotals.p;
+                collab_groups_count_kernel<<<1, 1024, 0, s->stream>>>(G);
+                unsigned long long tot[5] = {0, 0, 0, 0, 0};
+                CK(cudaMemcpyAsync(tot, s->g_gtotals.p, 8, cudaMemcpyDeviceToHost, s->stream));
+                CK(cudaStreamSynchronize(s->stream));
+                const size_t ng = (size_t)tot[0];
+                TRY(s->d_groups.reserve(std::max<size_t>(ng, 1))); TRY(s->d_items.reserve(std::max<size_t>(ng, 1)));
+                G.groups = s->d_groups.p; G.items = s->d_items.p;
+                collab_groups_fill_kernel<<<1, 1024, 0, s->stream>>>(G);
+                s->stat_launches += 2;
+                CK(cudaMemcpyAsync(tot, s->g_gtotals.p, 40, cudaMemcpyDeviceToHost, s->stream));
+                CK(cudaStreamSynchronize(s->stream));
+                CK(cudaGetLastError());
+                const unsigned long long arena_bytes = tot[1], out_rows = tot[2];
+                if (arena_bytes > 0xF0000000ull || out_rows > 0x7fffff00ull / 32)
+                    return fail(PK_ERR_UNSUPPORTED, "collaborative batch too large (split the batch)");
+                s->stat_groups += (int64_t)ng;
+                if (ng > 0) {
+                    TRY(s->d_arena.reserve(std::max<uint64_t>(arena_bytes, 16)));
+                    CK(cudaMemsetAsync(s->d_arena.p, 0, std::max<uint64_t>(arena_bytes, 16), s->stream));
+                    TRY(s->d_f32b.reserve((size_t)std::max<unsigned long long>(out_rows, 1) * 32));
+                    PrepParams PP;
+                    PP.rec = s->d_rec.p; PP.rec_off = s->d_rec_off.p; PP.groups = s->d_groups.p; PP.arena = s->d_arena.p;
+                    PP.excl_ids = nullptr; PP.lean_fail = nullptr;
+                    group_prep_kernel<<<(unsigned)ng, kPrepThreads, 0, s->stream>>>(PP);
+                    ++s->stat_launches;
+                    CK(cudaGetLastError());
+                    ScanParams SP = base_scan_params(s, 1);
+                    SP.cand_rows = s->d_i32d.p;                        // the flat candidate rows of the batch
+                    SP.out_f = s->d_f32b.p;
+                    const uint32_t fixed = scan_fixed_smem(0);
+                    CK(cudaEventRecord(s->ev2, s->stream));
+                    if (ng > (size_t)tot[4]) {
+                        SP.want_smem = 1; SP.smem_arena_bytes = (uint32_t)tot[3];
+                        TRY((launch_scan_t<EPI_STORE, false>(s, SP, s->d_items.p, ng, true, (uint32_t)tot[3] + fixed)));
+                    }
+                    if (tot[4] > 0) {
+                        SP.want_smem = 0; SP.smem_arena_bytes = 0;
+                        TRY((launch_scan_t<EPI_STORE, false>(s, SP, s->d_items.p, ng, false, fixed)));
+                    }
+                    CK(cudaEventRecord(s->ev3, s->stream));
+                    s->rescore_time_pending = false;
+                }
+                CollabReduce3Params R;
+                R.nq = m; R.w = s->d_f32a.p; R.mat = s->d_f32b.p; R.pair_off = s->g_pair_off.p; R.cand_off = s->g_cand_off.p;
+                R.n_slots = s->g_nslots.p; R.q_adj_off = s->g_qoff.p; R.q_deg = s->g_qdeg.p; R.fr_slot = s->g_fr_slot.p;
+                R.group_off = s->g_group_off.p; R.key_id = s->d_i32c.p; R.items = s->d_items.p; R.out_keys = s->d_keys_a.p;
+                collab_reduce3_kernel<<<dim3(8, m), 128, 0, s->stream>>>(R);
+                ++s->stat_launches;
+                CK(cudaGetLastError());
+                // the matrix kernels' time joins the scan-kernel statistic
+                CK(cudaStreamSynchronize(s->stream));
+                if (ng > 0) {
+                    float ms = 0.f;
+                    CK(cudaEventElapsedTime(&ms, s->ev2, s->ev3));
+                    s->stat_scan_ns += (int64_t)((double)ms * 1e6);
+                    s->stat_pairs += (int64_t)out_rows * 32;
+                }
+            }
         }
         TRY(launch_slice_topk(s, s->d_keys_a.p, s->g_cand_off.p, m, K, s->d_keys_b.p));
         CK(cudaMemcpyAsync(keys.data() + (size_t)q0 * K, s->d_keys_b.p, (size_t)m * K * 8, cudaMemcpyDeviceToHost, s->stream));
@@ -2067,6 +2227,7 @@ int pk_store_create(int device, pk_store** out) {
 void pk_store_destroy(pk_store* s) {
     if (!s) return;
     cudaSetDevice(s->device);
+    for (int r = 0; r < 7; ++r) if (s->peer_mapped[r]) cudaIpcCloseMemHandle(s->peer_mapped[r]);
     if (s->stream) cudaStreamSynchronize(s->stream);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
@@ -2211,6 +2372,7 @@ int pk_store_load_world(pk_store* s, const pk_world* w) {
     s->shard_begin = 0; s->shard_end = n;
     ++s->gen;
     s->job.valid = false;
+    s->seed_b = s->seed_e = -1;
     s->loaded = true;
     return PK_OK;
 }
@@ -2487,6 +2649,55 @@ int pk_fullscan_execute_shortlists(pk_store* s) {
     return fullscan_shortlists(s);
 }
 
+int pk_fullscan_theta_export(pk_store* s, void* handle64) {
+    if (!s || !handle64) return fail(PK_ERR_ARG, "null argument");
+    CK(cudaSetDevice(s->device));
+    TRY(s->d_theta_x.reserve(pk_store::kThetaCap));
+    cudaIpcMemHandle_t h;
+    static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    CK(cudaIpcGetMemHandle(&h, s->d_theta_x.p));
+    memcpy(handle64, &h, 64);
+    return PK_OK;
+}
+
+void* pk_fullscan_theta_ptr(pk_store* s) {
+    if (!s) return nullptr;
+    cudaSetDevice(s->device);
+    if (s->d_theta_x.reserve(pk_store::kThetaCap) != PK_OK) return nullptr;
+    return s->d_theta_x.p;
+}
+
+int pk_fullscan_theta_peers(pk_store* s, const void* handles, int n_ranks, int rank, const void* const* d_ptrs) {
+    if (!s || n_ranks < 1 || n_ranks > 8 || rank < 0 || rank >= n_ranks || (!handles && !d_ptrs)) return fail(PK_ERR_ARG, "bad argument");
+    CK(cudaSetDevice(s->device));
+    for (int r = 0; r < 7; ++r) {
+        if (s->peer_mapped[r]) cudaIpcCloseMemHandle(s->peer_mapped[r]);
+        s->peer_mapped[r] = nullptr; s->peer_theta[r] = nullptr;
+    }
+    s->n_peers = 0;
+    s->exec_counter = 0;            // every rank restarts its execution counter here: the tags stay in step
+    for (int r = 0; r < n_ranks; ++r) {
+        if (r == rank) continue;
+        void* p = nullptr;
+        if (d_ptrs) p = const_cast<void*>(d_ptrs[r]);
+        else {
+            cudaIpcMemHandle_t h;
+            memcpy(&h, (const char*)handles + (size_t)r * 64, 64);
+            cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+            if (e != cudaSuccess) {
+                cudaGetLastError();
+                for (int i = 0; i < s->n_peers; ++i) { if (s->peer_mapped[i]) cudaIpcCloseMemHandle(s->peer_mapped[i]); s->peer_mapped[i] = nullptr; s->peer_theta[i] = nullptr; }
+                s->n_peers = 0;
+                return fail(PK_ERR_CUDA, "cudaIpcOpenMemHandle(rank %d): %s (the scan runs without threshold sharing)", r, cudaGetErrorString(e));
+            }
+            s->peer_mapped[s->n_peers] = p;
+        }
+        if (!p) continue;
+        s->peer_theta[s->n_peers++] = reinterpret_cast<const unsigned long long*>(p);
+    }
+    return PK_OK;
+}
+
 int pk_fullscan_shortlist_keys(pk_store* s, uint64_t* d_short) {
     if (!s || !d_short) return fail(PK_ERR_ARG, "null argument");
     FullscanJob& J = s->job;
@@ -2597,7 +2808,7 @@ int pk_candidates_batch(pk_store* s, int mode, int nq, const int32_t* q_uid, int
     if (limit < 1 || limit > 16384 || s->max_deg > 32768 || !s->adj_override.empty() || s->adj.size() > 0x7fffff00ull)
         return fail(PK_ERR_UNSUPPORTED, "the device expansion takes limits in [1, 16384] on an adjacency without overridden rows");
     if (nq == 0) return PK_OK;
-    CK(cudaSetDevice(s->device));
+    TRY(ensure_ready(s));
     for (int q0 = 0; q0 < nq; q0 += 8192) {
         const int m = std::min(8192, nq - q0);
         TRY(expand_batch(s, mode, m, q_uid + q0, limit, true));

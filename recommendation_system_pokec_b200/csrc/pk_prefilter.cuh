@@ -66,6 +66,13 @@ struct PreParams {
     const uint4* lrec;
     const uint64_t* lrec_off;
     const uint2* lmask;          // [row] 64-bit mask of non-empty text columns (8 bytes per candidate: the level-1 test)
+    // Scan order.  The first n_list positions of a group's cursor are the shard's HEAVIEST rows (row_list, most tokens
+    // first-class candidates for every top-k), the following positions the shard in row order minus those rows
+    // (skip[row] != 0).  The thresholds theta are then close to their final values after a few hundred candidates
+    // instead of tens of thousands -- the warm-up is a fixed cost per launch, i.e. what an 8-GPU shard pays 8x as often.
+    const int32_t* row_list;
+    const uint8_t* skip;
+    int n_list;
     const GroupDesc* groups;
     const WorkItem* items;
     const uint8_t* arena;
@@ -88,8 +95,17 @@ struct PreParams {
     // BOUND (exact scalar fields, every jointly filled text column / set field at its largest sigma) lies below
     // theta for all 32 queries is skipped after its 64-byte header -- it cannot reach the exact top-k, so the
     // shortlist does not need it (the proof of shortlist_check_kernel only needs the candidates >= a_k - 2 margin).
-    // dyn_theta[group][32] carries the best theta any instance of the group has reached (float bits, atomicMax).
-    unsigned int* dyn_theta;
+    // dyn_theta[group][32] carries the best theta any instance of the group has reached: a 64-bit word
+    // {theta_tag, float bits}, raised with atomicMax (the array is zeroed per execution, so the tag is constant in it).
+    // peer_theta[r] are the same arrays of the OTHER ranks of a sharded scan, mapped through NVLink peer memory
+    // (cudaIpc): warp 0 of every CTA polls one peer per chunk and folds what it finds into its own array.  Every
+    // rank's k-th best score is a lower bound of the merged k-th best, so a peer's theta is valid on this shard too --
+    // if it belongs to the same execution of the same plan, which is what the tag (plan fingerprint + execution
+    // counter) says; anything else is ignored.
+    unsigned long long* dyn_theta;
+    const unsigned long long* peer_theta[7];
+    int n_peers;
+    unsigned int theta_tag;
     int K;                       // the caller's k (theta watches list position K - 1)
     float theta_drop;            // 2 margin + slack
     int cand_begin, cand_end;    // the shard's row range
@@ -156,7 +172,7 @@ __device__ __forceinline__ void l1_update_warp(float th, const float* frow, floa
 // arguments; keys are unique -- one per candidate row).
 __device__ __forceinline__ void shortlist_insert(uint64_t* list, int K, uint64_t key, int* lock, volatile uint64_t* tau,
                                                  int lane, int k_user, float theta_drop, volatile float* theta,
-                                                 unsigned int* g_theta, const float* frow, float ub_text, float inv_total,
+                                                 unsigned long long* g_theta, unsigned int tag, const float* frow, float ub_text, float inv_total,
                                                  volatile uint4* q4, volatile float* bnd) {
     if (lane == 0) {
         while (atomicCAS(lock, 0, 1) != 0) __nanosleep(32);
@@ -185,7 +201,7 @@ __device__ __forceinline__ void shortlist_insert(uint64_t* list, int K, uint64_t
                 const float th = fmaxf(__uint_as_float(key_score_bits(kk)) - theta_drop, 0.f);
                 if (th > *theta) {
                     *theta = th;
-                    if (g_theta) atomicMax(g_theta, __float_as_uint(th));
+                    if (g_theta) atomicMax(g_theta, ((unsigned long long)tag << 32) | __float_as_uint(th));
                     th_moved = th;
                 }
             }
@@ -247,7 +263,7 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
     } else {
         // ---- pick a group and one of its shortlist instances (PreParams: dynamic scheduling) ----
         if (warp == 0) {
-            const int n_cand = P.cand_end - P.cand_begin;
+            const int n_cand = P.n_list + (P.cand_end - P.cand_begin);      // cursor positions
             int g = -1, inst = -1;
             for (int attempt = 0; attempt < 8 && g < 0; ++attempt) {
                 int best = -1, best_rem = 0;
@@ -281,12 +297,12 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
         const int gi = pick[0], inst = pick[1];
         if (gi < 0) break;
         it.group = P.dyn_groups[gi];
-        it.cand_begin = P.cand_begin; it.cand_end = P.cand_end;
+        it.cand_begin = 0; it.cand_end = P.n_list + (P.cand_end - P.cand_begin);        // cursor positions, see PreParams
         it.out_slot = gi * P.max_inst + inst;
     }
     const GroupDesc* gd = P.groups + it.group;
     int* const cursor = STORE ? next : P.dyn_cursor + pick[0];
-    const int cursor_base = STORE ? 0 : it.cand_begin;
+    const int cursor_base = 0;
 
     {
         const uint4* src = reinterpret_cast<const uint4*>(P.arena + gd->arena_off);
@@ -349,7 +365,8 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
         l1b[lane] = q_active ? 0.f : 3.0e38f;        // theta = 0: every count admissible
     }
     __syncthreads();
-    unsigned int* const g_theta = STORE ? nullptr : P.dyn_theta + (size_t)pick[0] * 32 + lane;
+    unsigned long long* const g_theta = STORE ? nullptr : P.dyn_theta + (size_t)pick[0] * 32 + lane;
+    int peer_rr = 0;                // next peer to poll (warp 0)
     float th_g = 0.f;               // the group's published threshold, re-read once per chunk
 
 #ifdef PK_PRE_CHUNK
@@ -369,11 +386,34 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
         const int c1 = min(c0 + kChunk, it.cand_end);
         uint64_t offv = 0;
         uint2 cm = make_uint2(0u, 0u);
-        if (c0 + lane < c1) { offv = __ldg(P.lrec_off + c0 + lane); if (!STORE) cm = __ldg(P.lmask + c0 + lane); }
-        uint32_t surv = (c1 - c0 >= 32) ? kFull : ((1u << (c1 - c0)) - 1u);
+        int myrow = c0 + lane;
+        bool live = c0 + lane < c1;
+        if (!STORE && live) {
+            const int pos = c0 + lane;
+            if (pos < P.n_list) myrow = __ldg(P.row_list + pos);
+            else {
+                myrow = P.cand_begin + (pos - P.n_list);
+                if (P.skip != nullptr && __ldg(P.skip + myrow) != 0) live = false;      // already scanned as a heavy row
+            }
+        }
+        if (live) {
+            offv = __ldg(P.lrec_off + myrow);
+            if (!STORE) cm = __ldg(P.lmask + myrow);
+        }
+        uint32_t surv = __ballot_sync(kFull, live);
         if (!STORE) {
             // thresholds published by the other instances of the group
-            th_g = __uint_as_float(*reinterpret_cast<volatile unsigned int*>(g_theta));
+            if (warp == 0 && P.n_peers > 0) {
+                // one peer per chunk, round robin: its threshold for MY query, accepted only under the same tag
+                const unsigned long long pv = *reinterpret_cast<const volatile unsigned long long*>(
+                    P.peer_theta[peer_rr] + (size_t)pick[0] * 32 + lane);
+                peer_rr = (peer_rr + 1 == P.n_peers) ? 0 : peer_rr + 1;
+                if ((unsigned int)(pv >> 32) == P.theta_tag) atomicMax(g_theta, pv);
+            }
+            {
+                const unsigned long long gv = *reinterpret_cast<volatile unsigned long long*>(g_theta);
+                th_g = ((unsigned int)(gv >> 32) == P.theta_tag) ? __uint_as_float((unsigned int)gv) : 0.f;
+            }
             if (th_g > reinterpret_cast<volatile float*>(theta)[lane]) {
                 reinterpret_cast<volatile float*>(theta)[lane] = th_g;
                 if (th_g > reinterpret_cast<volatile float*>(l1b)[lane])
@@ -397,7 +437,7 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
         while (surv) {
             const int si = __ffs(surv) - 1;
             surv &= surv - 1;
-            const int ci = c0 + si;
+            const int ci = STORE ? c0 + si : __shfl_sync(kFull, myrow, si);      // the candidate's store row
             const uint64_t off = __shfl_sync(kFull, offv, si);
             const uint4* cr = P.lrec + off;
             const uint32_t* cw = reinterpret_cast<const uint32_t*>(cr);
@@ -574,7 +614,7 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                         pass &= pass - 1;
                         const uint64_t kj = __shfl_sync(kFull, key, j);
                         shortlist_insert(lists + j * Ks, Ks, kj, locks + j, reinterpret_cast<volatile uint64_t*>(tau) + j, lane, P.K,
-                                         P.theta_drop, reinterpret_cast<volatile float*>(theta) + j, g_theta - lane + j,
+                                         P.theta_drop, reinterpret_cast<volatile float*>(theta) + j, g_theta - lane + j, P.theta_tag,
                                          l1f + j * 8, ub_text, inv_total, reinterpret_cast<volatile uint4*>(l1q) + j,
                                          reinterpret_cast<volatile float*>(l1b) + j);
                     }

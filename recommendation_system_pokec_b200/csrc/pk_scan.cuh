@@ -221,6 +221,7 @@ struct ScanParams {
     const int32_t* cand_rows;    // explicit candidate rows (negative = skip), or null = the row index itself
     const int32_t* group_flag;   // when set: CTAs of groups whose flag is 0 exit at once (fallback pass of the full scan)
     int group_lo, group_hi;      // CTAs of groups outside [group_lo, group_hi) exit at once (re-score split over ranks)
+    int want_smem;               // >= 0: CTAs of groups whose in_smem differs exit at once (device-planned items are not sorted)
     int T;
     int K, Kp;                   // top-k and its padding to a multiple of 32
     int exclude_mode;
@@ -312,6 +313,7 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
     const GroupDesc* gd = P.groups + it.group;
     if (P.group_flag && P.group_flag[it.group] == 0) return;   // uniform for the CTA
     if (it.group < P.group_lo || it.group >= P.group_hi) return;
+    if (P.want_smem >= 0 && gd->in_smem != P.want_smem) return;
 
     // ---- shared memory carve-up ------------------------------------------------------------
     const uint32_t arena_sm = SM ? P.smem_arena_bytes : 0u;
@@ -433,6 +435,18 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
                 ++used;
                 if (FIELDS) fo[0] = (float)((double)matches / (sqrt((double)q_acnt) * sqrt((double)c_bcnt)));
             }
+            // The fields that need the sigma(z(s)) chain (an fp64 division, exp, another division) are QUEUED per lane --
+            // {field, numerator}, in field order -- and evaluated after the candidate's last cell, entry k of every
+            // lane together.  Evaluated where they arise (round 1) the chain ran once per candidate cell in which ANY
+            // lane had a match, with 3-4 lanes active: 44 % of this kernel's warp instructions.  The sum then runs in
+            // the reference's field order (clubs, friends, text columns ascending), sigma(z(0)) for the joint fields
+            // that are not in the queue, so every double is added exactly where the reference adds it.
+            double qv[2 + kMaxT], qd[2] = {0.0, 0.0};
+            uint8_t qf[2 + kMaxT];
+            int qn = 0;
+            uint64_t matched = 0ull;
+            bool has_set[2] = {false, false};
+            int inter_of[2] = {0, 0};
             // clubs / friends: |{b in B : b in A}| / (sqrt|A| sqrt|B|) (:79-91, src/recommender.cpp:119-128)
             #pragma unroll
             for (int which = 0; which < 2; ++which) {
@@ -456,20 +470,20 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
                 }
                 const uint32_t q_n = which ? q_nfr : q_ncl;
                 if (q_n > 0) {
-                    const int f = 5 + which;
-                    double sg = N->sig0[f];
+                    has_set[which] = true;
+                    inter_of[which] = inter;
+                    ++used;
                     if (inter > 0) {
-                        const double denom = (which ? q_sqf : q_sqc) * __hiloint2double(which ? (int)h4.w : (int)h4.y,
-                                                                                        which ? (int)h4.z : (int)h4.x);
-                        const float s = (denom > 0.0) ? (float)((double)inter / denom) : 0.0f;
-                        sg = pk_sigmoid(pk_z(N, f, (double)s));
-                        if (FIELDS) fo[1 + which] = s;
-                    } else if (FIELDS) fo[1 + which] = 0.0f;
-                    if (FIELDS) fo[3 + T + which] = __int_as_float(inter);
-                    sum += sg; ++used;
+                        qf[qn] = (uint8_t)(5 + which);
+                        qv[qn] = (double)inter;
+                        qd[which] = (which ? q_sqf : q_sqc) * __hiloint2double(which ? (int)h4.w : (int)h4.y, which ? (int)h4.z : (int)h4.x);
+                        ++qn;
+                    }
+                    if (FIELDS) { fo[1 + which] = 0.0f; fo[3 + T + which] = __int_as_float(inter); }
                 }
             }
             // text columns (:93-114): tf-idf cosine per jointly non-empty column
+            const uint64_t joint = q_mask & c_mask;
             if (c_ncells > 0) {
                 const uint4* cells = cr + (o_cells >> 2);
                 const uint32_t* keys = cw + o_keys;
@@ -500,19 +514,13 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
                             if ((mj >> lane) & 1u) dot = __dadd_rn(dot, __dmul_rn(vals[bj + __popc(mj & lane_lt)], wj));
                         }
                         pos = e;
-                        if (pos == cend) {   // cell complete: this lane's sigma for column ct
+                        if (pos == cend) {   // cell complete: queue this lane's dot product of column ct
                             const int ct = (int)(ch.x & 0xffu);
-                            if ((q_mask >> ct) & 1ull) {
-                                const int f = kNumFixed + ct;
-                                double sg = N->sig0[f];
-                                float s = 0.0f;
-                                if (dot != 0.0) {
-                                    const double denom = nq[ct * 32 + lane] * __hiloint2double((int)ch.w, (int)ch.z);
-                                    s = (denom > 0.0) ? (float)(dot / denom) : 0.0f;
-                                    sg = (s == 1.0f) ? N->sig1[f] : pk_sigmoid(pk_z(N, f, (double)s));
-                                }
-                                if (FIELDS) fo[3 + ct] = s;
-                                sum += sg;
+                            if (dot != 0.0 && ((joint >> ct) & 1ull)) {
+                                qf[qn] = (uint8_t)(kNumFixed + ct);
+                                qv[qn] = dot;
+                                ++qn;
+                                matched |= 1ull << ct;
                             }
                             dot = 0.0;
                             ++cell;
@@ -520,7 +528,36 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
                         }
                     }
                 }
-                used += __popcll(q_mask & c_mask);
+                used += __popcll(joint);
+            }
+            // evaluation pass: queue entry k of every lane of the warp together
+            for (int k = 0; k < qn; ++k) {
+                const int f = qf[k];
+                double den;
+                if (f >= kNumFixed) {          // the candidate cell's norm sits at the rank of the column in its mask
+                    const int ct = f - kNumFixed;
+                    const uint4 cc = __ldg(cr + (o_cells >> 2) + __popcll(c_mask & ((1ull << ct) - 1ull)));
+                    den = nq[ct * 32 + lane] * __hiloint2double((int)cc.w, (int)cc.z);
+                } else den = qd[f - 5];
+                const float s = (den > 0.0) ? (float)(qv[k] / den) : 0.0f;
+                qv[k] = (f >= kNumFixed && s == 1.0f) ? N->sig1[f] : pk_sigmoid(pk_z(N, f, (double)s));
+                if (FIELDS) fo[f >= kNumFixed ? 3 + (f - kNumFixed) : f - 4] = s;
+            }
+            // ordered sum
+            {
+                int k = 0;
+                if (has_set[0]) sum += (inter_of[0] > 0) ? qv[k++] : N->sig0[5];
+                if (has_set[1]) sum += (inter_of[1] > 0) ? qv[k++] : N->sig0[6];
+                uint64_t jm = (c_ncells > 0) ? joint : 0ull;
+                while (jm) {
+                    const int ct = __ffsll((long long)jm) - 1;
+                    jm &= jm - 1;
+                    if ((matched >> ct) & 1ull) sum += qv[k++];
+                    else {
+                        sum += N->sig0[kNumFixed + ct];
+                        if (FIELDS) fo[3 + ct] = 0.0f;
+                    }
+                }
             }
 
             // S, F, harmonic mean (:116-123)

@@ -26,7 +26,7 @@ ABI_SYMBOLS = (
     "pk_idf_size", "pk_get_idf", "pk_set_adj_row", "pk_pair_similarity", "pk_pair_fields", "pk_pair_overlap",
     "pk_fullscan_topk", "pk_fullscan_prepare", "pk_fullscan_execute", "pk_fullscan_fetch", "pk_fullscan_keys", "pk_recommend", "pk_candidates", "pk_fullscan_local_keys", "pk_merge_keys", "pk_sync",
     "pk_normalizers_from_pairs", "pk_edge_cache_build", "pk_edge_cache_drop", "pk_edge_cache_row", "pk_fullscan_execute_shortlists", "pk_fullscan_shortlist_keys", "pk_fullscan_execute_finish",
-    "pk_stream", "pk_stat", "pk_debug_prefilter", "pk_world_save", "pk_world_open", "pk_world_close", "pk_candidates_batch",
+    "pk_stream", "pk_stat", "pk_debug_prefilter", "pk_world_save", "pk_world_open", "pk_world_close", "pk_candidates_batch", "pk_fullscan_theta_export", "pk_fullscan_theta_ptr", "pk_fullscan_theta_peers",
 )
 STAT_KERNEL_LAUNCHES, STAT_PAIRS_SCORED, STAT_STORE_BYTES, STAT_SCAN_KERNEL_NS, STAT_SCAN_LAUNCHES, STAT_GROUPS, \
     STAT_SHARD_RECORD_BYTES, STAT_H2D_BYTES, STAT_D2H_BYTES, STAT_PREFILTER, STAT_FALLBACK_QUERIES, STAT_RESCORE_NS, \
@@ -279,6 +279,25 @@ class DeviceRecommender:
 
     def fullscan_execute(self):
         _check(self.lib, self.lib.pk_fullscan_execute(self.h))
+
+    def theta_export(self) -> bytes:
+        """the cudaIpc handle of this store's pruning-threshold array (64 bytes)"""
+        buf = C.create_string_buffer(64)
+        _check(self.lib, self.lib.pk_fullscan_theta_export(self.h, buf))
+        return buf.raw
+
+    def theta_ptr(self) -> int:
+        self.lib.pk_fullscan_theta_ptr.restype = C.c_void_p
+        self.lib.pk_fullscan_theta_ptr.argtypes = [C.c_void_p]
+        return int(self.lib.pk_fullscan_theta_ptr(self.h) or 0)
+
+    def theta_peers(self, handles: bytes = None, n_ranks: int = 1, rank: int = 0, ptrs=None):
+        """maps the other ranks' threshold arrays (handles: n_ranks x 64 bytes) or, in one process, their device pointers"""
+        if ptrs is not None:
+            arr = (C.c_void_p * n_ranks)(*[C.c_void_p(p) for p in ptrs])
+            _check(self.lib, self.lib.pk_fullscan_theta_peers(self.h, None, int(n_ranks), int(rank), arr))
+        else:
+            _check(self.lib, self.lib.pk_fullscan_theta_peers(self.h, handles, int(n_ranks), int(rank), None))
 
     def fullscan_execute_shortlists(self):
         _check(self.lib, self.lib.pk_fullscan_execute_shortlists(self.h))

@@ -57,3 +57,31 @@ def all_gather_keys(local_keys, world_size):
     out = torch.zeros((world_size,) + tuple(local_keys.shape), dtype=local_keys.dtype, device=local_keys.device)
     dist.all_gather_into_tensor(out.view(-1), local_keys.reshape(-1).contiguous())
     return out
+
+
+
+def share_thetas(dev, rank, world_size, device):
+    """Gives every rank's store the cudaIpc handles of the other ranks' pruning-threshold arrays
+    (pk_fullscan_theta_export -> all-gather of 64 bytes per rank -> pk_fullscan_theta_peers): the pre-filter then reads
+    its peers' thresholds over NVLink while it scans.  Returns True when the peers were mapped; a box without peer
+    access keeps scanning without sharing (the results do not depend on it)."""
+    import torch
+    import torch.distributed as dist
+    if world_size <= 1:
+        return False
+    mine = torch.tensor(list(dev.theta_export()), dtype=torch.uint8, device=device)
+    allh = torch.zeros(world_size * 64, dtype=torch.uint8, device=device)
+    dist.all_gather_into_tensor(allh, mine)
+    ok = True
+    try:
+        dev.theta_peers(bytes(allh.cpu().numpy().tobytes()), world_size, rank)
+    except Exception as e:                 # PokecError: no peer access
+        import sys
+        print(f"[sharding] rank {rank}: thresholds not shared ({e})", file=sys.stderr, flush=True)
+        ok = False
+    flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if int(flag.item()) == 0 and ok:       # all or nothing: a half-connected group would still be correct, but keep it simple
+        dev.theta_peers(None, 1, 0, ptrs=[0])
+        ok = False
+    return ok

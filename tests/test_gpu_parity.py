@@ -292,6 +292,65 @@ def test_sharded_scan_with_shared_rescore(env):
         assert np.array_equal(x, y)
 
 
+def test_sharded_scan_thresholds_shared_over_peer_memory(small_world):
+    """three `ranks` = three stores of this process on three candidate shards, each reading the other two's pruning
+    thresholds while it scans (pk_fullscan_theta_peers with device pointers; across processes the same arrays travel as
+    cudaIpc handles).  A rank's own shortlist may now lack candidates that cannot reach the GLOBAL top-k -- the merged,
+    proven, re-scored result must still equal the unsharded scan.  A store that prepared other queries, or is one
+    execution ahead, must be ignored (tag mismatch), not believed."""
+    import torch
+    from recommendation_system_pokec_b200.engine import DeviceRecommender, STAT_SHORTLIST
+    w = small_world
+    cuts = [0, w.n // 3 + 5, 2 * w.n // 3 - 11, w.n]
+    devs = [DeviceRecommender(w) for _ in range(3)]
+    ptrs = [d.theta_ptr() for d in devs]
+    assert all(ptrs)
+    q = sample_queries(w, 150, seed=14)
+    k = 50
+    ref = devs[0].fullscan(q, k, EXCLUDE_SELF_AND_ADJ)                      # unsharded, no peers yet
+    for r, d in enumerate(devs):
+        d.set_shard(cuts[r], cuts[r + 1])
+        d.theta_peers(None, 3, r, ptrs=[0 if i == r else ptrs[i] for i in range(3)])
+
+    def run(queries_of):
+        shorts = None
+        for r, d in enumerate(devs):
+            d.fullscan_prepare(queries_of(r), k, EXCLUDE_SELF_AND_ADJ)
+            ks = d.stat(STAT_SHORTLIST)
+            if shorts is None:
+                shorts = torch.zeros((3, len(q), ks), dtype=torch.int64, device="cuda")
+        for r, d in enumerate(devs):                                        # lock-step: execution n of every rank
+            d.fullscan_execute_shortlists()
+            d.fullscan_shortlist_keys(shorts[r].data_ptr())
+            d.sync()
+        keys = torch.zeros((3, len(q), k), dtype=torch.int64, device="cuda")
+        for r, d in enumerate(devs):
+            d.fullscan_execute_finish(shorts.data_ptr(), 3, r, 3)
+            d.fullscan_keys(keys[r].data_ptr())
+            d.sync()
+        return devs[0].merge_keys(keys.data_ptr(), 3, len(q), k)
+
+    for _ in range(2):                                                      # two executions: the tags move together
+        merged = run(lambda r: q)
+        for x, y in zip(merged, ref):
+            assert np.array_equal(x, y)
+    # rank 1 prepares a permutation of the batch: same size, other fingerprint -> its thresholds must not be used
+    q2 = q[::-1].copy()
+    d1_alone = devs[1].fullscan(q2, k, EXCLUDE_SELF_AND_ADJ)               # (also puts rank 1 one execution ahead)
+    devs[0].fullscan_prepare(q, k, EXCLUDE_SELF_AND_ADJ)
+    devs[0].fullscan_execute()
+    got0 = devs[0].fullscan_fetch()
+    solo = DeviceRecommender(w)
+    solo.set_shard(cuts[0], cuts[1])
+    want0 = solo.fullscan(q, k, EXCLUDE_SELF_AND_ADJ)
+    # rank 0 saw only stale / foreign thresholds from its peers: its shard-local result is the plain shard scan
+    for x, y in zip(got0, want0):
+        assert np.array_equal(x, y)
+    assert d1_alone[2].min() > 0
+    for d in devs + [solo]:
+        d.close()
+
+
 def test_sharded_scan_tie_heavy_fallback(oracle_libs):
     """unproven queries in the N-rank pipeline: every rank runs their exact scan over its own shard, the key merge
     puts the shards together -- identical to the unsharded result"""

@@ -145,3 +145,4 @@ def test_two_rank_shared_rescore_over_gloo(tmp_path, oracle_libs):
     s.close()
     mp.spawn(_worker_shared_rescore, args=(2, port, 20, 64, str(tmp_path)), nprocs=2, join=True)
     assert (tmp_path / "ok0").exists() and (tmp_path / "ok1").exists()
+

@@ -25,7 +25,7 @@ sys.path.insert(0, ROOT)
 
 from recommendation_system_pokec_b200.synth import POKEC_N  # noqa: E402
 from recommendation_system_pokec_b200.cabi import EXCLUDE_SELF_AND_ADJ  # noqa: E402
-from recommendation_system_pokec_b200.sharding import shard_rows  # noqa: E402
+from recommendation_system_pokec_b200.sharding import shard_rows, share_thetas  # noqa: E402
 
 
 def sweep(w, ws, rank, lr, B, k, n_batches, depth=2, keep_batches=(), batch_fn=None, stats=None):
@@ -54,6 +54,7 @@ def sweep(w, ws, rank, lr, B, k, n_batches, depth=2, keep_batches=(), batch_fn=N
         def __init__(self):
             self.dev = DeviceRecommender(w, device=lr)
             self.dev.set_shard(lo, hi)
+            share_thetas(self.dev, rank, ws, f"cuda:{lr}")      # slot i of every rank pairs with slot i of the others
             self.stream = torch.cuda.ExternalStream(self.dev.stream(), device=lr)
             self.local = torch.zeros((B, k), dtype=torch.int64, device=f"cuda:{lr}")
             self.gathered = torch.zeros((ws, B, k), dtype=torch.int64, device=f"cuda:{lr}")

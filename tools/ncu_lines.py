@@ -45,7 +45,7 @@ def main():
         try:
             inst = int(r[ci["Instructions Executed"]])
             smp = int(r[ci["# Samples"]])
-            wf = int(r[ci["L1 Wavefronts Shared"]] or 0)
+            wf = int(r[ci["L1 Wavefronts Shared"]] or 0) if "L1 Wavefronts Shared" in ci else 0
             ti = int(r[ci["Thread Instructions Executed"]])
         except (ValueError, KeyError):
             continue
