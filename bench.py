@@ -369,7 +369,7 @@ def main():
               "users": args.users, "queries_per_step": args.queries, "topk": args.topk,
               "exclude": "self + existing friends (recommender_graph.cpp:46-52)",
               "l2": "inputs larger than L2 (packed store >> 126 MB)",
-              "normalizers": "compute_column_normalizers(.., 100000, 5) semantics (src/utils.cpp:155-240) on the device (SURVEY 8 f3)",
+              "normalizers": "compute_column_normalizers(.., 100000, 5) (src/utils.cpp:155-240)",
               "parallelism": f"candidate rows sharded over {world_size} GPU(s); NCCL all-gather of the approximate shortlists, exact re-score split by query group, NCCL all-gather of the top-k keys + merge" if world_size > 1
               else "1 GPU"}
 
@@ -378,12 +378,11 @@ def main():
         if rank != 0:
             return 0
         w = build_world(args.users)      # the same world as our arm; the sample is its first rows
-        config["normalizers"] = "the reference's own compute_column_normalizers(.., 100000, 5) on the sampled store"
         base, step_s = cpu_reference_run(w, args.users, min(args.cpu_sample_users, w.n), 2, max(args.steps, 1), args.warmup, threads)
         out = {"impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus,
                "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True,
                "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
-               "cpu_baseline": base,
+               "cpu_baseline": base, "normalizer_source": "the reference's own compute_column_normalizers on the sampled store",
                "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                "gpu_launches": 0}
         emit(out)
@@ -582,7 +581,7 @@ def main():
                         "rescore_and_fallback_ms": dev.stat(engine.STAT_RESCORE_NS) / 1e6,
                         "lean_record_bytes_shard": dev.stat(engine.STAT_SHARD_LEAN_BYTES),
                         "exact_record_bytes_shard": dev.stat(engine.STAT_SHARD_RECORD_BYTES),
-                        "normalizer_pairs": n_norm_pairs,
+                        "normalizer_pairs": n_norm_pairs, "normalizer_source": "pk_normalizers_from_pairs on the device (SURVEY 8 f3)",
                         "thresholds_shared_over_nvlink": bool(thetas_shared)}}
 
     # ---- C5 (N > 1): the all-users sweep through the end-to-end calls, two batches in flight ----------------
