@@ -271,7 +271,7 @@ def run_list_config(name, dev, orc, world, q, mode, k, limit, threads, peak, rep
     """one BASELINE list-mode config on the resident store: end-to-end query-users/s (host uids in, host lists out),
     parity of a query sample with the reference, the reference timed on that sample, the 8d byte-formula roofline"""
     from recommendation_system_pokec_b200 import engine
-    dev.recommend(mode, q[:256], k, limit)                       # warm-up (allocations)
+    dev.recommend(mode, q, k, limit)                             # warm-up at the full batch size (grow-only device buffers)
     t = time.perf_counter()
     for _ in range(reps):
         got = dev.recommend(mode, q, k, limit)

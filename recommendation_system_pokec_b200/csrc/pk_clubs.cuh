@@ -35,12 +35,14 @@ struct ClubParams {
     int32_t* con_slot;                // per contribution (indexed inside the user's slot slice): table slot or -1
     uint64_t* slot_key;               // in: 0; during: club id + 1; out: sort key of (score, club id) or 0
     double* slot_acc;                 // in: 0
+    uint64_t* out_keys;               // the user's keys compacted to the front of its slice (selection reads only these)
+    int32_t* out_cnt;                 // [nu] number of keys of each user
 };
 
 __global__ void __launch_bounds__(kClubThreads) clubs_scatter_kernel(const ClubParams P) {
     const int u = blockIdx.x, tid = threadIdx.x;
     const int eb = P.user_edge_begin[u], ee = P.user_edge_begin[u + 1];
-    if (eb == ee) return;                 // no entries (unknown user, no profiled friend): the slice stays empty
+    if (eb == ee) { if (tid == 0) P.out_cnt[u] = 0; return; }     // no entries (unknown user, no profiled friend)
     const int sb = P.user_slot_begin[u];
     const uint32_t cap = (uint32_t)(P.user_slot_begin[u + 1] - sb);
     const uint32_t msk = cap - 1u;
@@ -86,28 +88,54 @@ __global__ void __launch_bounds__(kClubThreads) clubs_scatter_kernel(const ClubP
     }
     __syncthreads();
 
-    // phase B (every thread replays the ordered stream, adds into the slots it owns)
-    for (int e = eb; e < ee; ++e) {
-        const ClubEdge ed = P.edges[e];
-        const double w = (double)P.fas[ed.w_idx];
-        double v = w;
-        if (ed.s_idx >= 0) v = __dmul_rn(w, (double)P.fas[ed.s_idx]);   // contrib = wuf * s_f_fof (:58)
-        const uint32_t c0 = P.con_off[e];
-        const uint32_t c1 = (e + 1 < ee) ? P.con_off[e + 1] : 0xffffffffu;
-        const uint32_t* tr = reinterpret_cast<const uint32_t*>(P.rec + P.rec_off[ed.target_row]);
-        const uint32_t ncl = (c1 != 0xffffffffu) ? (c1 - c0) : tr[8];
-        for (uint32_t j = 0; j < ncl; ++j) {
-            const int32_t sl = cslot[c0 + j];
-            if (sl >= 0 && (sl & (kClubThreads - 1)) == tid) acc[sl] = __dadd_rn(acc[sl], v);
+    // phase B: ONE warp replays the ordered stream -- edge after edge, the target's clubs across the lanes -- so every
+    // club's double sum is taken in the reference's visiting order (round 1 let all 256 threads replay the whole
+    // stream and add only into the slots they owned: 256 x the reads).  Two lanes meet in one slot only when a target
+    // lists a club twice; the lowest of them then adds the value once per occurrence.
+    if (tid < 32) {
+        const int lane = tid;
+        for (int e = eb; e < ee; ++e) {
+            const ClubEdge ed = P.edges[e];
+            const double w = (double)P.fas[ed.w_idx];
+            double v = w;
+            if (ed.s_idx >= 0) v = __dmul_rn(w, (double)P.fas[ed.s_idx]);   // contrib = wuf * s_f_fof (:58)
+            const uint32_t c0 = P.con_off[e];
+            const uint32_t c1 = (e + 1 < ee) ? P.con_off[e + 1] : 0xffffffffu;
+            const uint32_t* tr = reinterpret_cast<const uint32_t*>(P.rec + P.rec_off[ed.target_row]);
+            const uint32_t ncl = (c1 != 0xffffffffu) ? (c1 - c0) : tr[8];
+            for (uint32_t j0 = 0; j0 < ncl; j0 += 32) {
+                const uint32_t j = j0 + lane;
+                const int32_t sl = (j < ncl) ? cslot[c0 + j] : -1;
+                const uint32_t live = __ballot_sync(0xffffffffu, sl >= 0);
+                const uint32_t same = __match_any_sync(0xffffffffu, sl >= 0 ? sl : -1 - lane) & live;
+                if (sl >= 0 && (__ffs(same) - 1) == lane) {
+                    double a = acc[sl];
+                    for (int r = __popc(same); r > 0; --r) a = __dadd_rn(a, v);
+                    acc[sl] = a;
+                }
+                __syncwarp();
+            }
         }
     }
     __syncthreads();
 
-    // phase C: sort keys (score desc, club id asc; :67-70)
-    for (uint32_t i = tid; i < cap; i += kClubThreads) {
-        const unsigned long long c1 = keys[i];
-        if (c1 != 0ull) keys[i] = make_key(__float_as_uint((float)acc[i]), (int32_t)(uint32_t)(c1 - 1ull));
+    // phase C: sort keys (score desc, club id asc; :67-70), compacted to the front of the user's slice
+    __shared__ int n_keys;
+    if (tid == 0) n_keys = 0;
+    __syncthreads();
+    for (uint32_t i0 = 0; i0 < cap; i0 += kClubThreads) {
+        const uint32_t i = i0 + tid;
+        const unsigned long long c1 = (i < cap) ? keys[i] : 0ull;
+        const bool has = c1 != 0ull;
+        const uint32_t m = __ballot_sync(0xffffffffu, has);
+        int base = 0;
+        if ((tid & 31) == 0 && m) base = atomicAdd(&n_keys, __popc(m));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (has) P.out_keys[sb + base + __popc(m & ((1u << (tid & 31)) - 1u))] =
+            make_key(__float_as_uint((float)acc[i]), (int32_t)(uint32_t)(c1 - 1ull));
     }
+    __syncthreads();
+    if (tid == 0) P.out_cnt[u] = n_keys;
 }
 
 }  // namespace pk

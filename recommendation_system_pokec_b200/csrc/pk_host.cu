@@ -755,7 +755,7 @@ ScanParams base_scan_params(pk_store* s, int K) {
 uint32_t lean_fixed_smem(int Ks) {
     const uint32_t norm = (uint32_t)((sizeof(LeanNorm) + 15) & ~15u);
     // lists, tau, locks, theta, level-1 tables {l1q 32 x 16, l1f 32 x 32, l1b 32 x 4}, next / pick, per-warp hit staging
-    return norm + 32u * Ks * 8u + 32u * 8u + 32u * 4u + 32u * 4u + (512u + 1024u + 128u) + 16u + (uint32_t)kPreWarps * 32u * 16u;
+    return norm + 32u * Ks * 8u + 32u * 8u + 32u * 4u + 32u * 4u + (512u + 1024u + 128u + 896u) + 16u + (uint32_t)kPreWarps * 32u * 16u;
 }
 
 void finish_group(pk_store* s, Plan& plan, GroupDesc& g, const uint32_t* excl_n, int Kp, bool with_lean = false, int Ks = 0) {
@@ -788,10 +788,11 @@ int launch_merge(pk_store* s, MergeParams M, int n_queries) {
 }
 
 // top-k of a flat key slice per user (collaborative / clubs / wide graph epilogue): keys[begin[u] .. begin[u+1])
-int launch_slice_topk(pk_store* s, const uint64_t* keys, const int32_t* begin, int nu, int K, uint64_t* out_keys) {
+int launch_slice_topk(pk_store* s, const uint64_t* keys, const int32_t* begin, int nu, int K, uint64_t* out_keys,
+                      const int32_t* cnt = nullptr) {
     MergeParams M;
     memset(&M, 0, sizeof(M));
-    M.keys = keys; M.seg_begin = begin; M.nq = nu; M.K = K; M.out_keys = out_keys;
+    M.keys = keys; M.seg_begin = begin; M.seg_cnt = cnt; M.nq = nu; M.K = K; M.out_keys = out_keys;
     return launch_merge(s, M, nu);
 }
 
@@ -1000,7 +1001,7 @@ int fullscan_prepare(pk_store* s, int nq, const int32_t* q_uid, int k, int exclu
         TRY(upload(s, J.dyn_groups, dyn_groups));
         TRY(J.dyn_state.reserve(std::max<size_t>(2 * dyn_groups.size(), 1)));      // cursor, instances per group
         if (dyn_groups.size() * 32 > pk_store::kThetaCap) return fail(PK_ERR_UNSUPPORTED, "more than 8192 query groups in one full-scan batch (split the batch)");
-        TRY(s->d_theta_x.reserve(pk_store::kThetaCap));
+        TRY(s->d_theta_x.reserve(2 * pk_store::kThetaCap));
         // exact re-score items: the 32 x Ks shortlist rows of each group, in list mode
         int rr_splits = 4;      // measured: 8 splits (6.92 waves) cost 4.7 ms against 3.9 ms (table staging per CTA)
         if (const char* e = getenv("POKEC_B200_RR_SPLITS")) rr_splits = std::max(1, atoi(e));
@@ -1117,6 +1118,10 @@ PreParams job_pre_params(pk_store* s) {
     Q.n_peers = s->n_peers;
     for (int r = 0; r < 7; ++r) Q.peer_theta[r] = s->peer_theta[r];
     Q.theta_tag = (J.plan_fp ^ (s->exec_counter * 0x9E3779B1u)) | 1u;
+    // the second half of the allocation: the rank-k_frac scores (PreParams::dyn_sfrac)
+    Q.dyn_sfrac = s->d_theta_x.p + pk_store::kThetaCap;
+    for (int r = 0; r < 7; ++r) Q.peer_sfrac[r] = s->peer_theta[r] ? s->peer_theta[r] + pk_store::kThetaCap : nullptr;
+    Q.k_frac = (J.K + s->n_peers) / (s->n_peers + 1);
     Q.K = J.K;
     Q.theta_drop = (getenv("POKEC_B200_NO_PRUNE") && getenv("POKEC_B200_NO_PRUNE")[0] == '1') ? 1e9f : 2.0f * s->margin + 1e-5f;
     Q.cand_begin = (int)J.cand_begin; Q.cand_end = (int)J.cand_end;
@@ -1155,6 +1160,7 @@ int fullscan_begin(pk_store* s) {
     // cursors, instance counters and thresholds start at 0; a new execution, a new threshold tag
     CK(cudaMemsetAsync(J.dyn_state.p, 0, std::max<size_t>(2 * (size_t)J.n_dyn, 1) * 4, s->stream));
     CK(cudaMemsetAsync(s->d_theta_x.p, 0, std::max<size_t>((size_t)J.n_dyn * 32, 1) * 8, s->stream));
+    CK(cudaMemsetAsync(s->d_theta_x.p + pk_store::kThetaCap, 0, std::max<size_t>((size_t)J.n_dyn * 32, 1) * 8, s->stream));
     ++s->exec_counter;
     CK(cudaEventRecord(s->pev[1], s->stream));
     CK(cudaEventRecord(s->ev0, s->stream));
@@ -1693,10 +1699,12 @@ int recommend_clubs_device(pk_store* s, int nq, const int32_t* q_uid, int k, uin
         P.rec = s->d_rec.p; P.rec_off = s->d_rec_off.p; P.fas = cached ? s->d_edge_fas.p : s->d_f32a.p; P.edges = s->d_edges.p;
         P.con_off = s->d_u32a.p; P.user_edge_begin = s->g_edge_off.p; P.user_slot_begin = s->g_slot_begin.p;
         P.user_row = s->g_qrow.p; P.con_slot = s->d_i32d.p; P.slot_key = s->d_keys_a.p; P.slot_acc = s->d_f64a.p;
+        TRY(s->d_keys_c.reserve((size_t)n_slots)); TRY(s->g_ntwo.reserve((size_t)m));
+        P.out_keys = s->d_keys_c.p; P.out_cnt = s->g_ntwo.p;        // (n_two is not read after the FILL pass)
         clubs_scatter_kernel<<<m, kClubThreads, 0, s->stream>>>(P);
         ++s->stat_launches;
         CK(cudaGetLastError());
-        TRY(launch_slice_topk(s, s->d_keys_a.p, s->g_slot_begin.p, m, K, s->d_keys_b.p));
+        TRY(launch_slice_topk(s, s->d_keys_c.p, s->g_slot_begin.p, m, K, s->d_keys_b.p, s->g_ntwo.p));
         CK(cudaMemcpyAsync(keys.data() + (size_t)q0 * K, s->d_keys_b.p, (size_t)m * K * 8, cudaMemcpyDeviceToHost, s->stream));
         CK(cudaStreamSynchronize(s->stream));
         TRY(collect_scan_time(s));
@@ -1996,10 +2004,12 @@ int recommend_clubs_cached(pk_store* s, int nq, const int32_t* q_uid, int k, uin
             C.rec = s->d_rec.p; C.rec_off = s->d_rec_off.p; C.fas = s->d_edge_fas.p; C.edges = s->d_edges.p;
             C.con_off = s->d_u32a.p; C.user_edge_begin = s->d_i32a.p; C.user_slot_begin = s->d_i32b.p;
             C.user_row = s->d_i32c.p; C.con_slot = s->d_i32d.p; C.slot_key = s->d_keys_a.p; C.slot_acc = s->d_f64a.p;
+            TRY(s->d_keys_c.reserve((size_t)total_slots)); TRY(s->d_i32e.reserve((size_t)nu));
+            C.out_keys = s->d_keys_c.p; C.out_cnt = s->d_i32e.p;
             clubs_scatter_kernel<<<nu, kClubThreads, 0, s->stream>>>(C);
             ++s->stat_launches;
             CK(cudaGetLastError());
-            TRY(launch_slice_topk(s, s->d_keys_a.p, s->d_i32b.p, nu, K, s->d_keys_b.p));
+            TRY(launch_slice_topk(s, s->d_keys_c.p, s->d_i32b.p, nu, K, s->d_keys_b.p, s->d_i32e.p));
             std::vector<uint64_t> uk((size_t)nu * K);
             CK(cudaMemcpyAsync(uk.data(), s->d_keys_b.p, uk.size() * 8, cudaMemcpyDeviceToHost, s->stream));
             CK(cudaStreamSynchronize(s->stream));
@@ -2116,10 +2126,12 @@ int recommend_clubs(pk_store* s, int nq, const int32_t* q_uid, int k, uint64_t* 
             C.rec = s->d_rec.p; C.rec_off = s->d_rec_off.p; C.fas = s->d_f32a.p; C.edges = s->d_edges.p;
             C.con_off = s->d_u32a.p; C.user_edge_begin = s->d_i32a.p; C.user_slot_begin = s->d_i32b.p;
             C.user_row = s->d_i32c.p; C.con_slot = s->d_i32d.p; C.slot_key = s->d_keys_a.p; C.slot_acc = s->d_f64a.p;
+            TRY(s->d_keys_c.reserve((size_t)total_slots)); TRY(s->d_i32e.reserve((size_t)nu));
+            C.out_keys = s->d_keys_c.p; C.out_cnt = s->d_i32e.p;
             clubs_scatter_kernel<<<nu, kClubThreads, 0, s->stream>>>(C);
             ++s->stat_launches;
             CK(cudaGetLastError());
-            TRY(launch_slice_topk(s, s->d_keys_a.p, s->d_i32b.p, nu, K, s->d_keys_b.p));
+            TRY(launch_slice_topk(s, s->d_keys_c.p, s->d_i32b.p, nu, K, s->d_keys_b.p, s->d_i32e.p));
             std::vector<uint64_t> uk((size_t)nu * K);
             CK(cudaMemcpyAsync(uk.data(), s->d_keys_b.p, uk.size() * 8, cudaMemcpyDeviceToHost, s->stream));
             CK(cudaStreamSynchronize(s->stream));
@@ -2652,7 +2664,7 @@ int pk_fullscan_execute_shortlists(pk_store* s) {
 int pk_fullscan_theta_export(pk_store* s, void* handle64) {
     if (!s || !handle64) return fail(PK_ERR_ARG, "null argument");
     CK(cudaSetDevice(s->device));
-    TRY(s->d_theta_x.reserve(pk_store::kThetaCap));
+    TRY(s->d_theta_x.reserve(2 * pk_store::kThetaCap));
     cudaIpcMemHandle_t h;
     static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
     CK(cudaIpcGetMemHandle(&h, s->d_theta_x.p));
@@ -2663,7 +2675,7 @@ int pk_fullscan_theta_export(pk_store* s, void* handle64) {
 void* pk_fullscan_theta_ptr(pk_store* s) {
     if (!s) return nullptr;
     cudaSetDevice(s->device);
-    if (s->d_theta_x.reserve(pk_store::kThetaCap) != PK_OK) return nullptr;
+    if (s->d_theta_x.reserve(2 * pk_store::kThetaCap) != PK_OK) return nullptr;
     return s->d_theta_x.p;
 }
 

@@ -106,6 +106,14 @@ struct PreParams {
     const unsigned long long* peer_theta[7];
     int n_peers;
     unsigned int theta_tag;
+    // The k-th best of ONE shard says little about the k-th best of all shards (of the global top-50 a shard of eight
+    // holds ~6).  So every rank also publishes, per query, the score at its local rank k_frac = ceil(k / ranks)
+    // (dyn_sfrac, same tagging; the peers' arrays sit at the same offset of their mapped allocations): the ranks
+    // together hold at least ranks * k_frac >= k candidates scoring at least the MINIMUM of those values, which
+    // therefore bounds the merged k-th best from below -- a far tighter threshold than any single rank's own k-th best.
+    unsigned long long* dyn_sfrac;
+    const unsigned long long* peer_sfrac[7];
+    int k_frac;
     int K;                       // the caller's k (theta watches list position K - 1)
     float theta_drop;            // 2 margin + slack
     int cand_begin, cand_end;    // the shard's row range
@@ -172,7 +180,8 @@ __device__ __forceinline__ void l1_update_warp(float th, const float* frow, floa
 // arguments; keys are unique -- one per candidate row).
 __device__ __forceinline__ void shortlist_insert(uint64_t* list, int K, uint64_t key, int* lock, volatile uint64_t* tau,
                                                  int lane, int k_user, float theta_drop, volatile float* theta,
-                                                 unsigned long long* g_theta, unsigned int tag, const float* frow, float ub_text, float inv_total,
+                                                 unsigned long long* g_theta, unsigned int tag, unsigned long long* g_sfrac, int k_frac,
+                                                 const float* frow, float ub_text, float inv_total,
                                                  volatile uint4* q4, volatile float* bnd) {
     if (lane == 0) {
         while (atomicCAS(lock, 0, 1) != 0) __nanosleep(32);
@@ -196,6 +205,10 @@ __device__ __forceinline__ void shortlist_insert(uint64_t* list, int K, uint64_t
         if (lane == 0) {
             vl[pos] = key;
             *tau = vl[K - 1];
+            if (g_sfrac) {                           // sharded scan: the score at local rank k_frac, for the other ranks
+                const uint64_t kf = vl[k_frac - 1];
+                if (kf != 0ull && pos < k_frac) atomicMax(g_sfrac, ((unsigned long long)tag << 32) | key_score_bits(kf));
+            }
             const uint64_t kk = vl[k_user - 1];
             if (kk != 0ull && pos < k_user) {      // the k-th best moved: raise this query's pruning threshold
                 const float th = fmaxf(__uint_as_float(key_score_bits(kk)) - theta_drop, 0.f);
@@ -251,7 +264,8 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
     uint4* l1q = reinterpret_cast<uint4*>(theta + 32);                              // [32] {query mask lo, hi, jmin, -}
     float* l1f = reinterpret_cast<float*>(l1q + 32);                                // [32][8] {n, largest sigmas descending}
     float* l1b = l1f + 32 * 8;                                                      // [32] theta up to which l1q[].z/w hold
-    int* next = reinterpret_cast<int*>(l1b + 32);
+    float* pcache = l1b + 32;                                                       // [7][32] the peers' rank-k_frac scores, as last polled
+    int* next = reinterpret_cast<int*>(pcache + 7 * 32);
     uint4* stage = reinterpret_cast<uint4*>(next + 4) + warp * 32;                  // per-warp hit staging
     int* pick = next + 1;                                                           // {group index, instance}
 
@@ -313,6 +327,7 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
         for (uint32_t i = tid; i < kNormBytes / 16; i += kPreThreads) ndst[i] = __ldg(nsrc + i);
         for (int i = tid; i < 32 * Ks; i += kPreThreads) lists[i] = 0ull;
         if (tid < 32) { tau[tid] = 0ull; locks[tid] = 0; theta[tid] = 0.f; }
+        if (tid < 7 * 32) pcache[tid] = 0.f;
         if (tid == 0) *next = it.cand_begin;
     }
     __syncthreads();
@@ -366,6 +381,7 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
     }
     __syncthreads();
     unsigned long long* const g_theta = STORE ? nullptr : P.dyn_theta + (size_t)pick[0] * 32 + lane;
+    unsigned long long* const g_sfrac = (STORE || P.n_peers == 0) ? nullptr : P.dyn_sfrac + (size_t)pick[0] * 32 + lane;
     int peer_rr = 0;                // next peer to poll (warp 0)
     float th_g = 0.f;               // the group's published threshold, re-read once per chunk
 
@@ -404,11 +420,20 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
         if (!STORE) {
             // thresholds published by the other instances of the group
             if (warp == 0 && P.n_peers > 0) {
-                // one peer per chunk, round robin: its threshold for MY query, accepted only under the same tag
-                const unsigned long long pv = *reinterpret_cast<const volatile unsigned long long*>(
-                    P.peer_theta[peer_rr] + (size_t)pick[0] * 32 + lane);
-                peer_rr = (peer_rr + 1 == P.n_peers) ? 0 : peer_rr + 1;
+                // one peer per chunk, round robin: its threshold and its rank-k_frac score for MY query, accepted only
+                // under the same tag
+                const size_t at = (size_t)pick[0] * 32 + lane;
+                const unsigned long long pv = *reinterpret_cast<const volatile unsigned long long*>(P.peer_theta[peer_rr] + at);
+                const unsigned long long ps = *reinterpret_cast<const volatile unsigned long long*>(P.peer_sfrac[peer_rr] + at);
                 if ((unsigned int)(pv >> 32) == P.theta_tag) atomicMax(g_theta, pv);
+                if ((unsigned int)(ps >> 32) == P.theta_tag) pcache[peer_rr * 32 + lane] = __uint_as_float((unsigned int)ps);
+                peer_rr = (peer_rr + 1 == P.n_peers) ? 0 : peer_rr + 1;
+                // the merged k-th best is at least the smallest rank-k_frac score over ALL ranks (0 = not known yet)
+                const unsigned long long os = *reinterpret_cast<volatile unsigned long long*>(g_sfrac);
+                float lo = ((unsigned int)(os >> 32) == P.theta_tag) ? __uint_as_float((unsigned int)os) : 0.f;
+                for (int r = 0; r < P.n_peers; ++r) lo = fminf(lo, pcache[r * 32 + lane]);
+                const float th2 = lo - P.theta_drop;
+                if (th2 > 0.f) atomicMax(g_theta, ((unsigned long long)P.theta_tag << 32) | __float_as_uint(th2));
             }
             {
                 const unsigned long long gv = *reinterpret_cast<volatile unsigned long long*>(g_theta);
@@ -615,6 +640,7 @@ __global__ void __launch_bounds__(kPreThreads, 1) fas_prefilter_kernel(const Pre
                         const uint64_t kj = __shfl_sync(kFull, key, j);
                         shortlist_insert(lists + j * Ks, Ks, kj, locks + j, reinterpret_cast<volatile uint64_t*>(tau) + j, lane, P.K,
                                          P.theta_drop, reinterpret_cast<volatile float*>(theta) + j, g_theta - lane + j, P.theta_tag,
+                                         g_sfrac ? g_sfrac - lane + j : nullptr, P.k_frac,
                                          l1f + j * 8, ub_text, inv_total, reinterpret_cast<volatile uint4*>(l1q) + j,
                                          reinterpret_cast<volatile float*>(l1b) + j);
                     }

@@ -610,6 +610,7 @@ struct MergeParams {
     const int32_t* n_lists_q;   // mode A: number of lists of each query
     const int32_t* lane;        // mode A
     const int32_t* seg_begin;   // mode C
+    const int32_t* seg_cnt;     // mode C: length of each segment (null = up to the next segment's begin)
     int n_lists;                // mode B
     int nq, K, stride_k;
     int cap;                    // sort buffer capacity in keys (power of two, >= 2 K and >= kMergeThreads)
@@ -654,7 +655,7 @@ __global__ void __launch_bounds__(kMergeThreads) merge_topk_kernel(const MergePa
     if (modeC) {
         const int b = P.seg_begin[q];
         seg = P.keys + b;
-        total = P.seg_begin[q + 1] - b;
+        total = P.seg_cnt ? P.seg_cnt[q] : P.seg_begin[q + 1] - b;
     } else if (modeA) {
         const int nl = alt ? P.alt_n_lists_q[q] : P.n_lists_q[q];
         list0 = ((size_t)(alt ? P.alt_slot0 : P.slot0)[q] * 32 + P.lane[q]) * stride;
