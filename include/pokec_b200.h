@@ -62,6 +62,14 @@ int pk_store_load_world(pk_store* s, const pk_world* w);
  * user-id range across the GPUs of one box.) */
 int pk_store_set_shard(pk_store* s, int64_t row_begin, int64_t row_end);
 
+/* Tuning knobs of a store.
+ *   PK_OPT_PREFILTER_RESERVE_SMS  the persistent pre-filter of the full scan normally takes every SM for the length of the
+ *                                 scan; a caller that keeps two batches in flight on two stores / streams can ask it to
+ *                                 leave `value` SMs free, so that the previous batch's merges, re-score and NCCL
+ *                                 all-gathers overlap the scan instead of queueing behind it (0 = default). */
+enum { PK_OPT_PREFILTER_RESERVE_SMS = 1 };
+int pk_store_set_option(pk_store* s, int which, int64_t value);
+
 /* Replaces set_field_normalizers + set_column_normalizers (src/recommender.cpp:27-33): `n_fields`
  * = 7 + T entries, the 7 fixed keys (public, gender, completion, age, region, clubs, friends)
  * followed by the text columns.  has[i]==0 means "no entry in the map" (z = 6(s-0.5),

@@ -260,6 +260,7 @@ struct pk_store {
     void* peer_mapped[7] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // cudaIpcOpenMemHandle results
     int n_peers = 0;
     uint32_t exec_counter = 0;
+    int reserve_sms = 0;              // SMs the persistent pre-filter leaves free (pk_store_set_option)
     DevBuf<int32_t> d_seed_rows;
     DevBuf<uint8_t> d_seed_skip;
     std::vector<int32_t> seed_cache;          // seed rows of the shard [seed_b, seed_e) with divisor seed_div
@@ -1189,7 +1190,9 @@ int fullscan_shortlists(pk_store* s) {
     PreParams Q = job_pre_params(s);
     // shortlist instances a CTA never takes stay empty; cursors and instance counters restart at 0
     CK(cudaMemsetAsync(J.keys_pre.p, 0, std::max<size_t>(J.n_pre, 1) * 32 * (size_t)Ks * 8, s->stream));
-    const size_t pre_grid = std::min<size_t>((size_t)J.sm_count, J.n_pre);     // one persistent CTA per SM
+    // one persistent CTA per SM -- minus the SMs a pipelining caller asked to keep free, so that the short kernels and
+    // the NCCL all-gathers of the PREVIOUS batch (other stream) find room while this scan runs
+    const size_t pre_grid = std::min<size_t>((size_t)std::max(J.sm_count - s->reserve_sms, 1), J.n_pre);
     TRY(launch_prefilter(s, Q, pre_grid, J.max_smem_lean, Ks, false));
     CK(cudaEventRecord(s->ev1, s->stream));
     if (J.n_pre) { s->scan_time_pending = true; ++s->stat_scan_launches; }
@@ -2387,6 +2390,17 @@ int pk_store_load_world(pk_store* s, const pk_world* w) {
     s->seed_b = s->seed_e = -1;
     s->loaded = true;
     return PK_OK;
+}
+
+int pk_store_set_option(pk_store* s, int which, int64_t value) {
+    if (!s) return fail(PK_ERR_ARG, "null store");
+    switch (which) {
+        case PK_OPT_PREFILTER_RESERVE_SMS:
+            if (value < 0 || value > 64) return fail(PK_ERR_ARG, "reserve_sms out of range");
+            s->reserve_sms = (int)value;
+            return PK_OK;
+        default: return fail(PK_ERR_ARG, "unknown option %d", which);
+    }
 }
 
 int pk_store_set_shard(pk_store* s, int64_t row_begin, int64_t row_end) {

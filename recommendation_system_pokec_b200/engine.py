@@ -26,11 +26,13 @@ ABI_SYMBOLS = (
     "pk_idf_size", "pk_get_idf", "pk_set_adj_row", "pk_pair_similarity", "pk_pair_fields", "pk_pair_overlap",
     "pk_fullscan_topk", "pk_fullscan_prepare", "pk_fullscan_execute", "pk_fullscan_fetch", "pk_fullscan_keys", "pk_recommend", "pk_candidates", "pk_fullscan_local_keys", "pk_merge_keys", "pk_sync",
     "pk_normalizers_from_pairs", "pk_edge_cache_build", "pk_edge_cache_drop", "pk_edge_cache_row", "pk_fullscan_execute_shortlists", "pk_fullscan_shortlist_keys", "pk_fullscan_execute_finish",
-    "pk_stream", "pk_stat", "pk_debug_prefilter", "pk_world_save", "pk_world_open", "pk_world_close", "pk_candidates_batch", "pk_fullscan_theta_export", "pk_fullscan_theta_ptr", "pk_fullscan_theta_peers",
+    "pk_stream", "pk_stat", "pk_debug_prefilter", "pk_world_save", "pk_world_open", "pk_world_close", "pk_candidates_batch", "pk_store_set_option", "pk_fullscan_theta_export", "pk_fullscan_theta_ptr", "pk_fullscan_theta_peers",
 )
 STAT_KERNEL_LAUNCHES, STAT_PAIRS_SCORED, STAT_STORE_BYTES, STAT_SCAN_KERNEL_NS, STAT_SCAN_LAUNCHES, STAT_GROUPS, \
     STAT_SHARD_RECORD_BYTES, STAT_H2D_BYTES, STAT_D2H_BYTES, STAT_PREFILTER, STAT_FALLBACK_QUERIES, STAT_RESCORE_NS, \
     STAT_SHARD_LEAN_BYTES, STAT_SHORTLIST, STAT_MARGIN_E9, STAT_EDGE_CACHE, STAT_PREP_NS, STAT_MERGE_NS = range(18)
+
+OPT_PREFILTER_RESERVE_SMS = 1
 
 _lib = None
 
@@ -211,6 +213,9 @@ class DeviceRecommender:
     def set_adj_row(self, uid, nb):
         nb = np.ascontiguousarray(nb, np.int32)
         _check(self.lib, self.lib.pk_set_adj_row(self.h, int(uid), ptr(nb, i32p), C.c_int64(len(nb))))
+
+    def set_option(self, which, value):
+        _check(self.lib, self.lib.pk_store_set_option(self.h, int(which), C.c_int64(int(value))))
 
     def set_shard(self, row_begin, row_end):
         _check(self.lib, self.lib.pk_store_set_shard(self.h, C.c_int64(row_begin), C.c_int64(row_end)))

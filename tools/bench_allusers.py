@@ -28,7 +28,7 @@ from recommendation_system_pokec_b200.cabi import EXCLUDE_SELF_AND_ADJ  # noqa: 
 from recommendation_system_pokec_b200.sharding import shard_rows, share_thetas  # noqa: E402
 
 
-def sweep(w, ws, rank, lr, B, k, n_batches, depth=2, keep_batches=(), batch_fn=None, stats=None):
+def sweep(w, ws, rank, lr, B, k, n_batches, depth=2, keep_batches=(), batch_fn=None, stats=None, reserve_sms=None):
     """`n_batches` consecutive batches of B distinct query users (walked in uid order) through the end-to-end calls --
     host uids in, host top-k out, host planning + H2D, both all-gathers and the merge every batch.  `depth` stores on the
     same GPU take the batches in turn, each on its own stream: the host planning and H2D of batch i + 1 overlap the
@@ -41,6 +41,8 @@ def sweep(w, ws, rank, lr, B, k, n_batches, depth=2, keep_batches=(), batch_fn=N
     from recommendation_system_pokec_b200 import engine
     from recommendation_system_pokec_b200.engine import DeviceRecommender
     lo, hi = shard_rows(w.n, rank, ws)
+    if reserve_sms is None:        # on small shards the tail of a batch (merges, re-score, all-gathers) is worth overlapping
+        reserve_sms = int(os.environ.get("POKEC_B200_RESERVE_SMS", "4" if ws >= 4 and depth > 1 else "0"))
 
     def batch_uids(b):
         if batch_fn is not None:
@@ -54,6 +56,8 @@ def sweep(w, ws, rank, lr, B, k, n_batches, depth=2, keep_batches=(), batch_fn=N
         def __init__(self):
             self.dev = DeviceRecommender(w, device=lr)
             self.dev.set_shard(lo, hi)
+            if reserve_sms > 0:
+                self.dev.set_option(engine.OPT_PREFILTER_RESERVE_SMS, reserve_sms)
             share_thetas(self.dev, rank, ws, f"cuda:{lr}")      # slot i of every rank pairs with slot i of the others
             self.stream = torch.cuda.ExternalStream(self.dev.stream(), device=lr)
             self.local = torch.zeros((B, k), dtype=torch.int64, device=f"cuda:{lr}")
