@@ -6,7 +6,8 @@ test can put the CUDA-backed `Recommender` and the reference's CPU `Recommender`
 through the reference's own C++ API.
 
 Needs the reference headers, so it only builds where /root/reference exists (this container); the .so is
-git-ignored and travels to the GPU box with the gpurun snapshot.  No reference SOURCE file is compiled in.
+git-ignored and travels to the GPU box with the gpurun snapshot.  No reference source of the REPLACED path is compiled
+in; src/test.cpp (the hold-out harness, a caller of recommend_collaborative) is, unmodified, from where it lies.
 """
 import os
 import subprocess
@@ -26,7 +27,8 @@ def build(force=False):
     from recommendation_system_pokec_b200.build import build as build_cuda
     build_cuda()
     srcs = [os.path.join(HERE, "recommender_b200.cpp"), os.path.join(HERE, "tfidf_index_b200.cpp"),
-            os.path.join(ROOT, "oracle", "ref_driver.cpp")]
+            os.path.join(ROOT, "oracle", "ref_driver.cpp"),
+            os.path.join(REF, "src", "test.cpp")]      # the reference's hold-out harness: caller code, compiled where it lies
     deps = srcs + [os.path.join(ROOT, "include", "pokec_b200.h"), os.path.join(ROOT, "include", "pokec_world.h"),
                    os.path.join(HERE, "recommender_b200_batch.h")]
     if not force and os.path.exists(OUT) and all(os.path.getmtime(d) <= os.path.getmtime(OUT) for d in deps):

@@ -17,7 +17,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 REF = os.environ.get("POKEC_REFERENCE_DIR", "/root/reference")
 REF_SOURCES = ["recommender.cpp", "recommender_similarity.cpp", "recommender_graph.cpp",
-               "recommender_clubs.cpp", "tfidf_index.cpp", "utils.cpp"]
+               "recommender_clubs.cpp", "tfidf_index.cpp", "utils.cpp",
+               "test.cpp"]      # test.cpp = the hold-out harness, a CALLER of the path (ref_holdout_test)
 
 
 def _newer(target, deps):

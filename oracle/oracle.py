@@ -190,6 +190,14 @@ class CpuOracle:
                                               C.c_longlong(cap)))
         return a[:n].copy(), b[:n].copy()
 
+    def holdout_test(self, sample_size, out_path):
+        """the reference's friends hold-out harness (src/test.cpp:13-105), unmodified, on this handle's Recommender (the
+        compiled reference, or the CUDA-backed drop-in); returns the ratios it wrote, one per tested user"""
+        assert self.kind == "reference"
+        self.lib.ref_holdout_test(self.h, int(sample_size), str(out_path).encode())
+        with open(out_path) as f:
+            return [line.strip() for line in f if line.strip()]
+
     def set_adj_row(self, uid, nb):
         assert self.kind == "reference"
         nb = np.ascontiguousarray(nb, np.int32)

@@ -12,6 +12,7 @@
 #include "utils.h"
 #endif
 #include "tfidf_index.h"
+#include "test.h"             // reference header: run_friends_holdout_test (src/test.cpp:13-105)
 
 #include "pokec_world.h"
 
@@ -399,6 +400,16 @@ int ref_world_file_round_trip(void* hv, const char* path) {
     return 0;
 }
 #endif
+
+// The reference's only live "test" (src/main.cpp:147 -> src/test.cpp:13-105), UNMODIFIED and compiled where it lies:
+// it builds its own Recommender over a copy of the adjacency, removes a fifth of a user's friends behind it, asks
+// recommend_collaborative(uid, hold_k, 1000) and writes one hit ratio per tested user to out_path.  In the drop-in
+// library the same caller code runs against the CUDA-backed Recommender.
+int ref_holdout_test(void* hv, int sample_size, const char* out_path) {
+    auto* h = (RefHandle*)hv;
+    run_friends_holdout_test(h->profiles, h->adj, h->cols, *h->rec, sample_size, out_path);
+    return 0;
+}
 
 // mutate one adjacency row behind the live Recommender (what src/test.cpp:59-73 does)
 int ref_set_adj_row(void* hv, int uid, int n, const int32_t* nb) {

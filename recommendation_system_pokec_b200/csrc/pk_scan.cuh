@@ -374,16 +374,45 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
     const int total_possible = N->total_possible;
     (void)total_possible;
 
-    // ---- candidate loop: warps grab small chunks of the item's candidate slice -----------------
-    constexpr int kChunk = 4;
-    for (;;) {
-        int c0 = 0;
-        if (lane == 0) c0 = atomicAdd(next, kChunk);
-        c0 = __shfl_sync(kFull, c0, 0);
-        if (c0 >= it.cand_end) break;
-        const int c1 = min(c0 + kChunk, it.cand_end);
-        for (int ci = c0; ci < c1; ++ci) {
-            const int64_t crow = P.cand_rows ? (int64_t)P.cand_rows[ci] : (int64_t)ci;
+    // ---- candidate loop -------------------------------------------------------------------------
+    // A warp claims one candidate at a time from the item's cursor and keeps two claims ahead of the one it is
+    // scoring: the record offset of claim + 2 is being loaded while the whole record of claim + 1 (header, id lists,
+    // cells, token keys, weights: ~1.1 KB of a randomly placed row in the list modes) is prefetched, one 128-byte
+    // line per lane.  Without it a candidate costs a chain of dependent DRAM round trips (row -> offset -> header ->
+    // keys -> weights) that the 16 warps of the CTA cannot hide: the kernel ran at ~17 % of its issue slots.
+    auto claim = [&]() {
+        int c = 0;
+        if (lane == 0) c = atomicAdd(next, 1);
+        return __shfl_sync(kFull, c, 0);
+    };
+    auto row_of = [&](int ci) -> int64_t {
+        if (ci >= it.cand_end) return -1;
+        return P.cand_rows ? (int64_t)__ldg(P.cand_rows + ci) : (int64_t)ci;
+    };
+    int c_cur = claim(), c_n1 = claim(), c_n2 = claim();
+    int64_t r_cur = row_of(c_cur), r_n1 = row_of(c_n1), r_n2 = row_of(c_n2);
+    uint64_t o_n1 = 0, e_n1 = 0, o_n2 = 0, e_n2 = 0;
+    if (r_n1 >= 0) { o_n1 = __ldg(P.rec_off + r_n1); e_n1 = __ldg(P.rec_off + r_n1 + 1); }
+    if (r_n2 >= 0) { o_n2 = __ldg(P.rec_off + r_n2); e_n2 = __ldg(P.rec_off + r_n2 + 1); }
+    for (; c_cur < it.cand_end; ) {
+#ifndef PK_SCAN_NO_PREFETCH
+        if (r_n1 >= 0 && o_n1 + 8ull * lane < e_n1) {
+            const uint4* pf = P.rec + o_n1 + 8ull * lane;
+#ifdef PK_SCAN_PREFETCH_L1
+            asm volatile("prefetch.global.L1 [%0];" :: "l"(pf));
+#else
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(pf));
+#endif
+        }
+#endif
+        const int ci = c_cur;
+        const int64_t crow = r_cur;
+        // rotate the claims (the loads of claim + 2 stay in flight while this candidate is scored)
+        c_cur = c_n1; r_cur = r_n1;
+        c_n1 = c_n2; r_n1 = r_n2; o_n1 = o_n2; e_n1 = e_n2;
+        c_n2 = claim(); r_n2 = row_of(c_n2);
+        if (r_n2 >= 0) { o_n2 = __ldg(P.rec_off + r_n2); e_n2 = __ldg(P.rec_off + r_n2 + 1); }
+        {
             if (crow < 0) continue;   // empty shortlist slot (warp-uniform)
             const uint4* cr = P.rec + P.rec_off[crow];
             const uint32_t* cw = reinterpret_cast<const uint32_t*>(cr);
@@ -395,6 +424,9 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
             const int c_bcnt = (int)h3.z;
             const uint32_t o_clubs = kHdrWords, o_friends = o_clubs + pad4(c_ncl), o_cells = o_friends + pad4(c_nfr),
                            o_keys = o_cells + 4 * c_ncells, o_w = o_keys + pad4(c_ntok);
+            // the first 32 token keys are wanted after the id lists: issue the load now
+            uint32_t key_first = 0;
+            if ((uint32_t)lane < c_ntok) key_first = __ldg(cw + o_keys + lane);
 
             float* fo = nullptr;
             if (FIELDS) {
@@ -485,49 +517,41 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
             // text columns (:93-114): tf-idf cosine per jointly non-empty column
             const uint64_t joint = q_mask & c_mask;
             if (c_ncells > 0) {
-                const uint4* cells = cr + (o_cells >> 2);
+                // The candidate's token keys ascend over the record (column, then token), so the hits of one column
+                // are consecutive: the loop runs over the HITS only and closes a column's dot product when the next
+                // hit belongs to another column (round 1 walked every cell of the candidate, one dependent load of
+                // the cell header each).  A lane's products are added in ascending token order, as the reference's
+                // map walk adds them (src/recommender.cpp:86-100).
                 const uint32_t* keys = cw + o_keys;
                 const double* tokw = reinterpret_cast<const double*>(cw + o_w);
-                uint32_t cell = 0;
-                uint4 ch = __ldg(cells);
+                int cur_ct = -1;
                 double dot = 0.0;
                 for (uint32_t cb = 0; cb < c_ntok; cb += 32) {
                     const uint32_t i = cb + lane;
-                    uint32_t m = 0, base = 0;
-                    if (i < c_ntok) m = probe_text(t_text, log_st, __ldg(keys + i), &base);
-                    const uint32_t hitb = __ballot_sync(kFull, m != 0u);
+                    uint32_t m = 0, base = 0, key = 0;
+                    if (i < c_ntok) {
+                        key = cb ? __ldg(keys + i) : key_first;
+                        m = probe_text(t_text, log_st, key, &base);
+                    }
+                    uint32_t bits = __ballot_sync(kFull, m != 0u);
                     double wc = 0.0;
                     if (m) wc = __ldg(tokw + i);
-                    const uint32_t chunk_end = min(cb + 32u, c_ntok);
-                    uint32_t pos = cb;
-                    while (pos < chunk_end) {
-                        const uint32_t cend = ch.y;
-                        const uint32_t e = min(cend, chunk_end);
-                        const uint32_t hi = e - cb, lo = pos - cb;
-                        uint32_t bits = hitb & ((hi >= 32u) ? kFull : ((1u << hi) - 1u)) & ~((1u << lo) - 1u);
-                        while (bits) {
-                            const int j = __ffs(bits) - 1;
-                            bits &= bits - 1;
-                            const uint32_t mj = __shfl_sync(kFull, m, j);
-                            const uint32_t bj = __shfl_sync(kFull, base, j);
-                            const double wj = __shfl_sync(kFull, wc, j);
-                            if ((mj >> lane) & 1u) dot = __dadd_rn(dot, __dmul_rn(vals[bj + __popc(mj & lane_lt)], wj));
-                        }
-                        pos = e;
-                        if (pos == cend) {   // cell complete: queue this lane's dot product of column ct
-                            const int ct = (int)(ch.x & 0xffu);
-                            if (dot != 0.0 && ((joint >> ct) & 1ull)) {
-                                qf[qn] = (uint8_t)(kNumFixed + ct);
-                                qv[qn] = dot;
-                                ++qn;
-                                matched |= 1ull << ct;
-                            }
+                    while (bits) {
+                        const int j = __ffs(bits) - 1;
+                        bits &= bits - 1;
+                        const uint32_t mj = __shfl_sync(kFull, m, j);
+                        const uint32_t bj = __shfl_sync(kFull, base, j);
+                        const double wj = __shfl_sync(kFull, wc, j);
+                        const int ct = (int)(__shfl_sync(kFull, key, j) >> kTokBits);
+                        if (ct != cur_ct) {              // warp-uniform: the previous column is complete
+                            if (dot != 0.0) { qf[qn] = (uint8_t)(kNumFixed + cur_ct); qv[qn] = dot; ++qn; matched |= 1ull << cur_ct; }
                             dot = 0.0;
-                            ++cell;
-                            if (cell < c_ncells) ch = __ldg(cells + cell);
+                            cur_ct = ct;
                         }
+                        if ((mj >> lane) & 1u) dot = __dadd_rn(dot, __dmul_rn(vals[bj + __popc(mj & lane_lt)], wj));
                     }
                 }
+                if (dot != 0.0) { qf[qn] = (uint8_t)(kNumFixed + cur_ct); qv[qn] = dot; ++qn; matched |= 1ull << cur_ct; }
                 used += __popcll(joint);
             }
             // evaluation pass: queue entry k of every lane of the warp together

@@ -41,8 +41,11 @@ def sweep(w, ws, rank, lr, B, k, n_batches, depth=2, keep_batches=(), batch_fn=N
     from recommendation_system_pokec_b200 import engine
     from recommendation_system_pokec_b200.engine import DeviceRecommender
     lo, hi = shard_rows(w.n, rank, ws)
-    if reserve_sms is None:        # on small shards the tail of a batch (merges, re-score, all-gathers) is worth overlapping
-        reserve_sms = int(os.environ.get("POKEC_B200_RESERVE_SMS", "4" if ws >= 4 and depth > 1 else "0"))
+    if reserve_sms is None:
+        # SMs the persistent pre-filter leaves to the tail of the previous batch (merges, re-score, all-gathers).  Measured
+        # at 8 GPUs (profiles/r02v_reserve_n8.jsonl: 0 -> 286 / 272 k, 4 -> 280 k, 8 -> 278 k, 16 -> 274 k query-users/s): the
+        # tail needs throughput, not a few SMs, so nothing is gained -- the default stays 0.
+        reserve_sms = int(os.environ.get("POKEC_B200_RESERVE_SMS", "0"))
 
     def batch_uids(b):
         if batch_fn is not None:
@@ -158,6 +161,7 @@ def main():
     ap.add_argument("--batches", type=int, default=16)
     ap.add_argument("--topk", type=int, default=50)
     ap.add_argument("--depth", type=int, default=2, help="batches in flight (stores on the GPU); 1 = no overlap")
+    ap.add_argument("--reserve", default="", help="comma list: time the window once per value of PK_OPT_PREFILTER_RESERVE_SMS")
     args = ap.parse_args()
     fd = os.dup(1)
     os.dup2(2, 1)                      # NCCL prints its banner on stdout
@@ -171,6 +175,17 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
     from bench import build_world          # the bench world (cached on disk between invocations and ranks)
     w = build_world(args.users)
+    if args.reserve:                       # A/B of the SMs the persistent pre-filter leaves to the tail of the previous batch
+        sweep(w, ws, rank, lr, args.batch, args.topk, 4, args.depth)          # warm-up (allocations, NCCL channels)
+        for r in [int(x) for x in args.reserve.split(",")]:
+            rate, dt, _ = sweep(w, ws, rank, lr, args.batch, args.topk, args.batches, args.depth, reserve_sms=r)
+            if rank == 0:
+                os.write(fd, (json.dumps({"n_gpus": ws, "reserve_sms": r, "query_users_per_s": rate,
+                                          "ms_per_batch": dt / args.batches * 1e3}) + "\n").encode())
+        if ws > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
     rate, dt, _ = sweep(w, ws, rank, lr, args.batch, args.topk, args.batches, args.depth)
     if rank == 0:
         out = {"workload": "all-users FAS top-50 (BASELINE configs[4])", "n_gpus": ws, "users": w.n, "batch": args.batch,
