@@ -539,7 +539,7 @@ def main():
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
             tr = json.load(f)
-        if not (two_stage and world_size == 1 and tr.get("users") == args.users and tr.get("queries") == args.queries
+        if not (two_stage and tr.get("users") == args.users and tr.get("queries") == args.queries
                 and tr.get("warp_instructions_per_launch") and tr.get("smem_wavefronts_per_launch")):
             tr = None
     except Exception:
@@ -555,7 +555,16 @@ def main():
                         "algorithmic_frac is the SURVEY 8d figure (queries x canonical record bytes / time / HBM peak; "
                         "cross-query reuse not credited, can exceed 1); dram_frac is the physical DRAM fraction."}
     if tr is not None and scan_s > 0:
-        inst = float(tr["warp_instructions_per_launch"])
+        # N > 1: a rank scans 1/N of the candidates, so its share of the unsharded launch's counters is the ALGORITHMIC
+        # work of its launch; what a small shard executes beyond that (weaker pruning, fixed costs) counts as waste, i.e.
+        # lowers frac rather than raising it
+        inst = float(tr["warp_instructions_per_launch"]) / world_size
+        tr = dict(tr)
+        for key in ("dram_bytes_per_launch", "smem_wavefronts_per_launch", "smem_bank_conflicts_per_launch"):
+            if tr.get(key) is not None:
+                tr[key] = float(tr[key]) / world_size
+        if world_size > 1:
+            tr["source"] = f"1/{world_size} of: " + str(tr.get("source"))
         issue_peak = SM_COUNT * 4 * clk_hz
         roofline.update({"bound": "issue", "achieved": inst / scan_s / 1e9, "peak": issue_peak / 1e9, "unit": "G warp-instr/s",
                          "frac": inst / scan_s / issue_peak, "issue_frac": inst / scan_s / issue_peak,

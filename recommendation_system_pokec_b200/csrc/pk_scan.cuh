@@ -18,7 +18,10 @@
 
 namespace pk {
 
-constexpr int kScanThreads = 512;
+#ifndef PK_SCAN_THREADS
+#define PK_SCAN_THREADS 512
+#endif
+constexpr int kScanThreads = PK_SCAN_THREADS;
 constexpr int kScanWarps = kScanThreads / 32;
 constexpr int kPrepThreads = 256;
 constexpr unsigned kFull = 0xffffffffu;
@@ -473,9 +476,24 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
             // lane had a match, with 3-4 lanes active: 44 % of this kernel's warp instructions.  The sum then runs in
             // the reference's field order (clubs, friends, text columns ascending), sigma(z(0)) for the joint fields
             // that are not in the queue, so every double is added exactly where the reference adds it.
-            double qv[2 + kMaxT], qd[2] = {0.0, 0.0};
-            uint8_t qf[2 + kMaxT];
+            // The first kQReg entries of the queue live in REGISTERS (static indices only); the rest overflow into a
+            // local array that is rarely touched.  Round 2's first version kept the whole queue in local memory:
+            // 624 bytes x 512 threads did not fit the L1 left beside ~200 KB of tables (local hit rate 50 %), and the
+            // kernel stalled on its own stack (long scoreboard 39 % of the warp cycles).
+            double qr0 = 0.0, qr1 = 0.0, qr2 = 0.0, qr3 = 0.0, qd0 = 0.0, qd1 = 0.0;
+            uint32_t qfp = 0u;                       // fields of the register entries, one byte each
+            double qov[2 + kMaxT - 4];
+            uint8_t qfov[2 + kMaxT - 4];
             int qn = 0;
+            auto q_push = [&](int f, double v) {
+                if (qn == 0) qr0 = v; else if (qn == 1) qr1 = v; else if (qn == 2) qr2 = v; else if (qn == 3) qr3 = v;
+                else { qov[qn - 4] = v; qfov[qn - 4] = (uint8_t)f; }
+                if (qn < 4) qfp |= (uint32_t)f << (8 * qn);
+                ++qn;
+            };
+            auto q_take = [&](int k) -> double {
+                return k == 0 ? qr0 : k == 1 ? qr1 : k == 2 ? qr2 : k == 3 ? qr3 : qov[k - 4];
+            };
             uint64_t matched = 0ull;
             bool has_set[2] = {false, false};
             int inter_of[2] = {0, 0};
@@ -506,10 +524,9 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
                     inter_of[which] = inter;
                     ++used;
                     if (inter > 0) {
-                        qf[qn] = (uint8_t)(5 + which);
-                        qv[qn] = (double)inter;
-                        qd[which] = (which ? q_sqf : q_sqc) * __hiloint2double(which ? (int)h4.w : (int)h4.y, which ? (int)h4.z : (int)h4.x);
-                        ++qn;
+                        const double dd = (which ? q_sqf : q_sqc) * __hiloint2double(which ? (int)h4.w : (int)h4.y, which ? (int)h4.z : (int)h4.x);
+                        if (which) qd1 = dd; else qd0 = dd;
+                        q_push(5 + which, (double)inter);
                     }
                     if (FIELDS) { fo[1 + which] = 0.0f; fo[3 + T + which] = __int_as_float(inter); }
                 }
@@ -544,39 +561,43 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
                         const double wj = __shfl_sync(kFull, wc, j);
                         const int ct = (int)(__shfl_sync(kFull, key, j) >> kTokBits);
                         if (ct != cur_ct) {              // warp-uniform: the previous column is complete
-                            if (dot != 0.0) { qf[qn] = (uint8_t)(kNumFixed + cur_ct); qv[qn] = dot; ++qn; matched |= 1ull << cur_ct; }
+                            if (dot != 0.0) { q_push(kNumFixed + cur_ct, dot); matched |= 1ull << cur_ct; }
                             dot = 0.0;
                             cur_ct = ct;
                         }
                         if ((mj >> lane) & 1u) dot = __dadd_rn(dot, __dmul_rn(vals[bj + __popc(mj & lane_lt)], wj));
                     }
                 }
-                if (dot != 0.0) { qf[qn] = (uint8_t)(kNumFixed + cur_ct); qv[qn] = dot; ++qn; matched |= 1ull << cur_ct; }
+                if (dot != 0.0) { q_push(kNumFixed + cur_ct, dot); matched |= 1ull << cur_ct; }
                 used += __popcll(joint);
             }
             // evaluation pass: queue entry k of every lane of the warp together
-            for (int k = 0; k < qn; ++k) {
-                const int f = qf[k];
+            auto q_eval = [&](int f, double v) -> double {
                 double den;
                 if (f >= kNumFixed) {          // the candidate cell's norm sits at the rank of the column in its mask
                     const int ct = f - kNumFixed;
                     const uint4 cc = __ldg(cr + (o_cells >> 2) + __popcll(c_mask & ((1ull << ct) - 1ull)));
                     den = nq[ct * 32 + lane] * __hiloint2double((int)cc.w, (int)cc.z);
-                } else den = qd[f - 5];
-                const float s = (den > 0.0) ? (float)(qv[k] / den) : 0.0f;
-                qv[k] = (f >= kNumFixed && s == 1.0f) ? N->sig1[f] : pk_sigmoid(pk_z(N, f, (double)s));
+                } else den = (f == 5) ? qd0 : qd1;
+                const float s = (den > 0.0) ? (float)(v / den) : 0.0f;
                 if (FIELDS) fo[f >= kNumFixed ? 3 + (f - kNumFixed) : f - 4] = s;
-            }
+                return (f >= kNumFixed && s == 1.0f) ? N->sig1[f] : pk_sigmoid(pk_z(N, f, (double)s));
+            };
+            if (qn > 0) qr0 = q_eval((int)(qfp & 0xffu), qr0);
+            if (qn > 1) qr1 = q_eval((int)((qfp >> 8) & 0xffu), qr1);
+            if (qn > 2) qr2 = q_eval((int)((qfp >> 16) & 0xffu), qr2);
+            if (qn > 3) qr3 = q_eval((int)(qfp >> 24), qr3);
+            for (int k = 4; k < qn; ++k) qov[k - 4] = q_eval((int)qfov[k - 4], qov[k - 4]);
             // ordered sum
             {
                 int k = 0;
-                if (has_set[0]) sum += (inter_of[0] > 0) ? qv[k++] : N->sig0[5];
-                if (has_set[1]) sum += (inter_of[1] > 0) ? qv[k++] : N->sig0[6];
+                if (has_set[0]) sum += (inter_of[0] > 0) ? q_take(k++) : N->sig0[5];
+                if (has_set[1]) sum += (inter_of[1] > 0) ? q_take(k++) : N->sig0[6];
                 uint64_t jm = (c_ncells > 0) ? joint : 0ull;
                 while (jm) {
                     const int ct = __ffsll((long long)jm) - 1;
                     jm &= jm - 1;
-                    if ((matched >> ct) & 1ull) sum += qv[k++];
+                    if ((matched >> ct) & 1ull) sum += q_take(k++);
                     else {
                         sum += N->sig0[kNumFixed + ct];
                         if (FIELDS) fo[3 + ct] = 0.0f;
