@@ -19,7 +19,7 @@
 namespace pk {
 
 #ifndef PK_SCAN_THREADS
-#define PK_SCAN_THREADS 512
+#define PK_SCAN_THREADS 1024
 #endif
 constexpr int kScanThreads = PK_SCAN_THREADS;
 constexpr int kScanWarps = kScanThreads / 32;
@@ -378,11 +378,12 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
     (void)total_possible;
 
     // ---- candidate loop -------------------------------------------------------------------------
-    // A warp claims one candidate at a time from the item's cursor and keeps two claims ahead of the one it is
-    // scoring: the record offset of claim + 2 is being loaded while the whole record of claim + 1 (header, id lists,
-    // cells, token keys, weights: ~1.1 KB of a randomly placed row in the list modes) is prefetched, one 128-byte
-    // line per lane.  Without it a candidate costs a chain of dependent DRAM round trips (row -> offset -> header ->
-    // keys -> weights) that the 16 warps of the CTA cannot hide: the kernel ran at ~17 % of its issue slots.
+    // A warp claims one candidate at a time from the item's cursor in shared memory.  What bounds the kernel is the
+    // latency of its dependent chains (fp64 division / exp, table probes, the record's header -> keys -> weights),
+    // so it runs with as many warps as the register file allows: on the collaborative batch of the bench 512
+    // threads x 111 registers take 18.2 ms, 768 x 72 14.7 ms, 1024 x 64 12.8 ms.  PK_SCAN_PREFETCH keeps two claims
+    // ahead and prefetches the whole next record, one 128-byte line per lane (measured: 2 % at 512 threads, nothing
+    // at 768; its ~20 registers are worth more as occupancy).
     auto claim = [&]() {
         int c = 0;
         if (lane == 0) c = atomicAdd(next, 1);
@@ -392,22 +393,17 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
         if (ci >= it.cand_end) return -1;
         return P.cand_rows ? (int64_t)__ldg(P.cand_rows + ci) : (int64_t)ci;
     };
+#ifdef PK_SCAN_PREFETCH
     int c_cur = claim(), c_n1 = claim(), c_n2 = claim();
     int64_t r_cur = row_of(c_cur), r_n1 = row_of(c_n1), r_n2 = row_of(c_n2);
     uint64_t o_n1 = 0, e_n1 = 0, o_n2 = 0, e_n2 = 0;
     if (r_n1 >= 0) { o_n1 = __ldg(P.rec_off + r_n1); e_n1 = __ldg(P.rec_off + r_n1 + 1); }
     if (r_n2 >= 0) { o_n2 = __ldg(P.rec_off + r_n2); e_n2 = __ldg(P.rec_off + r_n2 + 1); }
     for (; c_cur < it.cand_end; ) {
-#ifndef PK_SCAN_NO_PREFETCH
         if (r_n1 >= 0 && o_n1 + 8ull * lane < e_n1) {
             const uint4* pf = P.rec + o_n1 + 8ull * lane;
-#ifdef PK_SCAN_PREFETCH_L1
-            asm volatile("prefetch.global.L1 [%0];" :: "l"(pf));
-#else
             asm volatile("prefetch.global.L2 [%0];" :: "l"(pf));
-#endif
         }
-#endif
         const int ci = c_cur;
         const int64_t crow = r_cur;
         // rotate the claims (the loads of claim + 2 stay in flight while this candidate is scored)
@@ -415,6 +411,12 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
         c_n1 = c_n2; r_n1 = r_n2; o_n1 = o_n2; e_n1 = e_n2;
         c_n2 = claim(); r_n2 = row_of(c_n2);
         if (r_n2 >= 0) { o_n2 = __ldg(P.rec_off + r_n2); e_n2 = __ldg(P.rec_off + r_n2 + 1); }
+#else
+    for (;;) {
+        const int ci = claim();
+        if (ci >= it.cand_end) break;
+        const int64_t crow = row_of(ci);
+#endif
         {
             if (crow < 0) continue;   // empty shortlist slot (warp-uniform)
             const uint4* cr = P.rec + P.rec_off[crow];
@@ -479,7 +481,9 @@ __global__ void __launch_bounds__(kScanThreads, 1) fas_scan_kernel(const ScanPar
             // The first kQReg entries of the queue live in REGISTERS (static indices only); the rest overflow into a
             // local array that is rarely touched.  Round 2's first version kept the whole queue in local memory:
             // 624 bytes x 512 threads did not fit the L1 left beside ~200 KB of tables (local hit rate 50 %), and the
-            // kernel stalled on its own stack (long scoreboard 39 % of the warp cycles).
+            // local loads missed half the time.  (Staging the entries of the whole warp in shared memory and evaluating
+            // them 32 at a time was also built: 14.7 -> 14.1 ms at 768 threads, but +28 % instructions and 35 KB of
+            // shared memory; at 1024 threads it lost to this version.)
             double qr0 = 0.0, qr1 = 0.0, qr2 = 0.0, qr3 = 0.0, qd0 = 0.0, qd1 = 0.0;
             uint32_t qfp = 0u;                       // fields of the register entries, one byte each
             double qov[2 + kMaxT - 4];
