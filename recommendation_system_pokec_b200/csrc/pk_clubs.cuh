@@ -3,18 +3,22 @@
 // The reference walks, per user, 1-hop entries (every friend f with w_f = FAS(user,f) > 0 adds w_f to
 // each of f's clubs) and then 2-hop entries (every fof in adj[f] with s = FAS(f,fof) > 0 adds w_f*s to
 // each of fof's clubs), skipping the user's own clubs, accumulating in double in visiting order.
-// The FAS values come from the store-mode scan; this kernel does the scatter.  To keep every club's
-// double sum in the reference's order (so the float cast is bit-identical), the scatter is made
-// deterministic: the distinct clubs of a user are first hashed into a per-user table (order-free),
-// then thread t of the CTA replays the ordered contribution stream and adds only into the slots it
-// owns (slot % blockDim == t).  Different clubs proceed in parallel, one club is always summed by one
-// thread in stream order.
+// The FAS values come from the pair kernel (or the per-edge cache); this kernel does the scatter.  To keep every
+// club's double sum in the reference's order (so the float cast is bit-identical) it is deterministic:
+//   A  all threads, parallel over the edges: the distinct clubs of the user are hashed into a per-user table
+//      (order-free) and every contribution gets {table slot, value} at its position in the visiting order;
+//   B  every warp replays that flat stream and adds only into the table slots it owns (slot % warps): contributions to
+//      different clubs commute, a club is always summed by one warp in stream order;
+//   C  all threads: sort keys, compacted.
 #pragma once
 #include "pk_layout.h"
 
 namespace pk {
 
-constexpr int kClubThreads = 256;
+#ifndef PK_CLUB_THREADS
+#define PK_CLUB_THREADS 256
+#endif
+constexpr int kClubThreads = PK_CLUB_THREADS;
 
 struct ClubEdge {
     int64_t w_idx;        // index of w_f in the scan output
@@ -54,6 +58,14 @@ __global__ void __launch_bounds__(kClubThreads) clubs_scatter_kernel(const ClubP
     unsigned long long* keys = reinterpret_cast<unsigned long long*>(P.slot_key + sb);
     double* acc = P.slot_acc + sb;
     int32_t* cslot = P.con_slot + sb;
+    // value of each contribution: lives in the user's slice of out_keys until phase C overwrites it with the keys
+    // (a user has at most cap / 2 contributions)
+    double* cval = reinterpret_cast<double*>(P.out_keys + sb);
+    uint32_t n_con;
+    {
+        const ClubEdge el = P.edges[ee - 1];
+        n_con = P.con_off[ee - 1] + reinterpret_cast<const uint32_t*>(P.rec + P.rec_off[el.target_row])[8];
+    }
 
     // phase A (parallel over edges): validity of each entry, distinct clubs into the table
     for (int e = eb + tid; e < ee; e += kClubThreads) {
@@ -64,6 +76,8 @@ __global__ void __launch_bounds__(kClubThreads) clubs_scatter_kernel(const ClubP
         const uint32_t* tr = reinterpret_cast<const uint32_t*>(P.rec + P.rec_off[ed.target_row]);
         const uint32_t ncl = tr[8];
         const uint32_t c0 = P.con_off[e];
+        double v = w;
+        if (ed.s_idx >= 0) v = __dmul_rn(w, (double)P.fas[ed.s_idx]);       // contrib = wuf * s_f_fof (:58)
         for (uint32_t j = 0; j < ncl; ++j) {
             const uint32_t club = tr[kHdrWords + j];
             bool skip = !valid;
@@ -84,38 +98,62 @@ __global__ void __launch_bounds__(kClubThreads) clubs_scatter_kernel(const ClubP
                 }
             }
             cslot[c0 + j] = sl;
+            cval[c0 + j] = v;
         }
     }
     __syncthreads();
 
-    // phase B: ONE warp replays the ordered stream -- edge after edge, the target's clubs across the lanes -- so every
-    // club's double sum is taken in the reference's visiting order (round 1 let all 256 threads replay the whole
-    // stream and add only into the slots they owned: 256 x the reads).  Two lanes meet in one slot only when a target
-    // lists a club twice; the lowest of them then adds the value once per occurrence.
-    if (tid < 32) {
-        const int lane = tid;
-        for (int e = eb; e < ee; ++e) {
-            const ClubEdge ed = P.edges[e];
-            const double w = (double)P.fas[ed.w_idx];
-            double v = w;
-            if (ed.s_idx >= 0) v = __dmul_rn(w, (double)P.fas[ed.s_idx]);   // contrib = wuf * s_f_fof (:58)
-            const uint32_t c0 = P.con_off[e];
-            const uint32_t c1 = (e + 1 < ee) ? P.con_off[e + 1] : 0xffffffffu;
-            const uint32_t* tr = reinterpret_cast<const uint32_t*>(P.rec + P.rec_off[ed.target_row]);
-            const uint32_t ncl = (c1 != 0xffffffffu) ? (c1 - c0) : tr[8];
-            for (uint32_t j0 = 0; j0 < ncl; j0 += 32) {
-                const uint32_t j = j0 + lane;
-                const int32_t sl = (j < ncl) ? cslot[c0 + j] : -1;
-                const uint32_t live = __ballot_sync(0xffffffffu, sl >= 0);
-                const uint32_t same = __match_any_sync(0xffffffffu, sl >= 0 ? sl : -1 - lane) & live;
-                if (sl >= 0 && (__ffs(same) - 1) == lane) {
-                    double a = acc[sl];
-                    for (int r = __popc(same); r > 0; --r) a = __dadd_rn(a, v);
-                    acc[sl] = a;
-                }
-                __syncwarp();
+    // phase B: the ordered stream is replayed by ALL warps, warp w adding only into the table slots it owns
+    // (slot % warps == w): every club is still summed by one warp in stream order, different clubs proceed in parallel.
+    // A warp scans the whole stream 32 contributions at a time (the next chunk's loads in flight), COMPACTS its own
+    // contributions into a 64-entry ring in shared memory and adds them 32 at a time; contributions to the same slot
+    // inside such a batch are added by the lowest lane, in order.  (Round 1 let every THREAD replay the whole stream;
+    // the first rewrite of round 2 used one warp edge by edge -- ~370 dependent L2 round trips per user, 9 ms per
+    // 4096-user batch; one warp over the flat stream took 3.3 ms, bound by the users with the most entries: 8000
+    // edges = 1200 serial read-modify-write steps.)
+    constexpr int kWarps = kClubThreads / 32;
+    __shared__ int32_t ring_sl[kWarps][64];
+    __shared__ double ring_v[kWarps][64];
+    {
+        const int lane = tid & 31, warp = tid >> 5;
+        const uint32_t lane_lt = (1u << lane) - 1u;
+        int32_t* rsl = ring_sl[warp];
+        double* rv = ring_v[warp];
+        int cnt = 0, done = 0;                                    // warp-uniform
+        auto add_batch = [&](int n) {
+            int32_t sl = -1;
+            if (lane < n) sl = rsl[(done + lane) & 63];
+            const uint32_t live = __ballot_sync(0xffffffffu, sl >= 0);
+            const uint32_t same = __match_any_sync(0xffffffffu, sl >= 0 ? sl : -1 - lane) & live;
+            if (sl >= 0 && (__ffs(same) - 1) == lane) {
+                double a = acc[sl];
+                for (uint32_t mm = same; mm; mm &= mm - 1u) a = __dadd_rn(a, rv[(done + __ffs(mm) - 1) & 63]);
+                acc[sl] = a;
             }
+            __syncwarp();
+        };
+        int32_t sl_n = -1;
+        double v_n = 0.0;
+        if ((uint32_t)lane < n_con) { sl_n = cslot[lane]; v_n = cval[lane]; }
+        for (uint32_t c0 = 0; c0 < n_con; c0 += 32) {
+            const int32_t sl = sl_n;
+            const double v = v_n;
+            const uint32_t cn = c0 + 32u + lane;
+            sl_n = -1;
+            if (cn < n_con) { sl_n = cslot[cn]; v_n = cval[cn]; }
+            const bool mine = sl >= 0 && (sl & (kWarps - 1)) == warp;
+            const uint32_t mm = __ballot_sync(0xffffffffu, mine);
+            if (mm == 0u) continue;
+            if (mine) {
+                const int pos = (cnt + __popc(mm & lane_lt)) & 63;
+                rsl[pos] = sl;
+                rv[pos] = v;
+            }
+            cnt += __popc(mm);
+            __syncwarp();
+            if (cnt - done >= 32) { add_batch(32); done += 32; }
         }
+        if (cnt > done) add_batch(cnt - done);
     }
     __syncthreads();
 
