@@ -16,7 +16,7 @@
 namespace pk {
 
 #ifndef PK_CLUB_THREADS
-#define PK_CLUB_THREADS 256
+#define PK_CLUB_THREADS 512
 #endif
 constexpr int kClubThreads = PK_CLUB_THREADS;
 
