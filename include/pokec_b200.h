@@ -174,6 +174,19 @@ int pk_candidates(pk_store* s, int mode, int32_t uid, int limit, int32_t* out, i
  * the loaded adjacency; single-user drop-in calls keep walking the caller's live rows on the host). */
 int pk_candidates_batch(pk_store* s, int mode, int nq, const int32_t* q_uid, int limit, int32_t* out_ids, int32_t* out_cnt);
 
+/* pk_candidates_batch on DEVICE buffers, allocating nothing.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same kernel, same lists; its scratch (per-warp hash sets, epochs, work-queue cursor, the
+ * [nq] row output) lives in one file-scope static device array of about 4 MB that every GPU loading the library holds
+ * until exit, which bounds the call: limit in [1, 992], nq <= 8192 (PK_ERR_UNSUPPORTED beyond, with a message).
+ * d_q_uid [nq], d_out_ids [nq][limit] and d_out_cnt [nq] are DEVICE pointers on the store's device.  The adjacency must
+ * already be resident (PK_ERR_STATE otherwise: call pk_candidates_batch or a batched pk_recommend once first).  No
+ * cudaMalloc / cudaFree / allocating library call is made.  Asynchronous on the store's stream: the inputs must be
+ * complete before the call, pk_sync() before the outputs are read.  Every call on a device shares the array: calls that
+ * overlap on the GPU (two stores or streams of one device) race -- serialise them. */
+int pk_candidates_batch_noalloc(pk_store* s, int mode, int nq, const int32_t* d_q_uid, int limit, int32_t* d_out_ids,
+                                int32_t* d_out_cnt);
+
 /* ---- multi-GPU plumbing (one process per GPU; the all-gather itself is the caller's NCCL) ----- */
 
 /* Local top-k of the shard as packed sort keys on the DEVICE: d_keys is a device buffer of

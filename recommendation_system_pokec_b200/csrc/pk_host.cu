@@ -2845,6 +2845,80 @@ int pk_candidates_batch(pk_store* s, int mode, int nq, const int32_t* q_uid, int
     return PK_OK;
 }
 
+// ---- pk_candidates_batch_noalloc: the raw device expansion on a STATIC scratch array ------------------------------------
+//
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  expand_kernel needs a per-warp hash
+// set, its epoch tags, a work-queue cursor and a [nq] row output; here they live in one file-scope device array instead
+// of the store's growable buffers.  Every GPU that loads the library holds the array (about 4 MB) until exit.
+//   layout (8-byte words): [kNaWarps][kNaTabCap] tables | kNaWarps epochs (uint32) | cursor (4 ints) | kNaMaxQ rows (int32)
+// The epoch-tagged tables never need clearing between calls (a call continues the epochs the last one left, exactly as
+// the store's own scratch does between launches); the cursor must start at zero and is cleared on every call.  Calls
+// share the array: two calls that overlap on the GPU (different stores / streams of one device) race.
+constexpr int kNaCtas = 32;                                   // CTAs of the no-alloc launch
+constexpr int kNaWarps = kNaCtas * kExpWarps;                 // 256 warps
+constexpr uint32_t kNaTabCap = 2048;                          // slots per warp: >= 2 (limit + 32)
+constexpr int kNaMaxLimit = (int)(kNaTabCap / 2) - 32;        // 992
+constexpr int kNaMaxQ = 8192;                                 // query users per call
+constexpr size_t kNaOffEpoch = (size_t)kNaWarps * kNaTabCap;  // in 8-byte words
+constexpr size_t kNaOffNext = kNaOffEpoch + kNaWarps / 2;
+constexpr size_t kNaOffRow = kNaOffNext + 32;
+constexpr size_t kNaWords = kNaOffRow + kNaMaxQ / 2;
+static __device__ __align__(256) unsigned long long pk_noalloc_scratch[kNaWords];
+
+// In host code `pk_noalloc_scratch` is a host-side stand-in, not a device address: the device address is asked for
+// once per device, with that device current, and cached.
+static int noalloc_scratch_ptr(int device, unsigned long long** out) {
+    constexpr int kMaxDev = 64;
+    static unsigned long long* ptrs[kMaxDev];
+    static std::atomic<int> have[kMaxDev];
+    if (device < 0 || device >= kMaxDev) return fail(PK_ERR_UNSUPPORTED, "device ordinal %d outside [0, %d)", device, kMaxDev);
+    if (!have[device].load(std::memory_order_acquire)) {
+        CK(cudaSetDevice(device));
+        void* p = nullptr;
+        CK(cudaGetSymbolAddress(&p, pk_noalloc_scratch));
+        if (!p) return fail(PK_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+        ptrs[device] = (unsigned long long*)p;                 // two racing callers store the same value
+        have[device].store(1, std::memory_order_release);
+    }
+    *out = ptrs[device];
+    return PK_OK;
+}
+
+int pk_candidates_batch_noalloc(pk_store* s, int mode, int nq, const int32_t* d_q_uid, int limit, int32_t* d_out_ids,
+                                int32_t* d_out_cnt) {
+    if (!s || nq < 0 || (nq > 0 && (!d_q_uid || !d_out_ids || !d_out_cnt))) return fail(PK_ERR_ARG, "bad argument");
+    if (!s->loaded) return fail(PK_ERR_STATE, "no world loaded");
+    if (mode != PK_MODE_GRAPH && mode != PK_MODE_COLLAB) return fail(PK_ERR_ARG, "bad mode %d", mode);
+    if (limit < 1 || limit > kNaMaxLimit)
+        return fail(PK_ERR_UNSUPPORTED, "pk_candidates_batch_noalloc takes limits in [1, %d] (static scratch); got %d", kNaMaxLimit, limit);
+    if (nq > kNaMaxQ)
+        return fail(PK_ERR_UNSUPPORTED, "pk_candidates_batch_noalloc takes at most %d query users per call; got %d", kNaMaxQ, nq);
+    if (!s->adj_override.empty() || s->adj.size() > 0x7fffff00ull)
+        return fail(PK_ERR_UNSUPPORTED, "the device expansion needs an adjacency without overridden rows");
+    if (s->graph_dirty)
+        return fail(PK_ERR_STATE, "the adjacency is not resident on the device yet and this entry point allocates nothing: "
+                                  "call pk_candidates_batch (or a batched pk_recommend) once first");
+    if (nq == 0) return PK_OK;
+    CK(cudaSetDevice(s->device));
+    unsigned long long* scratch = nullptr;
+    TRY(noalloc_scratch_ptr(s->device, &scratch));
+    int* next = reinterpret_cast<int*>(scratch + kNaOffNext);
+    CK(cudaMemsetAsync(next, 0, 16, s->stream));
+    ExpandParams X;
+    memset(&X, 0, sizeof(X));
+    X.G = dev_graph(s);
+    X.q_uid = d_q_uid; X.nq = nq; X.mode = mode; X.limit = limit; X.raw = 1; X.slots_only = 0;
+    X.scratch = scratch; X.epoch = reinterpret_cast<uint32_t*>(scratch + kNaOffEpoch); X.tab_cap = kNaTabCap;
+    X.next_query = next; X.cand_cap = limit;
+    X.q_row = reinterpret_cast<int32_t*>(scratch + kNaOffRow); X.cand_out = d_out_ids; X.cand_cnt = d_out_cnt;
+    const int ctas = std::max(1, std::min(kNaCtas, (nq + kExpWarps - 1) / kExpWarps));
+    expand_kernel<<<ctas, kExpWarps * 32, 0, s->stream>>>(X);
+    ++s->stat_launches;
+    CK(cudaGetLastError());
+    return PK_OK;
+}
+
 int pk_debug_prefilter(pk_store* s, int nq, const int32_t* q_uid, int64_t row_begin, int64_t row_end, float* out_approx,
                        float* out_exact) {
     TRY(ensure_ready(s));

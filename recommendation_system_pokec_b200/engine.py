@@ -26,7 +26,7 @@ ABI_SYMBOLS = (
     "pk_idf_size", "pk_get_idf", "pk_set_adj_row", "pk_pair_similarity", "pk_pair_fields", "pk_pair_overlap",
     "pk_fullscan_topk", "pk_fullscan_prepare", "pk_fullscan_execute", "pk_fullscan_fetch", "pk_fullscan_keys", "pk_recommend", "pk_candidates", "pk_fullscan_local_keys", "pk_merge_keys", "pk_sync",
     "pk_normalizers_from_pairs", "pk_edge_cache_build", "pk_edge_cache_drop", "pk_edge_cache_row", "pk_fullscan_execute_shortlists", "pk_fullscan_shortlist_keys", "pk_fullscan_execute_finish",
-    "pk_stream", "pk_stat", "pk_debug_prefilter", "pk_world_save", "pk_world_open", "pk_world_close", "pk_candidates_batch", "pk_store_set_option", "pk_fullscan_theta_export", "pk_fullscan_theta_ptr", "pk_fullscan_theta_peers",
+    "pk_stream", "pk_stat", "pk_debug_prefilter", "pk_world_save", "pk_world_open", "pk_world_close", "pk_candidates_batch", "pk_candidates_batch_noalloc", "pk_store_set_option", "pk_fullscan_theta_export", "pk_fullscan_theta_ptr", "pk_fullscan_theta_peers",
 )
 STAT_KERNEL_LAUNCHES, STAT_PAIRS_SCORED, STAT_STORE_BYTES, STAT_SCAN_KERNEL_NS, STAT_SCAN_LAUNCHES, STAT_GROUPS, \
     STAT_SHARD_RECORD_BYTES, STAT_H2D_BYTES, STAT_D2H_BYTES, STAT_PREFILTER, STAT_FALLBACK_QUERIES, STAT_RESCORE_NS, \
@@ -358,6 +358,12 @@ class DeviceRecommender:
         cnt = np.zeros(len(q), np.int32)
         _check(self.lib, self.lib.pk_candidates_batch(self.h, int(mode), len(q), ptr(q, i32p), int(limit), ptr(ids, i32p), ptr(cnt, i32p)))
         return ids, cnt
+
+    def candidates_batch_noalloc(self, mode, d_q_uid_ptr: int, nq, limit, d_out_ids_ptr: int, d_out_cnt_ptr: int):
+        """pk_candidates_batch on DEVICE buffers with static scratch (no allocation inside the call; limit <= 992,
+        nq <= 8192; the adjacency must already be resident).  Asynchronous on the store's stream: sync() before reading."""
+        _check(self.lib, self.lib.pk_candidates_batch_noalloc(self.h, int(mode), int(nq), C.c_void_p(d_q_uid_ptr), int(limit),
+                                                              C.c_void_p(d_out_ids_ptr), C.c_void_p(d_out_cnt_ptr)))
 
     # ---- multi-GPU plumbing --------------------------------------------------------------------------
     def fullscan_local_keys(self, q, k, exclude_mode, d_keys_ptr: int):
